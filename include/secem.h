@@ -1,0 +1,224 @@
+/*
+ * secem.h -- C ABI of libsecem.so: the B200 (sm_100a) implementation of safe-exploration's safe CEM-MPC hot path.
+ *
+ * The reference (oscarkey/safe-exploration @ 32f0582a + constrained-cem-mpc @ 4e207630) is pure Python and has no
+ * FFI; its plug-in boundaries on this path are the Python classes `CemSSM`, `DynamicsFunc`/`Constraint`,
+ * `ConstrainedCemMpc` and `SafeMPC`.  The Python mirror of those classes lives in
+ * `safe_exploration_b200/`; this header is what it binds with `ctypes`, and what a maintainer of the reference would
+ * bind from `safe_exploration/ssm_cem/` and `constrained_cem_mpc/`.  Each entry point cites the
+ * reference interface it replaces (paths relative to the reference root).
+ *
+ * Conventions
+ *   - every function returns 0 on success, <0 on error; `se_last_error()` returns the message (thread-local).
+ *   - all `dev_*` / `void*` array arguments are CALLER-OWNED DEVICE pointers, row-major contiguous, element type
+ *     selected by the handle's `se_dtype` (float or double); `host_*` arguments are host pointers to double.
+ *   - every call takes a `cudaStream_t` (passed as void*) and is asynchronous on it: no call synchronises the device
+ *     unless its comment says so.  Handles are not thread-safe; one handle per GPU.
+ *   - no torch / C++ types cross this boundary.
+ */
+#ifndef SECEM_H_
+#define SECEM_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define SE_MAX_NS 6   /* state dimension  (reference: pendulum 2, cart-pole 4, lunar lander 6) */
+#define SE_MAX_NU 3   /* action dimension */
+#define SE_MAX_FACES 16 /* faces of the safety polytope (pendulum 4, cart-pole 9) */
+#define SE_MAX_ACT_FACES 8
+#define SE_MAX_T 64   /* horizon */
+
+typedef enum { SE_F32 = 0, SE_F64 = 1 } se_dtype;
+
+/* objective selector: safe_exploration/safempc_cem.py:304-312 */
+typedef enum {
+  SE_OBJ_NEG_VARIANCE = 0, /* default: -sum_j sigma[:, j]                         (safempc_cem.py:310) */
+  SE_OBJ_ABS_STATE1 = 1,   /* |theta* - p[:, 1]|  (InvertedPendulum, environments.py:505-510)          */
+  SE_OBJ_NEG_LAST_STATE = 2 /* -p[:, -1]           (LunarLander, lunarlander.py:111-113)                */
+} se_objective;
+
+/* which variance-GEMM implementation runs (all produce the same quantity) */
+typedef enum {
+  SE_GEMM_AUTO = 0,
+  SE_GEMM_SIMT = 1, /* FP32 FFMA / FP64 DFMA register-tiled */
+  SE_GEMM_MMA = 2   /* FP64: DMMA m8n8k4; FP32: 3xTF32 mma.sync */
+} se_gemm_impl;
+
+typedef struct se_gp_s* se_gp_t;
+typedef struct se_cem_s* se_cem_t;
+
+const char* se_last_error(void);
+int se_version(void);
+
+/* ---------------------------------------------------------------------------------------------------------------
+ * Exact-GP state-space model.  Replaces GpCemSSM (safe_exploration/ssm_cem/gp_ssm_cem.py:17-133) behind the CemSSM
+ * interface (safe_exploration/ssm_cem/ssm_cem.py:11-131).
+ * ------------------------------------------------------------------------------------------------------------- */
+
+/* Build / refresh the device-side model.  Replaces GpCemSSM._update_model (gp_ssm_cem.py:96-101): the reference hands
+ * (X, Y^T) to GPyTorch which lazily builds its prediction caches; here the caller passes the materialised caches.
+ *   dev_x           [n, d]        training inputs, d = n_s + n_u
+ *   dev_alpha       [n_s, n]      (K_o + noise_o I)^-1 y_o
+ *   dev_linv        [n_s, n, n]   L_o^-1 (lower triangular), K_o + noise_o I = L_o L_o^T
+ *   host_lengthscale[n_s, d], host_outputscale[n_s], host_noise[n_s]  materialised (not raw) hyper-parameters of
+ *                   ScaleKernel(RBFKernel(ard)) + GaussianLikelihood (gp_ssm_cem.py:33, 45-57)
+ * The handle keeps its own padded copies; the caller may free its arrays once the stream has passed this call. */
+int se_gp_create(se_gp_t* out, int n_s, int n_u, int n, se_dtype dtype, const void* dev_x, const void* dev_alpha,
+                 const void* dev_linv, const double* host_lengthscale, const double* host_outputscale,
+                 const double* host_noise, void* stream);
+int se_gp_destroy(se_gp_t gp);
+/* workspace cap (bytes) for the materialised kernel rows K*[n_s, N_chunk, n]; default 6 GiB */
+int se_gp_set_workspace_limit(se_gp_t gp, uint64_t bytes);
+int se_gp_set_gemm_impl(se_gp_t gp, se_gemm_impl impl);
+
+/* mean [N, n_s], variance [N, n_s] (likelihood noise INCLUDED, gp_ssm_cem.py:93) and, if dev_jac != NULL, the
+ * Jacobian of the mean w.r.t. z, [N, n_s, d].  Replaces GpCemSSM.predict_without_jacobians / predict_with_jacobians
+ * (gp_ssm_cem.py:59-88) and compute_jacobian_fast (safe_exploration/ssm_pytorch/utilities.py:54-85).
+ *   dev_z [N, d] = [states | actions] */
+int se_gp_predict(se_gp_t gp, const void* dev_z, int64_t N, void* dev_mean, void* dev_var, void* dev_jac,
+                  void* stream);
+
+/* ---------------------------------------------------------------------------------------------------------------
+ * Problem constants: what CemSafeMPC._dynamics_func and construct_constraints close over
+ * (safe_exploration/safempc_cem.py:135-146, 162-200, 288-312).  All host pointers, double.
+ * ------------------------------------------------------------------------------------------------------------- */
+typedef struct {
+  int n_s, n_u;
+  const double* k_fb;    /* [n_u, n_s]  LQR feedback gain (safempc_simple.py:1118-1129)                   */
+  const double* a;       /* [n_s, n_s]  prior linear model (zeros when use_prior_model=False)              */
+  const double* b;       /* [n_s, n_u]                                                                     */
+  const double* l_mu;    /* [n_s]       Lipschitz constants (environments.py:477-482, 936-941)             */
+  const double* l_sigma; /* [n_s]                                                                          */
+  double c_safety;       /* beta_safety                                                                    */
+  int m_safe;            /* faces of the safety polytope h_mat x <= h_vec (0: no terminal constraint)      */
+  const double* h_mat;   /* [m_safe, n_s]                                                                  */
+  const double* h_vec;   /* [m_safe]                                                                       */
+  int m_act;             /* faces of the action polytope (0: no action constraint)                         */
+  const double* act_a;   /* [m_act, n_u]                                                                   */
+  const double* act_b;   /* [m_act]                                                                        */
+  double act_penalty;    /* 3   (constrained_cem_mpc.py:103)                                               */
+  double state_penalty;  /* 10  (safempc_cem.py:132)                                                       */
+  int objective;         /* se_objective                                                                   */
+  double objective_theta;
+  int all_states_constraint; /* 0 = reference behaviour (terminal ellipsoid only, quirk Q1); 1 = check every
+                                ellipsoid of the trajectory (intended semantics)                           */
+} se_problem;
+
+/* ---------------------------------------------------------------------------------------------------------------
+ * Reachability.  Replaces safe_exploration/gp_reachability_pytorch.py.
+ * ------------------------------------------------------------------------------------------------------------- */
+
+/* One ellipsoid step for N candidates: onestep_reachability (gp_reachability_pytorch.py:18-181), including
+ * compute_remainder_overapproximations_pytorch (utils.py:152-194), ellipsoid_from_rectangle_pytorch and
+ * sum_two_ellipsoids_pytorch (utils_ellipsoid.py:102-140, 282-309) and _fix_zeros_nans (:234-243).
+ *   dev_p [N, n_s]; dev_q [N, n_s, n_s] or NULL (point states); dev_u [N, n_u] (= k_ff)
+ *   dev_p1 [N, n_s], dev_q1 [N, n_s, n_s], dev_sigma [N, n_s]
+ *   dev_flags: int32[4] device counters, incremented: [0] #NaN variances, [1] #exact-zero variances / bounds
+ *              (the reference raises / warns on these; the Python wrapper reads them after the call) */
+int se_reach_onestep(se_gp_t gp, const se_problem* prob, const void* dev_p, const void* dev_q, const void* dev_u,
+                     int64_t N, void* dev_p1, void* dev_q1, void* dev_sigma, int32_t* dev_flags, void* stream);
+
+/* T steps for N ellipsoids: the loop of RolloutFunction._sample_trajectory (constrained_cem_mpc.py:175-183) with the
+ * dynamics of CemSafeMPC._dynamics_func, equivalently the NumPy multistep_reachability
+ * (safe_exploration/gp_reachability.py:168-221) batched over N.
+ *   dev_u [N, T, n_u]; host_k_fb_steps: NULL (use prob->k_fb for every step) or [T-1, n_u, n_s] per-step gains
+ *   (gp_reachability.py:213-216); outputs dev_p_all [N, T, n_s] / dev_q_all [N, T, n_s, n_s] / dev_sigma_all
+ *   [N, T, n_s] may be NULL; dev_pT [N, n_s], dev_qT [N, n_s, n_s] are the final ellipsoids. */
+int se_reach_multistep(se_gp_t gp, const se_problem* prob, const void* dev_p0, const void* dev_q0, const void* dev_u,
+                       int64_t N, int T, const double* host_k_fb_steps, void* dev_p_all, void* dev_q_all,
+                       void* dev_sigma_all, void* dev_pT, void* dev_qT, int32_t* dev_flags, void* stream);
+
+/* d [N, m] = h_mat p + c sqrt(diag(h_mat q h_mat^T)) - h_vec and inside[N] (uint8) = all(d < 0):
+ * lin_ellipsoid_safety_distance / is_ellipsoid_inside_polytope (gp_reachability_pytorch.py:184-231).
+ * dev_d or dev_inside may be NULL. */
+int se_safety_distance(se_dtype dtype, int n_s, int m, const double* host_h_mat, const double* host_h_vec,
+                       double c_safety, const void* dev_p, const void* dev_q, int64_t N, void* dev_d,
+                       uint8_t* dev_inside, void* stream);
+
+/* ---------------------------------------------------------------------------------------------------------------
+ * Constrained CEM.  Replaces ConstrainedCemMpc (constrained_cem_mpc.py:195-280) + RolloutFunction (:130-192) with the
+ * CemSafeMPC dynamics / constraints plugged in (safempc_cem.py:102-146, 288-312).
+ * ------------------------------------------------------------------------------------------------------------- */
+typedef struct {
+  int num_instances;   /* M independent MPC problems solved side by side (1 for ConstrainedCemMpc)              */
+  int num_rollouts;    /* N  population per instance (global, over all ranks)                                   */
+  int time_horizon;    /* T                                                                                     */
+  int num_elites;      /* E                                                                                     */
+  int num_iterations;  /* I                                                                                     */
+  int pick_best;       /* 0 = reference get_actions (first feasible rollout of the last iteration, quirk Q3);
+                          1 = arg-min objective among feasible                                                  */
+  /* sharding: this rank owns candidates [first_rollout, first_rollout + local_rollouts) of EVERY local instance;
+     world_size == 1: first_rollout = 0, local_rollouts = num_rollouts */
+  int first_rollout;
+  int local_rollouts;
+} se_cem_config;
+
+typedef struct {
+  void* actions;        /* [M, T, n_u]  chosen action sequence (undefined where found == 0)                      */
+  int32_t* found;       /* [M]          1 if a feasible rollout exists in the last iteration                     */
+  int32_t* best_id;     /* [M]          global rollout id that was returned, -1 if none                          */
+  void* means;          /* [I, M, T, n_u] sampling mean AFTER each iteration's refit, or NULL                    */
+  void* stds;           /* [I, M, T, n_u] or NULL                                                                */
+  int32_t* elite_ids;   /* [I, M, E]    global rollout ids in selection order, or NULL                           */
+  void* objective;      /* [I, M, N_local] or NULL                                                               */
+  void* constraint;     /* [I, M, N_local] or NULL                                                               */
+  void* rollout_actions;/* [I, M, N_local, T, n_u] or NULL                                                       */
+  void* trajectories;   /* [I, M, N_local, T+1, n_s + n_s^2] or NULL  ([p | vec(q)], PQFlattener layout)         */
+  int32_t* flags;       /* int32[4] counters as in se_reach_onestep, or NULL                                     */
+} se_cem_outputs;
+
+int se_cem_create(se_cem_t* out, se_gp_t gp, const se_problem* prob, const se_cem_config* cfg);
+int se_cem_destroy(se_cem_t cem);
+
+/* Attach an NCCL communicator (ncclComm_t as void*) for population sharding: one all-gather of the per-candidate
+ * (constraint, objective) costs per CEM iteration.  The reference has no counterpart (single process). */
+int se_cem_set_comm(se_cem_t cem, void* nccl_comm, int rank, int world_size);
+
+/* NCCL bootstrap helpers (the library resolves NCCL from the libnccl.so.2 the process already loaded, e.g. torch's):
+ * rank 0 calls se_nccl_unique_id, the 128 bytes travel to the other ranks by any means (the Python host uses
+ * torch.distributed.broadcast), then every rank calls se_nccl_comm_init.  No reference counterpart. */
+int se_nccl_unique_id(char* out128);
+int se_nccl_comm_init(void** comm_out, int world_size, const char* id128, int rank);
+int se_nccl_comm_destroy(void* comm);
+
+/* One MPC solve == ConstrainedCemMpc.get_actions (constrained_cem_mpc.py:259-280) for every instance.
+ *   dev_p0    [M, n_s]   initial (point) states
+ *   dev_noise NULL -> candidates are drawn on-device (Philox4x32-10 keyed by (seed, iteration, global rollout id));
+ *             else [I, M, N_global, T, n_u] standard-normal noise: actions = means + stds * noise, the RNG-fixed
+ *             equivalent of Normal(means, stds).sample((N,)) (constrained_cem_mpc.py:167) */
+int se_cem_solve(se_cem_t cem, const void* dev_p0, const void* dev_noise, uint64_t seed, const se_cem_outputs* out,
+                 void* stream);
+
+/* The sampler alone: writes what se_cem_solve would draw.  dev_noise_out [M, N_count, T, n_u]. */
+int se_cem_noise(se_dtype dtype, uint64_t seed, int iteration, int num_instances, int num_rollouts_global,
+                 int first_rollout, int count, int T, int n_u, void* dev_noise_out, void* stream);
+
+/* Elite selection + refit alone (constrained_cem_mpc.py:234-257) on given costs/actions, for parity tests of the
+ * integer part: dev_objective/dev_constraint [N], dev_actions [N, T, n_u] -> dev_elite_ids [E] (int32, selection
+ * order: ascending (cost, index)), dev_mean/dev_std [T, n_u]. */
+int se_cem_select_refit(se_dtype dtype, const void* dev_objective, const void* dev_constraint,
+                        const void* dev_actions, int N, int T, int n_u, int E, int32_t* dev_elite_ids,
+                        void* dev_mean, void* dev_std, void* stream);
+
+/* ---------------------------------------------------------------------------------------------------------------
+ * Measurement helpers (bench.py): launch counter and pipe-peak micro-benchmarks.
+ * ------------------------------------------------------------------------------------------------------------- */
+uint64_t se_launch_count(void);      /* kernels launched by this library since load / last reset */
+void se_launch_count_reset(void);
+/* Runs a register-resident FMA loop on every SM and returns the measured FLOP/s (synchronises the device).
+ * kind: 0 = FP32 FFMA, 1 = FP64 DFMA, 2 = FP64 DMMA m8n8k4 */
+int se_measure_peak(int kind, double* flops_out);
+/* Device time (ms, CUDA events recorded by the library on the launch stream) spent in the variance GEMM kernel and
+ * in the kernel-row kernel since the last reset, and their launch counts; timing must be enabled first
+ * (it inserts events, so leave it off outside benchmarks).  Synchronises the stream. */
+int se_gp_timing_enable(se_gp_t gp, int enable);
+int se_gp_timing_read(se_gp_t gp, double* gemm_ms, int64_t* gemm_launches, double* kstar_ms,
+                      int64_t* kstar_launches, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SECEM_H_ */

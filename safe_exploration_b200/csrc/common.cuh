@@ -1,0 +1,112 @@
+// common.cuh -- shared declarations of libsecem (sm_100a).  See include/secem.h for the C ABI.
+#pragma once
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include <atomic>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+
+#include "../../include/secem.h"
+
+#define SE_MAX_D (SE_MAX_NS + SE_MAX_NU)
+#define SE_HD __host__ __device__ __forceinline__
+
+namespace se {
+
+// ---- error plumbing ---------------------------------------------------------------------------------------------
+extern thread_local char g_last_error[1024];
+extern std::atomic<uint64_t> g_launches;
+
+inline int fail(const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_last_error, sizeof(g_last_error), fmt, ap);
+  va_end(ap);
+  return -1;
+}
+
+#define SE_CUDA(expr)                                                                                  \
+  do {                                                                                                 \
+    cudaError_t _e = (expr);                                                                           \
+    if (_e != cudaSuccess)                                                                             \
+      return ::se::fail("%s:%d: %s -> %s", __FILE__, __LINE__, #expr, cudaGetErrorString(_e));         \
+  } while (0)
+
+#define SE_TRY(expr)            \
+  do {                          \
+    int _r = (expr);            \
+    if (_r != 0) return _r;     \
+  } while (0)
+
+#define SE_REQUIRE(cond, ...)                        \
+  do {                                               \
+    if (!(cond)) return ::se::fail(__VA_ARGS__);     \
+  } while (0)
+
+// every kernel launch of the library goes through this so bench.py can report `gpu_launches`
+#define SE_LAUNCH(kernel, grid, block, smem, stream, ...)                                              \
+  do {                                                                                                 \
+    kernel<<<(grid), (block), (smem), (stream)>>>(__VA_ARGS__);                                        \
+    ::se::g_launches.fetch_add(1, std::memory_order_relaxed);                                          \
+    cudaError_t _e = cudaPeekAtLastError();                                                            \
+    if (_e != cudaSuccess)                                                                             \
+      return ::se::fail("%s:%d: launch %s -> %s", __FILE__, __LINE__, #kernel, cudaGetErrorString(_e)); \
+  } while (0)
+
+inline int64_t round_up(int64_t x, int64_t m) { return (x + m - 1) / m * m; }
+inline int64_t ceil_div(int64_t x, int64_t m) { return (x + m - 1) / m; }
+
+// ---- device-side views -------------------------------------------------------------------------------------------
+// GP model in its padded device layout (DESIGN.md "Data layout in HBM")
+template <typename T>
+struct GpDev {
+  int n;        // training points
+  int n_pad;    // n rounded up to the GEMM tile (128); padded entries are zero
+  int ns, nu, d;
+  const T* xt;     // [d][n_pad]        training inputs, one contiguous row per input dimension
+  const T* alpha;  // [ns][n_pad]       (K + noise I)^-1 y
+  const T* w;      // [ns][n_pad][n_pad] L^-1, lower triangular, row i = i-th row of L^-1
+  T inv_l2[SE_MAX_NS][SE_MAX_D];  // 1 / lengthscale^2
+  T outputscale[SE_MAX_NS];
+  T noise[SE_MAX_NS];
+};
+
+// problem constants in kernel-parameter form (converted from se_problem on the host)
+template <typename T>
+struct ProbDev {
+  int ns, nu, m_safe, m_act, objective, all_states;
+  T k_fb[SE_MAX_NU][SE_MAX_NS];
+  T a[SE_MAX_NS][SE_MAX_NS];
+  T b[SE_MAX_NS][SE_MAX_NU];
+  T bchol[SE_MAX_NS][SE_MAX_NS];  // lower Cholesky factor C of B = I + k_fb^T k_fb   (utils.py:175-177)
+  T bmat[SE_MAX_NS][SE_MAX_NS];   // B itself (used by the closed-form n_s <= 2 path on q B)
+  T l_mu[SE_MAX_NS], l_sigma[SE_MAX_NS];
+  T c_safety;
+  T h_mat[SE_MAX_FACES][SE_MAX_NS];
+  T h_vec[SE_MAX_FACES];
+  T act_a[SE_MAX_ACT_FACES][SE_MAX_NU];
+  T act_b[SE_MAX_ACT_FACES];
+  T act_penalty, state_penalty, objective_theta;
+};
+
+template <typename T>
+struct Num;
+template <>
+struct Num<float> {
+  static constexpr se_dtype dtype = SE_F32;
+  static __device__ __forceinline__ float exp_(float x) { return expf(x); }
+  static __device__ __forceinline__ float sqrt_(float x) { return sqrtf(x); }
+  static __device__ __forceinline__ float abs_(float x) { return fabsf(x); }
+};
+template <>
+struct Num<double> {
+  static constexpr se_dtype dtype = SE_F64;
+  static __device__ __forceinline__ double exp_(double x) { return exp(x); }
+  static __device__ __forceinline__ double sqrt_(double x) { return sqrt(x); }
+  static __device__ __forceinline__ double abs_(double x) { return fabs(x); }
+};
+
+}  // namespace se

@@ -1,0 +1,71 @@
+// inst_cem.cu -- launchers of the CEM kernels (sampling, selection + refit, pick)
+#include "cem_kernels.cuh"
+#include "launchers.cuh"
+
+namespace se {
+
+template <typename T>
+int launch_cem_sample(const ActionSrc<T>& src, int num_inst, int first, int n_local, int ns, const T* p0, T* actions,
+                      T* p, T* rec_actions, cudaStream_t stream) {
+  const int pairs = (src.tnu + 1) / 2;
+  const int64_t total = (int64_t)num_inst * n_local * pairs;
+  SE_LAUNCH((cem_sample_kernel<T>), (int)ceil_div(total, 256), 256, 0, stream, src, num_inst, first, n_local, ns, p0,
+            actions, p, rec_actions);
+  return 0;
+}
+
+template <typename T>
+int launch_cem_noise(uint64_t seed, int iteration, int num_inst, int n_global, int first, int count, int tnu, T* out,
+                     cudaStream_t stream) {
+  const int pairs = (tnu + 1) / 2;
+  const int64_t total = (int64_t)num_inst * count * pairs;
+  SE_LAUNCH((cem_noise_kernel<T>), (int)ceil_div(total, 256), 256, 0, stream, seed, iteration, num_inst, n_global,
+            first, count, tnu, out);
+  return 0;
+}
+
+template <typename T>
+int launch_cem_select_refit(const SelectArgs<T>& a, int num_inst, cudaStream_t stream) {
+  const int smem = kMaxElites * 12;
+  static bool attr_set = false;
+  if (!attr_set) {
+    SE_CUDA(cudaFuncSetAttribute(cem_select_refit_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    attr_set = true;
+  }
+  SE_LAUNCH((cem_select_refit_kernel<T>), num_inst, kSelThreads, smem, stream, a);
+  return 0;
+}
+
+template <typename T>
+int launch_cem_pick(const CostView<T>& costs, int n_global, int pick_best, const ActionSrc<T>& src, int num_inst,
+                    T* actions_out, int32_t* found, int32_t* best_id, cudaStream_t stream) {
+  SE_LAUNCH((cem_pick_kernel<T>), num_inst, 256, 0, stream, costs, n_global, pick_best, src, actions_out, found,
+            best_id);
+  return 0;
+}
+
+template <typename T>
+int launch_cem_pack_costs(const T* objective, const T* constraint, int64_t count, T* pack, T* rec_obj, T* rec_con,
+                          cudaStream_t stream) {
+  SE_LAUNCH((cem_pack_costs_kernel<T>), (int)ceil_div(count, 256), 256, 0, stream, objective, constraint, count, pack,
+            rec_obj, rec_con);
+  return 0;
+}
+
+int launch_cem_init_dist(double* mean, double* stdv, int count, cudaStream_t stream) {
+  SE_LAUNCH(cem_init_dist_kernel, (int)ceil_div(count, 256), 256, 0, stream, mean, stdv, count);
+  return 0;
+}
+
+#define SE_INST(T)                                                                                                  \
+  template int launch_cem_sample<T>(const ActionSrc<T>&, int, int, int, int, const T*, T*, T*, T*, cudaStream_t);   \
+  template int launch_cem_noise<T>(uint64_t, int, int, int, int, int, int, T*, cudaStream_t);                       \
+  template int launch_cem_select_refit<T>(const SelectArgs<T>&, int, cudaStream_t);                                 \
+  template int launch_cem_pick<T>(const CostView<T>&, int, int, const ActionSrc<T>&, int, T*, int32_t*, int32_t*,   \
+                                  cudaStream_t);                                                                    \
+  template int launch_cem_pack_costs<T>(const T*, const T*, int64_t, T*, T*, T*, cudaStream_t);
+SE_INST(float)
+SE_INST(double)
+#undef SE_INST
+
+}  // namespace se

@@ -1,0 +1,37 @@
+// inst_reach.cuh -- launch_reach_step<SE_T>, launch_safety_distance<SE_T>
+#include "launchers.cuh"
+#include "reach_kernels.cuh"
+
+namespace se {
+
+template <>
+int launch_reach_step<SE_T>(const ProbDev<SE_T>& pr, const StepIO<SE_T>& io, int64_t N, cudaStream_t stream) {
+  if (N <= 0) return 0;
+  const int grid = (int)ceil_div(N, 128);
+#define SE_CASE(NS_, NU_)                                                                         \
+  if (pr.ns == NS_ && pr.nu == NU_) {                                                             \
+    SE_LAUNCH((reach_step_kernel<SE_T, NS_, NU_>), grid, 128, 0, stream, pr, io, N);              \
+    return 0;                                                                                     \
+  }
+  SE_FOR_NS_NU(SE_CASE)
+#undef SE_CASE
+  return fail("unsupported (n_s, n_u) = (%d, %d)", pr.ns, pr.nu);
+}
+
+template <>
+int launch_safety_distance<SE_T>(const ProbDev<SE_T>& pr, const SE_T* p, const SE_T* q, int64_t N, SE_T* d,
+                                 uint8_t* inside, cudaStream_t stream) {
+  if (N <= 0) return 0;
+  const int grid = (int)ceil_div(N, 128);
+  switch (pr.ns) {
+#define SE_CASE(NS_)                                                                                   \
+  case NS_:                                                                                            \
+    SE_LAUNCH((safety_distance_kernel<SE_T, NS_>), grid, 128, 0, stream, pr, p, q, N, d, inside);      \
+    return 0;
+    SE_CASE(1) SE_CASE(2) SE_CASE(3) SE_CASE(4) SE_CASE(5) SE_CASE(6)
+#undef SE_CASE
+  }
+  return fail("unsupported n_s = %d", pr.ns);
+}
+
+}  // namespace se

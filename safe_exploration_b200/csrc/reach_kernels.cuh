@@ -1,0 +1,380 @@
+// reach_kernels.cuh -- per-candidate ellipsoid algebra (a13-a22 in SURVEY.md 8a), one thread per candidate with the
+// n_s x n_s matrices held in registers (all loops have compile-time bounds).
+//
+// Restates safe_exploration/gp_reachability_pytorch.py:18-231, utils.py:152-194, utils_ellipsoid.py:102-140, 282-309
+// and the constraint / objective epilogue of safempc_cem.py:102-132, 304-312 + constrained_cem_mpc.py:100-110.
+#pragma once
+#include "common.cuh"
+
+namespace se {
+
+// largest eigenvalue of the symmetric NS x NS matrix m (cyclic Jacobi, destroys m)
+template <typename T, int NS>
+__device__ __forceinline__ T sym_lambda_max(T (&m)[NS][NS]) {
+  if (NS == 1) return m[0][0];
+  const T eps = sizeof(T) == 8 ? T(1e-300) : T(1e-37);
+#pragma unroll 1
+  for (int sweep = 0; sweep < 12; ++sweep) {
+    T off = T(0), diag = T(0);
+#pragma unroll
+    for (int i = 0; i < NS; ++i) {
+      diag += m[i][i] * m[i][i];
+#pragma unroll
+      for (int j = i + 1; j < NS; ++j) off += m[i][j] * m[i][j];
+    }
+    const T tol = sizeof(T) == 8 ? T(1e-30) : T(1e-13);
+    if (off <= tol * diag || off < eps) break;
+#pragma unroll
+    for (int p = 0; p < NS - 1; ++p)
+#pragma unroll
+      for (int q = p + 1; q < NS; ++q) {
+        const T apq = m[p][q];
+        if (Num<T>::abs_(apq) > eps) {
+          const T theta = (m[q][q] - m[p][p]) / (T(2) * apq);
+          const T t = (theta >= T(0) ? T(1) : T(-1)) / (Num<T>::abs_(theta) + Num<T>::sqrt_(theta * theta + T(1)));
+          const T c = T(1) / Num<T>::sqrt_(t * t + T(1));
+          const T s = t * c;
+          m[p][p] -= t * apq;
+          m[q][q] += t * apq;
+          m[p][q] = m[q][p] = T(0);
+#pragma unroll
+          for (int r = 0; r < NS; ++r) {
+            if (r != p && r != q) {
+              const T arp = m[r][p], arq = m[r][q];
+              m[r][p] = m[p][r] = c * arp - s * arq;
+              m[r][q] = m[q][r] = s * arp + c * arq;
+            }
+          }
+        }
+      }
+  }
+  T best = m[0][0];
+#pragma unroll
+  for (int i = 1; i < NS; ++i) best = m[i][i] > best ? m[i][i] : best;
+  return best;
+}
+
+// r^2 = lambda_max(q B), B = I + k_fb^T k_fb  (utils.py:175-185).  For NS <= 2 the characteristic polynomial of the
+// (possibly non-symmetric) product q B is solved in closed form, like the reference's general `eig`; for NS >= 3 the
+// product is similar to the symmetric C^T q C (B = C C^T), whose spectrum Jacobi resolves to full relative accuracy
+// (q is symmetric on the hot path; the symmetric part is used).
+template <typename T, int NS>
+__device__ __forceinline__ T remainder_r_sqr(const T (&q)[NS][NS], const ProbDev<T>& pr) {
+  if (NS == 1) return q[0][0] * pr.bmat[0][0];
+  if (NS == 2) {
+    T m00 = q[0][0] * pr.bmat[0][0] + q[0][1] * pr.bmat[1][0];
+    T m01 = q[0][0] * pr.bmat[0][1] + q[0][1] * pr.bmat[1][1];
+    T m10 = q[1][0] * pr.bmat[0][0] + q[1][1] * pr.bmat[1][0];
+    T m11 = q[1][0] * pr.bmat[0][1] + q[1][1] * pr.bmat[1][1];
+    const T half_tr = T(0.5) * (m00 + m11);
+    const T half_diff = T(0.5) * (m00 - m11);
+    const T disc = half_diff * half_diff + m01 * m10;  // = (tr/2)^2 - det, cancellation-free form
+    return half_tr + Num<T>::sqrt_(disc);              // NaN if the pair is complex (reference asserts)
+  }
+  T tmp[NS][NS], m[NS][NS];
+#pragma unroll
+  for (int i = 0; i < NS; ++i)
+#pragma unroll
+    for (int j = 0; j < NS; ++j) {
+      T s = T(0);
+#pragma unroll
+      for (int k = j; k < NS; ++k) s += T(0.5) * (q[i][k] + q[k][i]) * pr.bchol[k][j];  // (q_sym C)[i][j]
+      tmp[i][j] = s;
+    }
+#pragma unroll
+  for (int i = 0; i < NS; ++i)
+#pragma unroll
+    for (int j = i; j < NS; ++j) {
+      T s = T(0);
+#pragma unroll
+      for (int k = i; k < NS; ++k) s += pr.bchol[k][i] * tmp[k][j];  // (C^T tmp)[i][j]
+      m[i][j] = m[j][i] = s;
+    }
+  return sym_lambda_max<T, NS>(m);
+}
+
+// _fix_zeros_nans (gp_reachability_pytorch.py:234-243), per element: NaN is counted in flags[0]; an exact zero is
+// counted in flags[1] and replaced by 1e-5.  (The reference additionally clamps *negative* entries, but only when the
+// batch also holds an exact zero; a negative value here turns into NaN at the next sqrt and is reported there.)
+template <typename T>
+__device__ __forceinline__ T fix_zero_nan(T x, int32_t* flags) {
+  if (x != x) {
+    if (flags) atomicAdd(&flags[0], 1);
+    return x;
+  }
+  if (x == T(0)) {
+    if (flags) atomicAdd(&flags[1], 1);
+    return T(1e-5);
+  }
+  return x;
+}
+
+// support-function distance of the ellipsoid (p, q) to every face; returns true iff all d < 0
+// (gp_reachability_pytorch.py:184-231; c_safety = 1 on the CEM path, quirk Q2)
+template <typename T, int NS>
+__device__ __forceinline__ bool inside_polytope(const T (&p)[NS], const T (&q)[NS][NS], const ProbDev<T>& pr,
+                                                T c_safety, T* d_out) {
+  bool inside = true;
+  for (int f = 0; f < pr.m_safe; ++f) {
+    T hp = T(0), hqh = T(0);
+#pragma unroll
+    for (int i = 0; i < NS; ++i) {
+      hp += pr.h_mat[f][i] * p[i];
+      T qh = T(0);
+#pragma unroll
+      for (int j = 0; j < NS; ++j) qh += q[i][j] * pr.h_mat[f][j];
+      hqh += pr.h_mat[f][i] * qh;
+    }
+    const T d = hp + c_safety * Num<T>::sqrt_(hqh) - pr.h_vec[f];
+    if (d_out) d_out[f] = d;
+    if (d >= T(0)) inside = false;  // (d_safety >= 0).sum() == 0, gp_reachability_pytorch.py:230-231
+  }
+  return inside;
+}
+
+template <typename T>
+struct StepIO {
+  // state (in / out, updated in place unless out pointers are given)
+  const T* p_in;   // [N, NS]
+  const T* q_in;   // [N, NS, NS] (ignored when point != 0)
+  T* p_out;        // [N, NS]
+  T* q_out;        // [N, NS, NS]
+  const T* u;      // actions, row stride u_stride
+  int64_t u_stride;
+  const T* mean;   // [N, NS]
+  const T* var;    // [N, NS]
+  const T* jac;    // [N, NS, D] (unused in the point branch)
+  T* sigma_out;    // [N, NS] or null
+  int point;       // 1 = all states are points (q = None branch)
+  // CEM bookkeeping (null when called from se_reach_*)
+  T* objective;    // [N] running sum
+  T* constraint;   // [N] written at the last step (and accumulated on every step if all_states)
+  int first_step, last_step;
+  const T* act_all;     // [N, T, NU] full action sequences for the action constraint (last step only)
+  int T_len;
+  // optional dumps
+  T* traj;         // [N, T+1, NS+NS*NS] or null
+  int t_index;     // step index (trajectory slot t_index + 1)
+  T* p_all;        // [N, T, NS] or null (multistep API)
+  T* q_all;        // [N, T, NS, NS]
+  T* sigma_all;    // [N, T, NS]
+  int32_t* flags;
+};
+
+template <typename T, int NS, int NU>
+__global__ void __launch_bounds__(128)
+reach_step_kernel(ProbDev<T> pr, StepIO<T> io, int64_t N) {
+  constexpr int D = NS + NU;
+  const int64_t c = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (c >= N) return;
+
+  T p[NS], u[NU], mu[NS], sg[NS];
+#pragma unroll
+  for (int i = 0; i < NS; ++i) {
+    p[i] = io.p_in[c * NS + i];
+    mu[i] = io.mean[c * NS + i];
+    sg[i] = fix_zero_nan<T>(io.var[c * NS + i], io.flags);  // sigm_0 (:76, :117)
+  }
+#pragma unroll
+  for (int j = 0; j < NU; ++j) u[j] = io.u[c * io.u_stride + j];
+
+  // p_0 = mu_0 + a p + b u   (:93-94, :132)
+  T p1[NS];
+#pragma unroll
+  for (int i = 0; i < NS; ++i) {
+    T s = mu[i];
+#pragma unroll
+    for (int k = 0; k < NS; ++k) s += pr.a[i][k] * p[k];
+#pragma unroll
+    for (int k = 0; k < NU; ++k) s += pr.b[i][k] * u[k];
+    p1[i] = s;
+  }
+
+  T q1[NS][NS];
+  if (io.point) {
+    // q_1 = diag(n_s (c_safety sqrt(sigm_0))^2)   (:82-91, utils_ellipsoid.py:302-309)
+#pragma unroll
+    for (int i = 0; i < NS; ++i)
+#pragma unroll
+      for (int j = 0; j < NS; ++j) q1[i][j] = T(0);
+#pragma unroll
+    for (int i = 0; i < NS; ++i) {
+      const T rk = fix_zero_nan<T>(pr.c_safety * Num<T>::sqrt_(sg[i]), io.flags);
+      q1[i][i] = T(NS) * rk * rk;
+    }
+  } else {
+    T q[NS][NS], h[NS][NS];
+#pragma unroll
+    for (int i = 0; i < NS; ++i)
+#pragma unroll
+      for (int j = 0; j < NS; ++j) q[i][j] = io.q_in[(c * NS + i) * NS + j];
+    // H = a + a_mu + (b_mu + b) k_fb   (:127-131)
+#pragma unroll
+    for (int i = 0; i < NS; ++i)
+#pragma unroll
+      for (int j = 0; j < NS; ++j) {
+        T s = pr.a[i][j] + io.jac[(c * NS + i) * D + j];
+#pragma unroll
+        for (int k = 0; k < NU; ++k) s += (io.jac[(c * NS + i) * D + NS + k] + pr.b[i][k]) * pr.k_fb[k][j];
+        h[i][j] = s;
+      }
+    // Q_0 = H q H^T   (:134)
+    T hq[NS][NS];
+#pragma unroll
+    for (int i = 0; i < NS; ++i)
+#pragma unroll
+      for (int j = 0; j < NS; ++j) {
+        T s = T(0);
+#pragma unroll
+        for (int k = 0; k < NS; ++k) s += h[i][k] * q[k][j];
+        hq[i][j] = s;
+      }
+    T tr_q0 = T(0);
+#pragma unroll
+    for (int i = 0; i < NS; ++i)
+#pragma unroll
+      for (int j = 0; j < NS; ++j) {
+        T s = T(0);
+#pragma unroll
+        for (int k = 0; k < NS; ++k) s += hq[i][k] * h[j][k];
+        q1[i][j] = s;  // holds Q_0 for now
+        if (i == j) tr_q0 += s;
+      }
+    // Lagrange remainder boxes   (:142-162, utils.py:152-194)
+    const T r_sqr = remainder_r_sqr<T, NS>(q, pr);
+    const T r = Num<T>::sqrt_(r_sqr);
+    T d_sig[NS], d_mu[NS];
+    T tr_sig = T(0), tr_mu = T(0);
+#pragma unroll
+    for (int i = 0; i < NS; ++i) {
+      const T ub_mean = pr.l_mu[i] * r_sqr;
+      const T ub_sigma = pr.l_sigma[i] * r;
+      const T bse = fix_zero_nan<T>(pr.c_safety * (Num<T>::sqrt_(sg[i]) + ub_sigma), io.flags);
+      d_sig[i] = T(NS) * bse * bse;
+      d_mu[i] = T(NS) * ub_mean * ub_mean;
+      tr_sig += d_sig[i];
+      tr_mu += d_mu[i];
+    }
+    // Q_L = Q_sigma (+) Q_mu ; q_1 = Q_L (+) Q_0   (:169-172, utils_ellipsoid.py:133-138; no guards, quirk Q8)
+    const T c1 = Num<T>::sqrt_(tr_sig / tr_mu);
+    T tr_l = T(0);
+    T d_l[NS];
+#pragma unroll
+    for (int i = 0; i < NS; ++i) {
+      d_l[i] = (T(1) + T(1) / c1) * d_sig[i] + (T(1) + c1) * d_mu[i];
+      tr_l += d_l[i];
+    }
+    const T c2 = Num<T>::sqrt_(tr_l / tr_q0);
+    const T f_l = T(1) + T(1) / c2, f_0 = T(1) + c2;
+#pragma unroll
+    for (int i = 0; i < NS; ++i)
+#pragma unroll
+      for (int j = 0; j < NS; ++j) q1[i][j] = f_0 * q1[i][j] + (i == j ? f_l * d_l[i] : T(0));
+  }
+
+  // ---- write the new ellipsoid ----
+#pragma unroll
+  for (int i = 0; i < NS; ++i) {
+    io.p_out[c * NS + i] = p1[i];
+    if (io.sigma_out) io.sigma_out[c * NS + i] = sg[i];
+#pragma unroll
+    for (int j = 0; j < NS; ++j) io.q_out[(c * NS + i) * NS + j] = q1[i][j];
+  }
+  if (io.p_all) {
+    const int64_t base = c * io.T_len + io.t_index;
+#pragma unroll
+    for (int i = 0; i < NS; ++i) {
+      io.p_all[base * NS + i] = p1[i];
+      if (io.sigma_all) io.sigma_all[base * NS + i] = sg[i];
+    }
+  } else if (io.sigma_all) {
+    const int64_t base = c * io.T_len + io.t_index;
+#pragma unroll
+    for (int i = 0; i < NS; ++i) io.sigma_all[base * NS + i] = sg[i];
+  }
+  if (io.q_all) {
+    const int64_t base = c * io.T_len + io.t_index;
+#pragma unroll
+    for (int i = 0; i < NS; ++i)
+#pragma unroll
+      for (int j = 0; j < NS; ++j) io.q_all[(base * NS + i) * NS + j] = q1[i][j];
+  }
+  if (io.traj) {
+    constexpr int S = NS + NS * NS;
+    T* dst = io.traj + (c * (io.T_len + 1) + io.t_index + 1) * S;
+#pragma unroll
+    for (int i = 0; i < NS; ++i) dst[i] = p1[i];
+#pragma unroll
+    for (int i = 0; i < NS; ++i)
+#pragma unroll
+      for (int j = 0; j < NS; ++j) dst[NS + i * NS + j] = q1[i][j];
+    if (io.first_step) {  // slot 0 = [p_0 | 0]  (PQFlattener.flatten(p, None), safempc_cem.py:40-54)
+      T* d0 = io.traj + c * (io.T_len + 1) * S;
+#pragma unroll
+      for (int i = 0; i < NS; ++i) d0[i] = p[i];
+#pragma unroll
+      for (int i = 0; i < NS * NS; ++i) d0[NS + i] = T(0);
+    }
+  }
+
+  // ---- CEM bookkeeping ----
+  if (io.objective) {
+    T cost;
+    if (pr.objective == SE_OBJ_NEG_VARIANCE) {
+      cost = T(0);
+#pragma unroll
+      for (int i = 0; i < NS; ++i) cost -= sg[i];  // -sum of variances incl. noise (quirk Q7)
+    } else if (pr.objective == SE_OBJ_ABS_STATE1) {
+      cost = Num<T>::abs_(pr.objective_theta - p1[NS > 1 ? 1 : 0]);
+    } else {
+      cost = -p1[NS - 1];
+    }
+    const T prev = io.first_step ? T(0) : io.objective[c];
+    io.objective[c] = prev + cost;
+  }
+  if (io.constraint) {
+    T cc = io.first_step ? T(0) : io.constraint[c];
+    if (pr.m_safe > 0 && (io.last_step || pr.all_states)) {
+      const bool inside = inside_polytope<T, NS>(p1, q1, pr, T(1), nullptr);
+      if (!inside) cc += pr.state_penalty;  // 10 * (1 - inside), safempc_cem.py:132
+    }
+    if (io.last_step && pr.m_act > 0) {
+      // ActionConstraint: penalty * #{t : some face has A u_t - b > 0}  (constrained_cem_mpc.py:29-41, 100-110)
+      int bad = 0;
+      for (int t = 0; t < io.T_len; ++t) {
+        bool out = false;
+        for (int f = 0; f < pr.m_act; ++f) {
+          T s = -pr.act_b[f];
+#pragma unroll
+          for (int k = 0; k < NU; ++k) s += pr.act_a[f][k] * io.act_all[(c * io.T_len + t) * NU + k];
+          if (s > T(0)) out = true;
+        }
+        bad += out ? 1 : 0;
+      }
+      cc += pr.act_penalty * T(bad);
+    }
+    io.constraint[c] = cc;
+  }
+}
+
+// stand-alone polytope distance (se_safety_distance)
+template <typename T, int NS>
+__global__ void safety_distance_kernel(ProbDev<T> pr, const T* __restrict__ p, const T* __restrict__ q, int64_t N,
+                                       T* __restrict__ d, uint8_t* __restrict__ inside) {
+  const int64_t c = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (c >= N) return;
+  T pp[NS], qq[NS][NS];
+#pragma unroll
+  for (int i = 0; i < NS; ++i) {
+    pp[i] = p[c * NS + i];
+#pragma unroll
+    for (int j = 0; j < NS; ++j) qq[i][j] = q[(c * NS + i) * NS + j];
+  }
+  T dd[SE_MAX_FACES];
+  const bool in = inside_polytope<T, NS>(pp, qq, pr, pr.c_safety, dd);
+  if (d)
+    for (int f = 0; f < pr.m_safe; ++f) d[c * pr.m_safe + f] = dd[f];
+  if (inside) inside[c] = in ? 1 : 0;
+}
+
+}  // namespace se

@@ -1,0 +1,751 @@
+// secem.cu -- C ABI of libsecem.so (include/secem.h): handle management and kernel orchestration.
+#include <dlfcn.h>
+
+#include <cmath>
+#include <vector>
+
+#include "cem_kernels.cuh"
+#include "gp_kernels.cuh"
+#include "launchers.cuh"
+#include "reach_kernels.cuh"
+
+namespace se {
+thread_local char g_last_error[1024] = "";
+std::atomic<uint64_t> g_launches{0};
+}  // namespace se
+
+using namespace se;
+
+// -------------------------------------------------------------------------------------------------------------------
+// handles
+// -------------------------------------------------------------------------------------------------------------------
+struct se_gp_s {
+  se_dtype dtype = SE_F64;
+  int ns = 0, nu = 0, d = 0, n = 0, n_pad = 0;
+  size_t esz = 8;
+  void* xt = nullptr;
+  void* alpha = nullptr;
+  void* w = nullptr;
+  double inv_l2[SE_MAX_NS][SE_MAX_D];
+  double outputscale[SE_MAX_NS];
+  double noise[SE_MAX_NS];
+  // workspace: materialised kernel rows K*[ns][rows_chunk][n_pad] + partial sums + posterior buffers
+  uint64_t ws_limit = 6ull << 30;
+  void* kst = nullptr;
+  size_t kst_bytes = 0;
+  void* partial = nullptr;
+  size_t partial_bytes = 0;
+  void* post_mean = nullptr;  // [cap, ns]
+  void* post_var = nullptr;
+  void* post_jac = nullptr;  // [cap, ns, d]
+  int64_t post_cap = 0;
+  int* counter = nullptr;
+  se_gemm_impl impl = SE_GEMM_AUTO;
+  int sm_count = 148;
+  // timing
+  bool timing = false;
+  std::vector<cudaEvent_t> ev_gemm, ev_kstar;  // (start, stop) pairs
+};
+
+template <typename T>
+static GpDev<T> gp_dev(const se_gp_s* g) {
+  GpDev<T> v;
+  v.n = g->n, v.n_pad = g->n_pad, v.ns = g->ns, v.nu = g->nu, v.d = g->d;
+  v.xt = static_cast<const T*>(g->xt);
+  v.alpha = static_cast<const T*>(g->alpha);
+  v.w = static_cast<const T*>(g->w);
+  for (int o = 0; o < SE_MAX_NS; ++o) {
+    for (int dd = 0; dd < SE_MAX_D; ++dd) v.inv_l2[o][dd] = (T)g->inv_l2[o][dd];
+    v.outputscale[o] = (T)g->outputscale[o];
+    v.noise[o] = (T)g->noise[o];
+  }
+  return v;
+}
+
+static int grow(void** ptr, size_t* have, size_t want) {
+  if (*have >= want) return 0;
+  if (*ptr) SE_CUDA(cudaFree(*ptr));
+  *ptr = nullptr;
+  *have = 0;
+  SE_CUDA(cudaMalloc(ptr, want));
+  *have = want;
+  return 0;
+}
+
+extern "C" const char* se_last_error(void) { return g_last_error; }
+extern "C" int se_version(void) { return 100; }
+extern "C" uint64_t se_launch_count(void) { return g_launches.load(); }
+extern "C" void se_launch_count_reset(void) { g_launches.store(0); }
+extern "C" int se_measure_peak(int kind, double* flops_out) {
+  SE_REQUIRE(kind >= 0 && kind <= 2 && flops_out, "se_measure_peak: bad arguments");
+  return measure_peak(kind, flops_out);
+}
+
+extern "C" int se_gp_create(se_gp_t* out, int n_s, int n_u, int n, se_dtype dtype, const void* dev_x,
+                            const void* dev_alpha, const void* dev_linv, const double* host_lengthscale,
+                            const double* host_outputscale, const double* host_noise, void* stream) {
+  SE_REQUIRE(out, "se_gp_create: out is NULL");
+  SE_REQUIRE(n_s >= 1 && n_s <= SE_MAX_NS, "se_gp_create: n_s = %d outside [1, %d]", n_s, SE_MAX_NS);
+  SE_REQUIRE(n_u >= 1 && n_u <= SE_MAX_NU, "se_gp_create: n_u = %d outside [1, %d]", n_u, SE_MAX_NU);
+  SE_REQUIRE(n >= 1, "se_gp_create: empty training set");
+  SE_REQUIRE(dtype == SE_F32 || dtype == SE_F64, "se_gp_create: bad dtype");
+  SE_REQUIRE(dev_x && dev_alpha && dev_linv && host_lengthscale && host_outputscale && host_noise,
+             "se_gp_create: NULL argument");
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  se_gp_s* g = new se_gp_s();
+  g->dtype = dtype;
+  g->esz = dtype == SE_F64 ? 8 : 4;
+  g->ns = n_s, g->nu = n_u, g->d = n_s + n_u, g->n = n;
+  g->n_pad = (int)round_up(n, kTile);
+  memset(g->inv_l2, 0, sizeof(g->inv_l2));
+  memset(g->outputscale, 0, sizeof(g->outputscale));
+  memset(g->noise, 0, sizeof(g->noise));
+  for (int o = 0; o < n_s; ++o) {
+    for (int dd = 0; dd < g->d; ++dd) {
+      const double l = host_lengthscale[o * g->d + dd];
+      if (!(l > 0.0)) {
+        delete g;
+        return fail("se_gp_create: lengthscale[%d][%d] = %g must be > 0", o, dd, l);
+      }
+      g->inv_l2[o][dd] = 1.0 / (l * l);
+    }
+    g->outputscale[o] = host_outputscale[o];
+    g->noise[o] = host_noise[o];
+  }
+  int dev = 0;
+  cudaGetDevice(&dev);
+  cudaDeviceGetAttribute(&g->sm_count, cudaDevAttrMultiProcessorCount, dev);
+  auto cleanup_fail = [&]() {
+    se_gp_destroy(g);
+    return -1;
+  };
+  const size_t np = (size_t)g->n_pad;
+  if (cudaMalloc(&g->xt, g->d * np * g->esz) != cudaSuccess || cudaMalloc(&g->alpha, n_s * np * g->esz) != cudaSuccess ||
+      cudaMalloc(&g->w, (size_t)n_s * np * np * g->esz) != cudaSuccess ||
+      cudaMalloc(&g->counter, 64 * sizeof(int)) != cudaSuccess) {
+    fail("se_gp_create: cudaMalloc failed (n_pad = %d): %s", g->n_pad, cudaGetErrorString(cudaGetLastError()));
+    return cleanup_fail();
+  }
+  int rc;
+  if (dtype == SE_F64)
+    rc = launch_pack_model<double>((const double*)dev_x, (const double*)dev_alpha, (const double*)dev_linv, n, g->d,
+                                   n_s, g->n_pad, (double*)g->xt, (double*)g->alpha, (double*)g->w, st);
+  else
+    rc = launch_pack_model<float>((const float*)dev_x, (const float*)dev_alpha, (const float*)dev_linv, n, g->d, n_s,
+                                  g->n_pad, (float*)g->xt, (float*)g->alpha, (float*)g->w, st);
+  if (rc != 0) return cleanup_fail();
+  *out = g;
+  return 0;
+}
+
+extern "C" int se_gp_destroy(se_gp_t g) {
+  if (!g) return 0;
+  for (void* p : {g->xt, g->alpha, g->w, g->kst, g->partial, g->post_mean, g->post_var, g->post_jac, (void*)g->counter})
+    if (p) cudaFree(p);
+  for (auto e : g->ev_gemm) cudaEventDestroy(e);
+  for (auto e : g->ev_kstar) cudaEventDestroy(e);
+  delete g;
+  return 0;
+}
+
+extern "C" int se_gp_set_workspace_limit(se_gp_t g, uint64_t bytes) {
+  SE_REQUIRE(g, "NULL handle");
+  g->ws_limit = bytes;
+  return 0;
+}
+extern "C" int se_gp_set_gemm_impl(se_gp_t g, se_gemm_impl impl) {
+  SE_REQUIRE(g, "NULL handle");
+  g->impl = impl;
+  return 0;
+}
+extern "C" int se_gp_timing_enable(se_gp_t g, int enable) {
+  SE_REQUIRE(g, "NULL handle");
+  g->timing = enable != 0;
+  for (auto e : g->ev_gemm) cudaEventDestroy(e);
+  for (auto e : g->ev_kstar) cudaEventDestroy(e);
+  g->ev_gemm.clear();
+  g->ev_kstar.clear();
+  return 0;
+}
+extern "C" int se_gp_timing_read(se_gp_t g, double* gemm_ms, int64_t* gemm_launches, double* kstar_ms,
+                                 int64_t* kstar_launches, void* stream) {
+  SE_REQUIRE(g, "NULL handle");
+  SE_CUDA(cudaStreamSynchronize(static_cast<cudaStream_t>(stream)));
+  auto total = [](std::vector<cudaEvent_t>& ev, double* ms, int64_t* cnt) {
+    double s = 0;
+    for (size_t i = 0; i + 1 < ev.size(); i += 2) {
+      float t = 0.f;
+      cudaEventElapsedTime(&t, ev[i], ev[i + 1]);
+      s += t;
+    }
+    if (ms) *ms = s;
+    if (cnt) *cnt = (int64_t)ev.size() / 2;
+    for (auto e : ev) cudaEventDestroy(e);
+    ev.clear();
+  };
+  total(g->ev_gemm, gemm_ms, gemm_launches);
+  total(g->ev_kstar, kstar_ms, kstar_launches);
+  return 0;
+}
+
+// rows of K* per chunk so that ns * rows * n_pad * esz <= ws_limit (multiple of the row tile)
+static int64_t chunk_rows(const se_gp_s* g, int64_t N) {
+  const int64_t n_rows_pad = round_up(N, kTile);
+  int64_t by_limit = (int64_t)(g->ws_limit / ((uint64_t)g->ns * g->n_pad * g->esz));
+  by_limit = by_limit / kTile * kTile;
+  if (by_limit < kTile) by_limit = kTile;
+  return n_rows_pad < by_limit ? n_rows_pad : by_limit;
+}
+
+// Ensure workspace for a batch of N candidates.  Allocates (cudaMalloc) only when the batch grows, so a caller that
+// wants to capture a CUDA graph warms the handle up with one eager call first.
+static int gp_reserve(se_gp_s* g, int64_t N) {
+  const int64_t rows = chunk_rows(g, N);
+  SE_TRY(grow(&g->kst, &g->kst_bytes, (size_t)g->ns * rows * g->n_pad * g->esz));
+  SE_TRY(grow(&g->partial, &g->partial_bytes, (size_t)g->ns * (g->n_pad / 64) * rows * g->esz));
+  return 0;
+}
+static int gp_reserve_posterior(se_gp_s* g, int64_t N) {
+  if (g->post_cap >= N) return 0;
+  for (void** p : {&g->post_mean, &g->post_var, &g->post_jac})
+    if (*p) {
+      cudaFree(*p);
+      *p = nullptr;
+    }
+  g->post_cap = 0;
+  SE_CUDA(cudaMalloc(&g->post_mean, (size_t)N * g->ns * g->esz));
+  SE_CUDA(cudaMalloc(&g->post_var, (size_t)N * g->ns * g->esz));
+  SE_CUDA(cudaMalloc(&g->post_jac, (size_t)N * g->ns * g->d * g->esz));
+  g->post_cap = N;
+  return 0;
+}
+
+static int record_event(std::vector<cudaEvent_t>& ev, cudaStream_t st) {
+  cudaEvent_t e;
+  SE_CUDA(cudaEventCreate(&e));
+  SE_CUDA(cudaEventRecord(e, st));
+  ev.push_back(e);
+  return 0;
+}
+
+// GP posterior for N candidates whose inputs are z_c = [p[c*p_stride : +ns] | u[c*u_stride : +nu]]
+template <typename T>
+static int gp_posterior(se_gp_s* g, const T* p, int64_t p_stride, const T* u, int64_t u_stride, int64_t N, T* mean,
+                        T* var, T* jac, cudaStream_t st) {
+  if (N <= 0) return 0;
+  SE_TRY(gp_reserve(g, N));
+  const GpDev<T> gd = gp_dev<T>(g);
+  const int64_t rows_chunk = chunk_rows(g, N);
+  for (int64_t row0 = 0; row0 < N; row0 += rows_chunk) {
+    const int nrows = (int)((N - row0) < rows_chunk ? (N - row0) : rows_chunk);
+    const int rows_pad = (int)round_up(nrows, kTile);
+    if (g->timing) SE_TRY(record_event(g->ev_kstar, st));
+    SE_TRY(launch_kstar<T>(gd, p, p_stride, u, u_stride, row0, nrows, rows_pad, (T*)g->kst, mean, jac, st));
+    if (g->timing) SE_TRY(record_event(g->ev_kstar, st));
+    int nb = 0;
+    if (g->timing) SE_TRY(record_event(g->ev_gemm, st));
+    SE_TRY(launch_trisumsq<T>(g->impl, (const T*)g->kst, gd.w, g->n_pad, rows_pad, g->ns, (T*)g->partial, g->counter,
+                              g->sm_count, &nb, st));
+    if (g->timing) SE_TRY(record_event(g->ev_gemm, st));
+    SE_TRY(launch_var<T>(gd, (const T*)g->partial, nb, rows_pad, row0, nrows, var, st));
+  }
+  return 0;
+}
+
+extern "C" int se_gp_predict(se_gp_t g, const void* dev_z, int64_t N, void* dev_mean, void* dev_var, void* dev_jac,
+                             void* stream) {
+  SE_REQUIRE(g && dev_z && dev_mean && dev_var, "se_gp_predict: NULL argument");
+  SE_REQUIRE(N >= 0, "se_gp_predict: N < 0");
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (g->dtype == SE_F64) {
+    const double* z = (const double*)dev_z;
+    return gp_posterior<double>(g, z, g->d, z + g->ns, g->d, N, (double*)dev_mean, (double*)dev_var,
+                                (double*)dev_jac, st);
+  }
+  const float* z = (const float*)dev_z;
+  return gp_posterior<float>(g, z, g->d, z + g->ns, g->d, N, (float*)dev_mean, (float*)dev_var, (float*)dev_jac, st);
+}
+
+// -------------------------------------------------------------------------------------------------------------------
+// problem constants
+// -------------------------------------------------------------------------------------------------------------------
+template <typename T>
+static int make_prob(const se_problem* pr, const double* k_fb_override, ProbDev<T>* out) {
+  SE_REQUIRE(pr, "se_problem is NULL");
+  const int ns = pr->n_s, nu = pr->n_u;
+  SE_REQUIRE(ns >= 1 && ns <= SE_MAX_NS && nu >= 1 && nu <= SE_MAX_NU, "se_problem: bad (n_s, n_u) = (%d, %d)", ns, nu);
+  SE_REQUIRE(pr->m_safe >= 0 && pr->m_safe <= SE_MAX_FACES, "se_problem: m_safe = %d outside [0, %d]", pr->m_safe,
+             SE_MAX_FACES);
+  SE_REQUIRE(pr->m_act >= 0 && pr->m_act <= SE_MAX_ACT_FACES, "se_problem: m_act = %d outside [0, %d]", pr->m_act,
+             SE_MAX_ACT_FACES);
+  SE_REQUIRE(pr->l_mu && pr->l_sigma, "se_problem: l_mu / l_sigma is NULL");
+  SE_REQUIRE(pr->m_safe == 0 || (pr->h_mat && pr->h_vec), "se_problem: h_mat / h_vec is NULL");
+  SE_REQUIRE(pr->m_act == 0 || (pr->act_a && pr->act_b), "se_problem: act_a / act_b is NULL");
+  ProbDev<T>& o = *out;
+  memset(&o, 0, sizeof(o));
+  o.ns = ns, o.nu = nu, o.m_safe = pr->m_safe, o.m_act = pr->m_act;
+  o.objective = pr->objective, o.all_states = pr->all_states_constraint;
+  const double* kf = k_fb_override ? k_fb_override : pr->k_fb;
+  double kfb[SE_MAX_NU][SE_MAX_NS] = {};
+  for (int k = 0; k < nu; ++k)
+    for (int j = 0; j < ns; ++j) {
+      kfb[k][j] = kf ? kf[k * ns + j] : 0.0;
+      o.k_fb[k][j] = (T)kfb[k][j];
+    }
+  for (int i = 0; i < ns; ++i) {
+    for (int j = 0; j < ns; ++j) o.a[i][j] = (T)(pr->a ? pr->a[i * ns + j] : (i == j ? 1.0 : 0.0));  // :60-62
+    for (int k = 0; k < nu; ++k) o.b[i][k] = (T)(pr->b ? pr->b[i * nu + k] : 0.0);
+    o.l_mu[i] = (T)pr->l_mu[i];
+    o.l_sigma[i] = (T)pr->l_sigma[i];
+  }
+  // B = S S^T = I + k_fb^T k_fb (utils.py:175-177) and its lower Cholesky factor
+  double bm[SE_MAX_NS][SE_MAX_NS] = {}, ch[SE_MAX_NS][SE_MAX_NS] = {};
+  for (int i = 0; i < ns; ++i)
+    for (int j = 0; j < ns; ++j) {
+      double s = i == j ? 1.0 : 0.0;
+      for (int k = 0; k < nu; ++k) s += kfb[k][i] * kfb[k][j];
+      bm[i][j] = s;
+    }
+  for (int j = 0; j < ns; ++j) {
+    double dsum = bm[j][j];
+    for (int k = 0; k < j; ++k) dsum -= ch[j][k] * ch[j][k];
+    ch[j][j] = std::sqrt(dsum);
+    for (int i = j + 1; i < ns; ++i) {
+      double s = bm[i][j];
+      for (int k = 0; k < j; ++k) s -= ch[i][k] * ch[j][k];
+      ch[i][j] = s / ch[j][j];
+    }
+  }
+  for (int i = 0; i < ns; ++i)
+    for (int j = 0; j < ns; ++j) {
+      o.bmat[i][j] = (T)bm[i][j];
+      o.bchol[i][j] = (T)ch[i][j];
+    }
+  o.c_safety = (T)pr->c_safety;
+  for (int f = 0; f < pr->m_safe; ++f) {
+    for (int j = 0; j < ns; ++j) o.h_mat[f][j] = (T)pr->h_mat[f * ns + j];
+    o.h_vec[f] = (T)pr->h_vec[f];
+  }
+  for (int f = 0; f < pr->m_act; ++f) {
+    for (int k = 0; k < nu; ++k) o.act_a[f][k] = (T)pr->act_a[f * nu + k];
+    o.act_b[f] = (T)pr->act_b[f];
+  }
+  o.act_penalty = (T)pr->act_penalty;
+  o.state_penalty = (T)pr->state_penalty;
+  o.objective_theta = (T)pr->objective_theta;
+  return 0;
+}
+
+// -------------------------------------------------------------------------------------------------------------------
+// reachability
+// -------------------------------------------------------------------------------------------------------------------
+template <typename T>
+static int reach_onestep_t(se_gp_s* g, const se_problem* prob, const T* p, const T* q, const T* u, int64_t N, T* p1,
+                           T* q1, T* sigma, int32_t* flags, cudaStream_t st) {
+  ProbDev<T> pr;
+  SE_TRY(make_prob<T>(prob, nullptr, &pr));
+  SE_REQUIRE(pr.ns == g->ns && pr.nu == g->nu, "se_reach_onestep: problem / GP dimension mismatch");
+  SE_REQUIRE(q == nullptr || prob->k_fb != nullptr, "se_reach_onestep: k_fb is required for ellipsoid states");
+  SE_TRY(gp_reserve_posterior(g, N));
+  T* mean = (T*)g->post_mean;
+  T* var = (T*)g->post_var;
+  T* jac = q ? (T*)g->post_jac : nullptr;
+  SE_TRY(gp_posterior<T>(g, p, g->ns, u, g->nu, N, mean, var, jac, st));
+  StepIO<T> io;
+  memset(&io, 0, sizeof(io));
+  io.p_in = p, io.q_in = q, io.p_out = p1, io.q_out = q1;
+  io.u = u, io.u_stride = g->nu;
+  io.mean = mean, io.var = var, io.jac = jac;
+  io.sigma_out = sigma;
+  io.point = q ? 0 : 1;
+  io.first_step = 1, io.last_step = 1, io.T_len = 1;
+  io.flags = flags;
+  return launch_reach_step<T>(pr, io, N, st);
+}
+
+extern "C" int se_reach_onestep(se_gp_t g, const se_problem* prob, const void* dev_p, const void* dev_q,
+                                const void* dev_u, int64_t N, void* dev_p1, void* dev_q1, void* dev_sigma,
+                                int32_t* dev_flags, void* stream) {
+  SE_REQUIRE(g && prob && dev_p && dev_u && dev_p1 && dev_q1, "se_reach_onestep: NULL argument");
+  SE_REQUIRE(N >= 0, "se_reach_onestep: N < 0");
+  if (N == 0) return 0;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (g->dtype == SE_F64)
+    return reach_onestep_t<double>(g, prob, (const double*)dev_p, (const double*)dev_q, (const double*)dev_u, N,
+                                   (double*)dev_p1, (double*)dev_q1, (double*)dev_sigma, dev_flags, st);
+  return reach_onestep_t<float>(g, prob, (const float*)dev_p, (const float*)dev_q, (const float*)dev_u, N,
+                                (float*)dev_p1, (float*)dev_q1, (float*)dev_sigma, dev_flags, st);
+}
+
+template <typename T>
+static int reach_multistep_t(se_gp_s* g, const se_problem* prob, const T* p0, const T* q0, const T* u, int64_t N,
+                             int T_len, const double* k_fb_steps, T* p_all, T* q_all, T* sigma_all, T* pT, T* qT,
+                             int32_t* flags, cudaStream_t st) {
+  SE_REQUIRE(T_len >= 1 && T_len <= SE_MAX_T, "se_reach_multistep: T = %d outside [1, %d]", T_len, SE_MAX_T);
+  SE_REQUIRE(prob->k_fb || k_fb_steps || (T_len == 1 && !q0), "se_reach_multistep: k_fb is required");
+  SE_TRY(gp_reserve_posterior(g, N));
+  T* mean = (T*)g->post_mean;
+  T* var = (T*)g->post_var;
+  for (int t = 0; t < T_len; ++t) {
+    ProbDev<T> pr;
+    // step 0 uses prob->k_fb (k_fb_init of gp_reachability.py:204-205); step i >= 1 uses k_fb[i-1] (:213-216)
+    const double* kf = (k_fb_steps && t >= 1) ? k_fb_steps + (size_t)(t - 1) * g->nu * g->ns : nullptr;
+    SE_TRY(make_prob<T>(prob, kf, &pr));
+    SE_REQUIRE(pr.ns == g->ns && pr.nu == g->nu, "se_reach_multistep: problem / GP dimension mismatch");
+    const bool point = (t == 0 && q0 == nullptr);
+    const T* p_in = t == 0 ? p0 : pT;
+    const T* q_in = t == 0 ? q0 : qT;
+    T* jac = point ? nullptr : (T*)g->post_jac;
+    SE_TRY(gp_posterior<T>(g, p_in, g->ns, u + (int64_t)t * g->nu, (int64_t)T_len * g->nu, N, mean, var, jac, st));
+    StepIO<T> io;
+    memset(&io, 0, sizeof(io));
+    io.p_in = p_in, io.q_in = q_in, io.p_out = pT, io.q_out = qT;
+    io.u = u + (int64_t)t * g->nu, io.u_stride = (int64_t)T_len * g->nu;
+    io.mean = mean, io.var = var, io.jac = jac;
+    io.point = point ? 1 : 0;
+    io.first_step = t == 0, io.last_step = t == T_len - 1, io.T_len = T_len, io.t_index = t;
+    io.p_all = p_all, io.q_all = q_all, io.sigma_all = sigma_all;
+    io.flags = flags;
+    SE_TRY(launch_reach_step<T>(pr, io, N, st));
+  }
+  return 0;
+}
+
+extern "C" int se_reach_multistep(se_gp_t g, const se_problem* prob, const void* dev_p0, const void* dev_q0,
+                                  const void* dev_u, int64_t N, int T, const double* host_k_fb_steps, void* dev_p_all,
+                                  void* dev_q_all, void* dev_sigma_all, void* dev_pT, void* dev_qT, int32_t* dev_flags,
+                                  void* stream) {
+  SE_REQUIRE(g && prob && dev_p0 && dev_u && dev_pT && dev_qT, "se_reach_multistep: NULL argument");
+  SE_REQUIRE(N >= 0, "se_reach_multistep: N < 0");
+  if (N == 0) return 0;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (g->dtype == SE_F64)
+    return reach_multistep_t<double>(g, prob, (const double*)dev_p0, (const double*)dev_q0, (const double*)dev_u, N,
+                                     T, host_k_fb_steps, (double*)dev_p_all, (double*)dev_q_all,
+                                     (double*)dev_sigma_all, (double*)dev_pT, (double*)dev_qT, dev_flags, st);
+  return reach_multistep_t<float>(g, prob, (const float*)dev_p0, (const float*)dev_q0, (const float*)dev_u, N, T,
+                                  host_k_fb_steps, (float*)dev_p_all, (float*)dev_q_all, (float*)dev_sigma_all,
+                                  (float*)dev_pT, (float*)dev_qT, dev_flags, st);
+}
+
+extern "C" int se_safety_distance(se_dtype dtype, int n_s, int m, const double* host_h_mat, const double* host_h_vec,
+                                  double c_safety, const void* dev_p, const void* dev_q, int64_t N, void* dev_d,
+                                  uint8_t* dev_inside, void* stream) {
+  SE_REQUIRE(host_h_mat && host_h_vec && dev_p && dev_q, "se_safety_distance: NULL argument");
+  SE_REQUIRE(N >= 0, "se_safety_distance: N < 0");
+  if (N == 0) return 0;
+  se_problem pr;
+  memset(&pr, 0, sizeof(pr));
+  const double zeros[SE_MAX_NS] = {};
+  pr.n_s = n_s, pr.n_u = 1, pr.l_mu = zeros, pr.l_sigma = zeros;
+  pr.c_safety = c_safety, pr.m_safe = m, pr.h_mat = host_h_mat, pr.h_vec = host_h_vec;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (dtype == SE_F64) {
+    ProbDev<double> pd;
+    SE_TRY(make_prob<double>(&pr, nullptr, &pd));
+    return launch_safety_distance<double>(pd, (const double*)dev_p, (const double*)dev_q, N, (double*)dev_d,
+                                          dev_inside, st);
+  }
+  ProbDev<float> pf;
+  SE_TRY(make_prob<float>(&pr, nullptr, &pf));
+  return launch_safety_distance<float>(pf, (const float*)dev_p, (const float*)dev_q, N, (float*)dev_d, dev_inside, st);
+}
+
+// -------------------------------------------------------------------------------------------------------------------
+// NCCL, resolved at run time from the already-loaded libnccl.so.2 (torch ships it); single-GPU use needs no NCCL
+// -------------------------------------------------------------------------------------------------------------------
+namespace {
+struct NcclId {
+  char bytes[128];
+};
+struct NcclApi {
+  int (*GetUniqueId)(NcclId*) = nullptr;
+  int (*CommInitRank)(void**, int, NcclId, int) = nullptr;
+  int (*CommDestroy)(void*) = nullptr;
+  int (*AllGather)(const void*, void*, size_t, int, void*, cudaStream_t) = nullptr;
+  const char* (*GetErrorString)(int) = nullptr;
+  bool ok = false;
+};
+NcclApi g_nccl;
+
+int nccl_load() {
+  if (g_nccl.ok) return 0;
+  void* h = dlopen("libnccl.so.2", RTLD_NOW | RTLD_GLOBAL);
+  if (!h) h = dlopen("libnccl.so", RTLD_NOW | RTLD_GLOBAL);
+  SE_REQUIRE(h, "NCCL not found: %s", dlerror());
+  g_nccl.GetUniqueId = reinterpret_cast<decltype(g_nccl.GetUniqueId)>(dlsym(h, "ncclGetUniqueId"));
+  g_nccl.CommInitRank = reinterpret_cast<decltype(g_nccl.CommInitRank)>(dlsym(h, "ncclCommInitRank"));
+  g_nccl.CommDestroy = reinterpret_cast<decltype(g_nccl.CommDestroy)>(dlsym(h, "ncclCommDestroy"));
+  g_nccl.AllGather = reinterpret_cast<decltype(g_nccl.AllGather)>(dlsym(h, "ncclAllGather"));
+  g_nccl.GetErrorString = reinterpret_cast<decltype(g_nccl.GetErrorString)>(dlsym(h, "ncclGetErrorString"));
+  SE_REQUIRE(g_nccl.GetUniqueId && g_nccl.CommInitRank && g_nccl.CommDestroy && g_nccl.AllGather,
+             "NCCL symbols missing");
+  g_nccl.ok = true;
+  return 0;
+}
+}  // namespace
+
+extern "C" int se_nccl_unique_id(char* out128) {
+  SE_TRY(nccl_load());
+  NcclId id;
+  const int r = g_nccl.GetUniqueId(&id);
+  SE_REQUIRE(r == 0, "ncclGetUniqueId failed: %d", r);
+  memcpy(out128, id.bytes, 128);
+  return 0;
+}
+extern "C" int se_nccl_comm_init(void** comm, int world_size, const char* id128, int rank) {
+  SE_TRY(nccl_load());
+  NcclId id;
+  memcpy(id.bytes, id128, 128);
+  const int r = g_nccl.CommInitRank(comm, world_size, id, rank);
+  SE_REQUIRE(r == 0, "ncclCommInitRank failed: %s", g_nccl.GetErrorString ? g_nccl.GetErrorString(r) : "?");
+  return 0;
+}
+extern "C" int se_nccl_comm_destroy(void* comm) {
+  if (!comm) return 0;
+  SE_TRY(nccl_load());
+  g_nccl.CommDestroy(comm);
+  return 0;
+}
+
+// -------------------------------------------------------------------------------------------------------------------
+// CEM
+// -------------------------------------------------------------------------------------------------------------------
+struct se_cem_s {
+  se_gp_s* gp = nullptr;
+  se_cem_config cfg{};
+  ProbDev<float> pf;
+  ProbDev<double> pd;
+  void* comm = nullptr;
+  int rank = 0, world = 1;
+  // device buffers
+  void *actions = nullptr, *p = nullptr, *q = nullptr, *objective = nullptr, *constraint = nullptr;
+  void *pack_local = nullptr, *pack_all = nullptr;
+  double *mean = nullptr, *stdv = nullptr;  // [I + 1][M][T * nu]
+  void* act_out = nullptr;                   // scratch outputs when the caller passes NULL
+  int32_t *found = nullptr, *best = nullptr;
+};
+
+extern "C" int se_cem_destroy(se_cem_t c) {
+  if (!c) return 0;
+  for (void* p : {c->actions, c->p, c->q, c->objective, c->constraint, c->pack_local, c->pack_all, (void*)c->mean,
+                  (void*)c->stdv, c->act_out, (void*)c->found, (void*)c->best})
+    if (p) cudaFree(p);
+  delete c;
+  return 0;
+}
+
+extern "C" int se_cem_create(se_cem_t* out, se_gp_t gp, const se_problem* prob, const se_cem_config* cfg) {
+  SE_REQUIRE(out && gp && prob && cfg, "se_cem_create: NULL argument");
+  SE_REQUIRE(cfg->num_instances >= 1, "se_cem_create: num_instances < 1");
+  SE_REQUIRE(cfg->time_horizon >= 1 && cfg->time_horizon <= SE_MAX_T, "se_cem_create: time_horizon = %d outside [1, %d]",
+             cfg->time_horizon, SE_MAX_T);
+  SE_REQUIRE(cfg->num_iterations >= 1, "se_cem_create: num_iterations < 1");
+  SE_REQUIRE(cfg->num_elites >= 1 && cfg->num_elites <= kMaxElites && cfg->num_elites <= cfg->num_rollouts,
+             "se_cem_create: num_elites = %d must be in [1, min(%d, num_rollouts = %d)]", cfg->num_elites, kMaxElites,
+             cfg->num_rollouts);
+  SE_REQUIRE(cfg->local_rollouts >= 1 && cfg->first_rollout >= 0 &&
+                 cfg->first_rollout + cfg->local_rollouts <= cfg->num_rollouts,
+             "se_cem_create: bad shard [%d, +%d) of %d", cfg->first_rollout, cfg->local_rollouts, cfg->num_rollouts);
+  SE_REQUIRE((int64_t)cfg->num_instances * cfg->num_rollouts < (1ll << 31), "se_cem_create: population too large");
+  SE_REQUIRE(prob->n_s == gp->ns && prob->n_u == gp->nu, "se_cem_create: problem / GP dimension mismatch");
+  SE_REQUIRE(prob->k_fb && prob->a && prob->b, "se_cem_create: k_fb, a, b are required");
+  se_cem_s* c = new se_cem_s();
+  c->gp = gp;
+  c->cfg = *cfg;
+  if (make_prob<float>(prob, nullptr, &c->pf) != 0 || make_prob<double>(prob, nullptr, &c->pd) != 0) {
+    delete c;
+    return -1;
+  }
+  const size_t esz = gp->esz;
+  const size_t M = cfg->num_instances, Nl = cfg->local_rollouts, T = cfg->time_horizon, ns = gp->ns, nu = gp->nu;
+  const size_t cand = M * Nl, tnu = T * nu;
+  bool ok = true;
+  auto alloc = [&](void** p, size_t bytes) { ok = ok && cudaMalloc(p, bytes) == cudaSuccess; };
+  alloc(&c->actions, cand * tnu * esz);
+  alloc(&c->p, cand * ns * esz);
+  alloc(&c->q, cand * ns * ns * esz);
+  alloc(&c->objective, cand * esz);
+  alloc(&c->constraint, cand * esz);
+  alloc(&c->pack_local, 2 * cand * esz);
+  alloc((void**)&c->mean, (cfg->num_iterations + 1) * M * tnu * sizeof(double));
+  alloc((void**)&c->stdv, (cfg->num_iterations + 1) * M * tnu * sizeof(double));
+  alloc(&c->act_out, M * tnu * esz);
+  alloc((void**)&c->found, M * sizeof(int32_t));
+  alloc((void**)&c->best, M * sizeof(int32_t));
+  if (!ok) {
+    fail("se_cem_create: cudaMalloc failed: %s", cudaGetErrorString(cudaGetLastError()));
+    se_cem_destroy(c);
+    return -1;
+  }
+  if (gp_reserve(gp, (int64_t)cand) != 0 || gp_reserve_posterior(gp, (int64_t)cand) != 0) {
+    se_cem_destroy(c);
+    return -1;
+  }
+  *out = c;
+  return 0;
+}
+
+extern "C" int se_cem_set_comm(se_cem_t c, void* nccl_comm, int rank, int world_size) {
+  SE_REQUIRE(c, "NULL handle");
+  SE_REQUIRE(world_size >= 1 && rank >= 0 && rank < world_size, "se_cem_set_comm: bad rank %d / %d", rank, world_size);
+  if (world_size > 1) {
+    SE_REQUIRE(nccl_comm, "se_cem_set_comm: NULL communicator");
+    SE_REQUIRE(c->cfg.local_rollouts * world_size == c->cfg.num_rollouts &&
+                   c->cfg.first_rollout == rank * c->cfg.local_rollouts,
+               "se_cem_set_comm: population must be split evenly: rank r owns [r N/W, (r+1) N/W)");
+    SE_TRY(nccl_load());
+    if (c->pack_all) cudaFree(c->pack_all);
+    const size_t cand = (size_t)c->cfg.num_instances * c->cfg.local_rollouts;
+    SE_CUDA(cudaMalloc(&c->pack_all, (size_t)world_size * 2 * cand * c->gp->esz));
+  }
+  c->comm = nccl_comm, c->rank = rank, c->world = world_size;
+  return 0;
+}
+
+template <typename T>
+static int cem_solve_t(se_cem_s* c, const ProbDev<T>& pr, const T* p0, const T* noise, uint64_t seed,
+                       const se_cem_outputs* out, cudaStream_t st) {
+  se_gp_s* g = c->gp;
+  const se_cem_config& cf = c->cfg;
+  const int M = cf.num_instances, Nl = cf.local_rollouts, Ng = cf.num_rollouts, T_len = cf.time_horizon;
+  const int ns = g->ns, nu = g->nu, tnu = T_len * nu, S = ns + ns * ns;
+  const int64_t cand = (int64_t)M * Nl;
+  SE_REQUIRE(c->world == 1 ? (Nl == Ng && cf.first_rollout == 0) : true,
+             "se_cem_solve: a sharded population needs se_cem_set_comm");
+  T* actions = (T*)c->actions;
+  T* p = (T*)c->p;
+  T* q = (T*)c->q;
+  T* objective = (T*)c->objective;
+  T* constraint = (T*)c->constraint;
+  T* pack_local = (T*)c->pack_local;
+  T* pack_all = c->world > 1 ? (T*)c->pack_all : pack_local;
+  T* mean = (T*)g->post_mean;
+  T* var = (T*)g->post_var;
+  T* jac = (T*)g->post_jac;
+  const size_t dist = (size_t)M * tnu;
+
+  if (out->flags) SE_CUDA(cudaMemsetAsync(out->flags, 0, 4 * sizeof(int32_t), st));
+  SE_TRY(launch_cem_init_dist(c->mean, c->stdv, (int)dist, st));
+
+  ActionSrc<T> src;
+  memset(&src, 0, sizeof(src));
+  src.seed = seed, src.n_global = Ng, src.tnu = tnu;
+  CostView<T> costs{pack_all, M, Nl};
+
+  for (int it = 0; it < cf.num_iterations; ++it) {
+    src.mode = noise ? 1 : 0;
+    src.iteration = it;
+    src.ext = noise ? noise + (size_t)it * M * Ng * tnu : nullptr;
+    src.mean = c->mean + (size_t)it * dist;
+    src.stdv = c->stdv + (size_t)it * dist;
+    T* rec_act = out->rollout_actions ? (T*)out->rollout_actions + (size_t)it * cand * tnu : nullptr;
+    T* rec_traj = out->trajectories ? (T*)out->trajectories + (size_t)it * cand * (T_len + 1) * S : nullptr;
+    SE_TRY(launch_cem_sample<T>(src, M, cf.first_rollout, Nl, ns, p0, actions, p, rec_act, st));
+
+    // RolloutFunction._sample_trajectory (constrained_cem_mpc.py:175-183): T sequential ellipsoid steps
+    for (int t = 0; t < T_len; ++t) {
+      const bool point = t == 0;  // get_action starts from a point state: q = None (safempc_cem.py:234-235, quirk Q9)
+      SE_TRY(gp_posterior<T>(g, p, ns, actions + (int64_t)t * nu, tnu, cand, mean, var, point ? nullptr : jac, st));
+      StepIO<T> io;
+      memset(&io, 0, sizeof(io));
+      io.p_in = p, io.q_in = q, io.p_out = p, io.q_out = q;
+      io.u = actions + (int64_t)t * nu, io.u_stride = tnu;
+      io.mean = mean, io.var = var, io.jac = jac;
+      io.point = point ? 1 : 0;
+      io.objective = objective, io.constraint = constraint;
+      io.first_step = t == 0, io.last_step = t == T_len - 1;
+      io.act_all = actions, io.T_len = T_len, io.t_index = t;
+      io.traj = rec_traj;
+      io.flags = out->flags;
+      SE_TRY(launch_reach_step<T>(pr, io, cand, st));
+    }
+
+    T* rec_obj = out->objective ? (T*)out->objective + (size_t)it * cand : nullptr;
+    T* rec_con = out->constraint ? (T*)out->constraint + (size_t)it * cand : nullptr;
+    SE_TRY(launch_cem_pack_costs<T>(objective, constraint, cand, pack_local, rec_obj, rec_con, st));
+    if (c->world > 1) {
+      // the one collective of the path: per-candidate (objective, constraint) costs of every rank
+      const int r = g_nccl.AllGather(pack_local, pack_all, (size_t)(2 * cand), sizeof(T) == 8 ? 8 : 7, c->comm, st);
+      SE_REQUIRE(r == 0, "ncclAllGather failed: %s", g_nccl.GetErrorString ? g_nccl.GetErrorString(r) : "?");
+    }
+
+    SelectArgs<T> sa;
+    memset(&sa, 0, sizeof(sa));
+    sa.costs = costs, sa.n_global = Ng, sa.num_elites = cf.num_elites, sa.src = src;
+    sa.mean_next = c->mean + (size_t)(it + 1) * dist;
+    sa.std_next = c->stdv + (size_t)(it + 1) * dist;
+    sa.elite_ids = out->elite_ids ? out->elite_ids + (size_t)it * M * cf.num_elites : nullptr;
+    sa.mean_hist = out->means ? (T*)out->means + (size_t)it * dist : nullptr;
+    sa.std_hist = out->stds ? (T*)out->stds + (size_t)it * dist : nullptr;
+    SE_TRY(launch_cem_select_refit<T>(sa, M, st));
+  }
+  // get_actions: rollouts of the LAST iteration (sampled from the distribution of iteration I-1)
+  T* act_out = out->actions ? (T*)out->actions : (T*)c->act_out;
+  int32_t* found = out->found ? out->found : c->found;
+  int32_t* best = out->best_id ? out->best_id : c->best;
+  SE_TRY(launch_cem_pick<T>(costs, Ng, cf.pick_best, src, M, act_out, found, best, st));
+  return 0;
+}
+
+extern "C" int se_cem_solve(se_cem_t c, const void* dev_p0, const void* dev_noise, uint64_t seed,
+                            const se_cem_outputs* out, void* stream) {
+  SE_REQUIRE(c && dev_p0 && out, "se_cem_solve: NULL argument");
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (c->gp->dtype == SE_F64)
+    return cem_solve_t<double>(c, c->pd, (const double*)dev_p0, (const double*)dev_noise, seed, out, st);
+  return cem_solve_t<float>(c, c->pf, (const float*)dev_p0, (const float*)dev_noise, seed, out, st);
+}
+
+extern "C" int se_cem_noise(se_dtype dtype, uint64_t seed, int iteration, int num_instances, int num_rollouts_global,
+                            int first_rollout, int count, int T, int n_u, void* dev_noise_out, void* stream) {
+  SE_REQUIRE(dev_noise_out && count >= 0 && T >= 1 && n_u >= 1 && num_instances >= 1, "se_cem_noise: bad arguments");
+  if (count == 0) return 0;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (dtype == SE_F64)
+    return launch_cem_noise<double>(seed, iteration, num_instances, num_rollouts_global, first_rollout, count, T * n_u,
+                                    (double*)dev_noise_out, st);
+  return launch_cem_noise<float>(seed, iteration, num_instances, num_rollouts_global, first_rollout, count, T * n_u,
+                                 (float*)dev_noise_out, st);
+}
+
+template <typename T>
+static int select_refit_t(const T* objective, const T* constraint, const T* actions, int N, int T_len, int n_u, int E,
+                          int32_t* elite_ids, T* mean_out, T* std_out, cudaStream_t st) {
+  // temporary device buffers (test / integration entry point, not on the solve path)
+  T* pack = nullptr;
+  double* dist = nullptr;
+  const int tnu = T_len * n_u;
+  SE_CUDA(cudaMalloc(&pack, (size_t)2 * N * sizeof(T)));
+  SE_CUDA(cudaMalloc(&dist, (size_t)4 * tnu * sizeof(double)));
+  int rc = launch_cem_pack_costs<T>(objective, constraint, N, pack, nullptr, nullptr, st);
+  if (rc == 0) rc = launch_cem_init_dist(dist, dist + tnu, tnu, st);
+  SelectArgs<T> sa;
+  memset(&sa, 0, sizeof(sa));
+  sa.costs = CostView<T>{pack, 1, N};
+  sa.n_global = N, sa.num_elites = E;
+  sa.src.mode = 2, sa.src.n_global = N, sa.src.tnu = tnu, sa.src.ext = actions;
+  sa.src.mean = dist, sa.src.stdv = dist + tnu;
+  sa.mean_next = dist + 2 * tnu, sa.std_next = dist + 3 * tnu;
+  sa.elite_ids = elite_ids, sa.mean_hist = mean_out, sa.std_hist = std_out;
+  if (rc == 0) rc = launch_cem_select_refit<T>(sa, 1, st);
+  cudaStreamSynchronize(st);
+  cudaFree(pack);
+  cudaFree(dist);
+  return rc;
+}
+
+extern "C" int se_cem_select_refit(se_dtype dtype, const void* dev_objective, const void* dev_constraint,
+                                   const void* dev_actions, int N, int T, int n_u, int E, int32_t* dev_elite_ids,
+                                   void* dev_mean, void* dev_std, void* stream) {
+  SE_REQUIRE(dev_objective && dev_constraint && dev_actions, "se_cem_select_refit: NULL argument");
+  SE_REQUIRE(E >= 1 && E <= kMaxElites && E <= N, "se_cem_select_refit: num_elites = %d must be in [1, min(%d, N = %d)]",
+             E, kMaxElites, N);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (dtype == SE_F64)
+    return select_refit_t<double>((const double*)dev_objective, (const double*)dev_constraint,
+                                  (const double*)dev_actions, N, T, n_u, E, dev_elite_ids, (double*)dev_mean,
+                                  (double*)dev_std, st);
+  return select_refit_t<float>((const float*)dev_objective, (const float*)dev_constraint, (const float*)dev_actions, N,
+                               T, n_u, E, dev_elite_ids, (float*)dev_mean, (float*)dev_std, st);
+}
