@@ -1,0 +1,328 @@
+#!/usr/bin/env python
+"""bench.py -- headline benchmark of the safe CEM-MPC hot path (BASELINE.json metric).
+
+A "step" is one MPC solve (one `ConstrainedCemMpc.get_actions`: I CEM iterations x N candidates x T ellipsoid steps)
+on synthetic data of the BASELINE config C2 (InvertedPendulum, GP on 2000 training points, horizon 10, population
+16384 per GPU).  metric = candidate ellipsoid-rollout steps / s = N T I / t_solve, whole job.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference] [--dtype f64|f32] [--config C2|C1|C3]
+
+N > 1 is launched by the driver under torch.distributed.run (one rank per GPU): the population is sharded over the
+ranks (weak scaling: 16384 candidates per GPU) with one NCCL all-gather of candidate costs per CEM iteration.
+`--impl reference` times the reference's CPU path (the float64 oracle port, all host threads) on a bounded sample of the
+same workload and prints the same JSON line with "impl": "reference".
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+import numpy as np  # noqa: E402
+import torch  # noqa: E402
+
+METRIC = 'candidate ellipsoid-rollout steps/sec'
+UNIT = 'candidate-steps/s'
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument('--gpus', type=int, default=1)
+    ap.add_argument('--steps', type=int, default=5)
+    ap.add_argument('--warmup', type=int, default=3)
+    ap.add_argument('--impl', default='b200', choices=['b200', 'reference'])
+    ap.add_argument('--dtype', default='f64', choices=['f64', 'f32'])
+    ap.add_argument('--config', default='C2', choices=['C1', 'C2', 'C3'])
+    ap.add_argument('--gemm', default='auto', choices=['auto', 'simt', 'mma'])
+    ap.add_argument('--cpu-sample', type=int, default=2048, help='candidates in the CPU-baseline sample')
+    ap.add_argument('--no-cpu-baseline', action='store_true')
+    return ap.parse_args()
+
+
+def make_workload(name: str, world: int):
+    from safe_exploration_b200 import workloads
+    if name == 'C1':
+        return workloads.pendulum_workload(n_train=100, num_rollouts=500 * world if world > 1 else 500, time_horizon=5,
+                                           num_elites=20, num_iterations=8, name='C1')
+    if name == 'C3':
+        return workloads.cartpole_workload(num_rollouts=max(8192 * world, 8192))
+    return workloads.pendulum_workload(num_rollouts=16384 * world)
+
+
+def workload_desc(w, world, dtype):
+    return {'workload': f'{w.name}: {w.meta["env"]} safe CEM-MPC, exact GP n_train={w.n_train}, horizon {w.time_horizon}, '
+                        f'population {w.num_rollouts} ({w.num_rollouts // world}/GPU), elites {w.num_elites}, '
+                        f'iterations {w.num_iterations}',
+            'n_s': w.n_s, 'n_u': w.n_u, 'n_train': w.n_train, 'time_horizon': w.time_horizon,
+            'population': w.num_rollouts, 'elites': w.num_elites, 'iterations': w.num_iterations,
+            'parallelism': f'population-sharded x{world}' if world > 1 else 'single GPU',
+            'cache': 'inputs_larger_than_l2 (kernel rows K* of one horizon step: %.0f MB vs 126 MB L2)' %
+                     (w.n_s * (w.num_rollouts // world) * w.n_train * (8 if dtype == 'f64' else 4) / 1e6)}
+
+
+# ---- CPU baseline: the reference's path, float64, eager torch, all host threads ------------------------------------------
+def cpu_reference_run(w, sample: int, repeats: int, warmup: int):
+    """One CEM iteration (sample -> T reachability steps -> constraint loop -> elite selection -> refit) of the oracle
+    port with the reference's per-item Python loops, on `sample` candidates of the same workload (full n_train, full
+    horizon).  Returns (candidate-steps/s, seconds per iteration, threads)."""
+    from oracle import oracle
+    threads = os.cpu_count() or 1
+    torch.set_num_threads(threads)
+    T = lambda x: torch.as_tensor(np.asarray(x, dtype=np.float64))
+    gp = oracle.OracleGpCemSSM(w.n_s, w.n_u, w.lengthscale, w.outputscale, w.noise)
+    gp.update_model(T(w.x_train), T(w.y_train), replace_old=True)
+    prob = oracle.SafeCemProblem(gp, w.l_mu, w.l_sigma, w.k_fb, w.a, w.b, w.beta_safety, w.h_mat, w.h_vec, w.act_a,
+                                 w.act_b)
+    elites = max(2, min(w.num_elites, sample // 4))
+    times = []
+    for rep in range(warmup + repeats):
+        noise = T(oracle.philox_normal_noise(rep, 0, 0, sample, w.time_horizon, w.n_u)).unsqueeze(0)
+        t0 = time.perf_counter()
+        oracle.cem_solve(prob, T(w.p0), noise, elites, loops=True)
+        dt = time.perf_counter() - t0
+        if rep >= warmup:
+            times.append(dt)
+    sec = float(np.median(times))
+    return sample * w.time_horizon / sec, sec, threads
+
+
+def run_reference(args):
+    rank = int(os.environ.get('RANK', '0'))
+    if rank != 0:
+        return
+    w = make_workload(args.config, 1)
+    value, sec, threads = cpu_reference_run(w, args.cpu_sample, max(1, args.steps), max(0, min(args.warmup, 1)))
+    line = {
+        'impl': 'reference', 'metric': METRIC, 'value': value, 'unit': UNIT, 'n_gpus': args.gpus, 'steps': args.steps,
+        'warmup': args.warmup, 'ms_per_step': sec * 1e3, 'higher_is_better': True, 'scaling': 'weak',
+        'vs_baseline': None, 'dtype': 'f64', 'data': 'synthetic', 'config': workload_desc(w, 1, 'f64'),
+        'cpu_baseline': {'value': value, 'unit': UNIT, 'cores': threads, 'kind': 'port',
+                         'sample': f'{args.cpu_sample} candidates x horizon {w.time_horizon} x 1 CEM iteration at full '
+                                   f'n_train={w.n_train} (reference per-item Python loops kept); '
+                                   f'the reference itself is Python + gpytorch 0.3.2 and cannot run on this box'},
+        'e2e': {'value': value, 'unit': UNIT, 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0},
+        'gpu_launches': 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+# ---- clocks ----------------------------------------------------------------------------------------------------------------
+class ClockSampler:
+    def __init__(self, index: int):
+        self.index, self.samples, self.reasons, self.max_mhz = index, [], set(), None
+        self._stop = threading.Event()
+        self._thread = threading.Thread(target=self._run, daemon=True)
+
+    def _run(self):
+        q = ('clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,'
+             'clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap')
+        names = ['hw_slowdown', 'hw_thermal_slowdown', 'sw_thermal_slowdown', 'sw_power_cap']
+        while not self._stop.is_set():
+            try:
+                out = subprocess.run(['nvidia-smi', f'--id={self.index}', f'--query-gpu={q}',
+                                      '--format=csv,noheader,nounits'], capture_output=True, text=True, timeout=5).stdout
+                f = [s.strip() for s in out.strip().split(',')]
+                self.samples.append(float(f[0]))
+                self.max_mhz = float(f[1])
+                for n, v in zip(names, f[2:6]):
+                    if v.lower().startswith('active'):
+                        self.reasons.add(n)
+            except Exception:
+                pass
+            self._stop.wait(0.2)
+
+    def __enter__(self):
+        self._thread.start()
+        return self
+
+    def __exit__(self, *a):
+        self._stop.set()
+        self._thread.join(timeout=6)
+
+    def summary(self):
+        return {'sm_mhz': float(np.median(self.samples)) if self.samples else None, 'sm_max_mhz': self.max_mhz,
+                'reasons': sorted(self.reasons), 'samples': len(self.samples)}
+
+
+def measured_peaks():
+    path = os.path.join(ROOT, 'MEASURED_PEAKS.json')
+    if os.path.exists(path):
+        with open(path) as f:
+            return json.load(f), 'measured'
+    return {'hbm_gbs': 6650.0, 'bf16_tflops': 1590.0, 'bf16_tflops_sustained': 1400.0}, 'fallback'
+
+
+# ---- the B200 arm ----------------------------------------------------------------------------------------------------------
+def run_b200(args):
+    import ctypes as C
+    import torch.distributed as dist
+    import safe_exploration_b200 as se
+    from safe_exploration_b200 import _lib, workloads
+    from safe_exploration_b200 import dist as sedist
+
+    rank = int(os.environ.get('RANK', '0'))
+    world = int(os.environ.get('WORLD_SIZE', '1'))
+    local_rank = int(os.environ.get('LOCAL_RANK', '0'))
+    if world != args.gpus and world > 1:
+        raise SystemExit(f'--gpus {args.gpus} but WORLD_SIZE={world}')
+    torch.cuda.set_device(local_rank)
+    dev = f'cuda:{local_rank}'
+    if world > 1:
+        dist.init_process_group('nccl', device_id=torch.device(dev))
+    lib = se.load_library()
+    dtype = torch.float64 if args.dtype == 'f64' else torch.float32
+    gemm = {'auto': _lib.SE_GEMM_AUTO, 'simt': _lib.SE_GEMM_SIMT, 'mma': _lib.SE_GEMM_MMA}[args.gemm]
+
+    w = make_workload(args.config, world)
+    ssm, mpc = workloads.build_solver(w, dtype=dtype, device=dev, record='none', seed=1234, gemm_impl=gemm)
+    comm = sedist.attach_population_sharding(mpc) if world > 1 else 0
+    p0 = torch.as_tensor(w.p0, device=dev, dtype=dtype).unsqueeze(0)
+    cand_steps = w.num_rollouts * w.time_horizon * w.num_iterations  # whole job, all ranks
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+            torch.cuda.synchronize()
+
+    # warm-up (also grows every workspace, so the timed region makes no allocation inside the library)
+    for _ in range(max(3, args.warmup)):
+        mpc.solve(p0, sync=False)
+    barrier()
+
+    # ---- device-resident timing: K solves between two events, max over ranks ----
+    _lib.check(lib.se_gp_timing_enable(ssm.handle, 1))
+    lib.se_launch_count_reset()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    with ClockSampler(local_rank) as clocks:
+        barrier()
+        ev0.record()
+        for _ in range(args.steps):
+            res = mpc.solve(p0, sync=False)
+        ev1.record()
+        barrier()
+    ms_total = ev0.elapsed_time(ev1)
+    launches = int(lib.se_launch_count())
+    gemm_ms, kstar_ms = C.c_double(0), C.c_double(0)
+    gemm_n, kstar_n = C.c_int64(0), C.c_int64(0)
+    _lib.check(lib.se_gp_timing_read(ssm.handle, C.byref(gemm_ms), C.byref(gemm_n), C.byref(kstar_ms),
+                                     C.byref(kstar_n), _lib.stream_ptr(dev)))
+    _lib.check(lib.se_gp_timing_enable(ssm.handle, 0))
+    if world > 1:
+        t = torch.tensor([ms_total], device=dev, dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms_total = float(t.item())
+    ms_per_step = ms_total / args.steps
+    value = cand_steps / (ms_per_step * 1e-3)
+    flags = res['flags'].cpu().tolist()
+
+    # ---- end to end through the public API: host state in, host action out, every step ----
+    class Env:
+        n_s, n_u = w.n_s, w.n_u
+        l_mu, l_sigm = w.l_mu, w.l_sigma
+        objective_spec = None
+
+    class Conf:
+        mpc_time_horizon, cem_num_rollouts = w.time_horizon, w.num_rollouts
+        cem_num_elites, cem_num_iterations = w.num_elites, w.num_iterations
+        use_prior_model, cem_record = True, 'none'
+
+    solver = se.B200CemSafeMPC(ssm, mpc._constraints, Env, Conf, {'lin_model': (w.a, w.b)}, None, None, w.beta_safety,
+                               safe_policy=lambda s: np.zeros(w.n_u), lqr=_FixedGain(w.k_fb), mpc=mpc, verbose=False)
+    state_host = np.ascontiguousarray(w.p0, dtype=np.float64)
+    for _ in range(2):
+        solver.get_action(state_host)
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        action, result = solver.get_action(state_host)
+    barrier()
+    e2e_sec = (time.perf_counter() - t0) / args.steps
+    if world > 1:
+        t = torch.tensor([e2e_sec], device=dev, dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        e2e_sec = float(t.item())
+    esz = 8 if args.dtype == 'f64' else 4
+    e2e = {'value': cand_steps / e2e_sec, 'unit': UNIT, 'ms_per_solve': e2e_sec * 1e3,
+           'h2d_bytes_per_step': w.n_s * esz, 'd2h_bytes_per_step': w.time_horizon * w.n_u * esz + 4 + 16,
+           'api': 'B200CemSafeMPC.get_action(ndarray) -> (ndarray, MpcResult)'}
+
+    # ---- roofline of the dominant kernel (variance GEMM) ----
+    peaks, peak_src = measured_peaks()
+    pipe_peak = None
+    if rank == 0:
+        f = C.c_double(0)
+        kinds = [0] if args.dtype == 'f32' else [1, 2]
+        best = 0.0
+        for k in kinds:
+            _lib.check(lib.se_measure_peak(k, C.byref(f)))
+            best = max(best, f.value)
+        pipe_peak = best / 1e12
+    rows_local = w.num_rollouts // world
+    flop_per_launch = w.n_s * float(rows_local) * float(w.n_train) ** 2  # n^2/2 FMA per (candidate, output) = n^2 flop
+    gemm_avg_ms = gemm_ms.value / max(1, gemm_n.value)
+    achieved = flop_per_launch / (gemm_avg_ms * 1e-3) / 1e12 if gemm_avg_ms > 0 else None
+    roofline = {
+        'bound': 'tensor', 'kernel': 'gp_trisumsq (variance GEMM: || L^-1 k* ||^2)',
+        'pipe': 'FP64 (DMMA / DFMA)' if args.dtype == 'f64' else 'FP32 FFMA',
+        'achieved': achieved, 'peak': pipe_peak, 'unit': 'TFLOP/s',
+        'frac': (achieved / pipe_peak) if (achieved and pipe_peak) else None,
+        'peak_source': 'measured in this run with se_measure_peak (register-resident FMA / DMMA loop on every SM); '
+                       f'MEASURED_PEAKS.json ({peak_src}) holds only HBM and bf16 numbers',
+        'flop_per_launch': flop_per_launch, 'avg_launch_ms': gemm_avg_ms, 'launches': int(gemm_n.value),
+        'share_of_step': gemm_ms.value / ms_total if ms_total > 0 else None,
+        'kstar_share_of_step': kstar_ms.value / ms_total if ms_total > 0 else None,
+        'traffic': None,
+        'hbm': {'algorithmic_bytes_per_launch': (w.n_s * rows_local * w.n_train + w.n_s * w.n_train ** 2 / 2) * esz,
+                'peak_gbs': peaks.get('hbm_gbs')},
+    }
+
+    cpu_baseline = None
+    if rank == 0 and not args.no_cpu_baseline:
+        w1 = make_workload(args.config, 1)
+        v, sec, threads = cpu_reference_run(w1, args.cpu_sample, 2, 1)
+        cpu_baseline = {'value': v, 'unit': UNIT, 'cores': threads, 'kind': 'port',
+                        'sample': f'{args.cpu_sample} candidates x horizon {w1.time_horizon} x 1 CEM iteration at full '
+                                  f'n_train={w1.n_train}, float64 eager torch, reference per-item loops kept '
+                                  f'({sec:.2f} s per sample)'}
+    if rank == 0:
+        line = {
+            'metric': METRIC, 'value': value, 'unit': UNIT, 'n_gpus': world, 'steps': args.steps,
+            'warmup': max(3, args.warmup), 'ms_per_step': ms_per_step, 'mpc_solve_ms': ms_per_step,
+            'higher_is_better': True, 'scaling': 'weak', 'vs_baseline': None, 'dtype': args.dtype, 'data': 'synthetic',
+            'config': workload_desc(w, world, args.dtype), 'e2e': e2e, 'gpu_launches': launches, 'roofline': roofline,
+            'cpu_baseline': cpu_baseline, 'clocks': clocks.summary(), 'numeric_flags': flags,
+            'found_solution': bool(int(res['found'][0])), 'last_result': result.name,
+        }
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        barrier()
+        mpc._destroy()
+        sedist.destroy_nccl_comm(comm)
+        dist.destroy_process_group()
+
+
+class _FixedGain:
+    """LqrFeedbackController stand-in carrying the workload's precomputed LQR gain."""
+
+    def __init__(self, k_fb):
+        self._k = np.asarray(k_fb, dtype=np.float64)
+
+    def get_control_matrix(self):
+        return self._k
+
+    def get_control_matrix_pytorch(self):
+        return torch.as_tensor(self._k)
+
+
+if __name__ == '__main__':
+    a = parse_args()
+    if a.impl == 'reference':
+        run_reference(a)
+    else:
+        run_b200(a)

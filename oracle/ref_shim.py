@@ -137,8 +137,8 @@ def install():
     poly_sub = _stub_module("polytope.polytope", Polytope=_Polytope, box2poly=_box2poly)
     poly_pkg.polytope = poly_sub
 
-    if not hasattr(torch, "eig"):
-        torch.eig = _torch_eig  # type: ignore[attr-defined]
+    # torch >= 1.13 keeps a `torch.eig` stub that only raises; replace it
+    torch.eig = _torch_eig  # type: ignore[attr-defined]
     # constrained_cem_mpc.py:167 samples Normal(means, stds) with stds that may reach 0 (quirk Q5).
     torch.distributions.Distribution.set_default_validate_args(False)
 

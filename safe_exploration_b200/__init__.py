@@ -1,0 +1,23 @@
+"""safe_exploration_b200 -- B200-native (sm_100a) safe CEM-MPC + GP ellipsoid reachability.
+
+Drop-in for the hot path of oscarkey/safe-exploration behind the reference's own interfaces:
+
+    reference                                            here
+    ---------------------------------------------------  ------------------------------------------
+    ssm_cem.GpCemSSM (CemSSM)                            ssm.B200GpCemSSM
+    gp_reachability_pytorch.onestep_reachability ...     reachability.onestep_reachability ...
+    constrained_cem_mpc.ConstrainedCemMpc                cem.B200ConstrainedCemMpc
+    safempc_cem.CemSafeMPC (SafeMPC)                     safempc.B200CemSafeMPC
+
+All numerics run in libsecem.so (csrc/, C ABI in include/secem.h); there is no CPU fallback.
+"""
+from ._lib import SE_F32, SE_F64, SE_GEMM_AUTO, SE_GEMM_MMA, SE_GEMM_SIMT, SecemError, load as load_library
+from .cem import (ActionConstraint, B200ConstrainedCemMpc, Constraint, DynamicsFunc, Rollouts, TorchPolytope,
+                  box2torchpoly, sample_noise, select_elites_refit)
+from .reachability import (SafeProblem, is_ellipsoid_inside_polytope, lin_ellipsoid_safety_distance,
+                           multistep_reachability, onestep_reachability)
+from .safempc import (B200CemSafeMPC, B200SafeDynamics, EllipsoidStateConstraint, EllipsoidTerminalConstraint,
+                      LqrFeedbackController, MpcResult, PQFlattener, SafeMPC, construct_constraints, dlqr)
+from .ssm import B200GpCemSSM, CemSSM, assert_shape
+
+__version__ = '0.1.0'

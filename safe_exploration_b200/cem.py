@@ -1,0 +1,299 @@
+"""Constrained CEM-MPC on the B200 behind the reference's `ConstrainedCemMpc` interface
+(constrained-cem-mpc/constrained_cem_mpc/constrained_cem_mpc.py:195-280).
+
+The whole optimisation -- sampling, T ellipsoid steps per candidate, constraint costs, elite selection, refit, final
+pick -- runs on the device inside one asynchronous `se_cem_solve` call; this module only owns tensors and mirrors the
+reference's plug-in types (`TorchPolytope`, `Constraint`s, `DynamicsFunc`, `Rollouts`).
+"""
+import ctypes as C
+from abc import ABC, abstractmethod
+from collections import namedtuple
+from typing import List, Optional, Sequence, Tuple, Union
+
+import numpy as np
+import torch
+from torch import Tensor
+
+from . import _lib
+from .reachability import SafeProblem, check_flags
+from .ssm import B200GpCemSSM, assert_shape
+
+# constrained_cem_mpc.py:127
+Rollouts = namedtuple('Rollouts', 'trajectories actions objective_costs constraint_costs')
+
+
+class TorchPolytope:
+    """{x : A x <= b} (constrained_cem_mpc.py:13-53).  Accepts anything with `.A`, `.b` (e.g. polytope.Polytope) or a
+    pair (A, b)."""
+
+    def __init__(self, polytope):
+        A, b = (polytope.A, polytope.b) if hasattr(polytope, 'A') else polytope
+        self._A = torch.as_tensor(np.asarray(A, dtype=np.float64))
+        self._b = torch.as_tensor(np.asarray(b, dtype=np.float64)).reshape(-1)
+        self.dim = self._A.shape[1]
+        cheb = getattr(polytope, 'chebXc', None)
+        self.chebXc = None if cheb is None else torch.as_tensor(np.asarray(cheb, dtype=np.float64))
+
+    def __contains__(self, x: Tensor) -> bool:
+        assert_shape(x, (self.dim,))
+        return not bool((self._A.to(x) @ x - self._b.to(x) > 0).any())
+
+    def contains_points(self, xs: Tensor) -> int:
+        """Number of rows of xs [N, dim] inside the polytope (boundary counts as inside: strict `>`)."""
+        assert xs.dim() == 2 and xs.shape[1] == self.dim, f'Wanted (N, {self.dim}) got {xs.shape}'
+        outside = ((xs @ self._A.to(xs).t() - self._b.to(xs)) > 0).any(dim=1)
+        return int(xs.shape[0] - outside.sum())
+
+    def to(self, device):
+        self._A = self._A.to(device)
+        self._b = self._b.to(device)
+        if self.chebXc is not None:
+            self.chebXc = self.chebXc.to(device)
+        return self
+
+
+def box2torchpoly(box) -> TorchPolytope:
+    """polytope.box2poly semantics (A = [I; -I], b = [hi; -lo]) -> TorchPolytope (constrained_cem_mpc.py:57-59)."""
+    box = np.asarray(box, dtype=np.float64)
+    n = box.shape[0]
+    poly = TorchPolytope((np.vstack((np.eye(n), -np.eye(n))), np.concatenate((box[:, 1], -box[:, 0]))))
+    poly.chebXc = torch.as_tensor(box.mean(axis=1))
+    return poly
+
+
+class Constraint(ABC):
+    """constrained_cem_mpc.py:62-68: cost >= 0 of one trajectory, 0 iff feasible."""
+
+    @abstractmethod
+    def __call__(self, trajectory: Tensor, actions: Tensor) -> float:
+        pass
+
+
+class ActionConstraint(Constraint):
+    """penalty x #{t : u_t outside the polytope} (constrained_cem_mpc.py:100-110).  Evaluated on the device for every
+    rollout; calling the object evaluates one rollout on the host with the same rule."""
+
+    def __init__(self, safe_region: TorchPolytope, penalty: float = 3):
+        self._self_region = safe_region
+        self._penalty = penalty
+
+    def __call__(self, trajectory: Tensor, actions: Tensor) -> float:
+        return self._penalty * (actions.shape[0] - self._self_region.contains_points(actions))
+
+
+class DynamicsFunc(ABC):
+    """constrained_cem_mpc.py:113-124."""
+
+    @abstractmethod
+    def __call__(self, states: Tensor, actions: Tensor) -> Tuple[Tensor, Tensor]:
+        pass
+
+
+class B200ConstrainedCemMpc:
+    """Drop-in for `ConstrainedCemMpc` whose dynamics are GP ellipsoid reachability (CemSafeMPC._dynamics_func).
+
+    Construction mirrors the reference (:204-220).  `dynamics_func` must be a `safempc.B200SafeDynamics` (it carries
+    the GP handle and the problem constants the fused kernels need); `constraints` is the reference's list
+    [ActionConstraint, EllipsoidTerminalConstraint | EllipsoidStateConstraint] and is folded into the device-side
+    problem.  `state_dimen` is the flat dimension n_s + n_s^2 (PQFlattener).
+
+    Extras over the reference: `noise` (RNG-fixed candidates), `seed`, `pick_best`, `record`, batched instances and
+    population sharding over ranks (`set_comm`).
+    """
+
+    def __init__(self, dynamics_func, constraints: Sequence[Constraint], state_dimen: int, action_dimen: int,
+                 time_horizon: int, num_rollouts: int, num_elites: int, num_iterations: int, rollout_function=None,
+                 seed: int = 0, pick_best: bool = False, record: str = 'full', num_instances: int = 1,
+                 rank: int = 0, world_size: int = 1):
+        from .safempc import B200SafeDynamics, fold_constraints  # local import: safempc imports this module
+        if rollout_function is not None:
+            raise TypeError('rollout_function injection is a unit-test hook of the reference; the B200 path runs the '
+                            'rollouts on the device')
+        if not isinstance(dynamics_func, B200SafeDynamics):
+            raise TypeError('dynamics_func must be a B200SafeDynamics (GP reachability); arbitrary Python dynamics '
+                            'cannot run inside the fused kernels')
+        self._dyn = dynamics_func
+        self._ssm: B200GpCemSSM = dynamics_func.ssm
+        n_s = self._ssm.num_states
+        if state_dimen != n_s + n_s * n_s:
+            raise ValueError(f'Wanted state_dimen {n_s + n_s * n_s}, got {state_dimen}')
+        if action_dimen != self._ssm.num_actions:
+            raise ValueError(f'Wanted action_dimen {self._ssm.num_actions}, got {action_dimen}')
+        if record not in ('full', 'costs', 'none'):
+            raise ValueError(f'record must be full|costs|none, got {record}')
+        if num_rollouts % world_size != 0:
+            raise ValueError(f'num_rollouts {num_rollouts} must be divisible by world_size {world_size}')
+        self._state_dimen = state_dimen
+        self._action_dimen = action_dimen
+        self._time_horizon = time_horizon
+        self._num_rollouts = num_rollouts
+        self._num_elites = num_elites
+        self._num_iterations = num_iterations
+        self._constraints = list(constraints)
+        self._rollout_function = self  # safempc_cem.py:270 reads mpc._rollout_function._constraints
+        self._problem: SafeProblem = fold_constraints(dynamics_func.problem, self._constraints)
+        self.seed = int(seed)
+        self.pick_best = bool(pick_best)
+        self.record = record
+        self.num_instances = int(num_instances)
+        self.rank, self.world_size = int(rank), int(world_size)
+        self._lib = _lib.load()
+        self._handle = C.c_void_p(None)
+        self._handle_key = None
+        self._comm = None
+        self.last_info = {}
+
+    # ---- handle -------------------------------------------------------------------------------------------------
+    def _destroy(self):
+        if getattr(self, '_handle', None):
+            self._lib.se_cem_destroy(self._handle)
+            self._handle = C.c_void_p(None)
+            self._handle_key = None
+
+    def __del__(self):
+        try:
+            self._destroy()
+        except Exception:
+            pass
+
+    def set_comm(self, nccl_comm: Optional[int], rank: int, world_size: int) -> None:
+        """Attach an NCCL communicator made by `dist.create_nccl_comm` (population sharding)."""
+        if self._num_rollouts % world_size != 0:
+            raise ValueError(f'num_rollouts {self._num_rollouts} must be divisible by world_size {world_size}')
+        self._comm, self.rank, self.world_size = nccl_comm, int(rank), int(world_size)
+        self._destroy()
+
+    def _ensure_handle(self):
+        gp_handle = self._ssm.handle
+        key = (gp_handle.value, self.num_instances, self.pick_best, self.rank, self.world_size)
+        if self._handle and self._handle_key == key:
+            return
+        self._destroy()
+        n_local = self._num_rollouts // self.world_size
+        cfg = _lib.SeCemConfig(self.num_instances, self._num_rollouts, self._time_horizon, self._num_elites,
+                               self._num_iterations, 1 if self.pick_best else 0, self.rank * n_local, n_local)
+        cs = self._problem.c_struct()
+        handle = C.c_void_p(None)
+        with torch.cuda.device(self._ssm.device):
+            _lib.check(self._lib.se_cem_create(C.byref(handle), gp_handle, C.byref(cs), C.byref(cfg)))
+            if self.world_size > 1:
+                _lib.check(self._lib.se_cem_set_comm(handle, C.c_void_p(self._comm), self.rank, self.world_size))
+        self._handle, self._handle_key = handle, key
+
+    # ---- solve ----------------------------------------------------------------------------------------------------
+    def solve(self, p0: Tensor, noise: Optional[Tensor] = None, seed: Optional[int] = None, sync: bool = True):
+        """Run the CEM optimisation for M = p0.shape[0] instances.
+
+        :param p0: [M, n_s] initial point states on the device
+        :param noise: None (on-device Philox) or [I, M, N, T, n_u] standard-normal noise
+        :returns: dict of device tensors: actions [M, T, n_u], found [M], best_id [M], means / stds [I, M, T, n_u],
+                  elite_ids [I, M, E], and per `record`: objective / constraint [I, M, N_local],
+                  rollout_actions [I, M, N_local, T, n_u], trajectories [I, M, N_local, T+1, S]
+        """
+        ssm = self._ssm
+        n_s, n_u, T, I, E = ssm.num_states, ssm.num_actions, self._time_horizon, self._num_iterations, self._num_elites
+        M = p0.shape[0]
+        assert_shape(p0, (M, n_s))
+        if M != self.num_instances:
+            self.num_instances = M
+        self._ensure_handle()
+        dev, dt = ssm.device, ssm.dtype
+        p0 = ssm._prep(p0, 'state')
+        n_local = self._num_rollouts // self.world_size
+        S = n_s + n_s * n_s
+        new = lambda shape, dtype=dt: torch.empty(shape, dtype=dtype, device=dev)
+        res = dict(actions=new((M, T, n_u)), found=new((M,), torch.int32), best_id=new((M,), torch.int32),
+                   means=new((I, M, T, n_u)), stds=new((I, M, T, n_u)), elite_ids=new((I, M, E), torch.int32),
+                   flags=torch.zeros(4, dtype=torch.int32, device=dev))
+        if self.record in ('full', 'costs'):
+            res['objective'] = new((I, M, n_local))
+            res['constraint'] = new((I, M, n_local))
+        if self.record == 'full':
+            res['rollout_actions'] = new((I, M, n_local, T, n_u))
+            res['trajectories'] = new((I, M, n_local, T + 1, S))
+        if noise is not None:
+            assert_shape(noise, (I, M, self._num_rollouts, T, n_u))
+            noise = ssm._prep(noise, 'noise')
+        out = _lib.SeCemOutputs()
+        for name, _ in _lib.SeCemOutputs._fields_:
+            t = res.get(name)
+            setattr(out, name, None if t is None else t.data_ptr())
+        if seed is None:
+            seed = self.seed
+            self.seed += 1  # a fresh candidate stream per solve, like successive draws from torch's generator
+        with torch.cuda.device(dev):
+            _lib.check(self._lib.se_cem_solve(self._handle, _lib.ptr(p0), _lib.ptr(noise), C.c_uint64(int(seed)),
+                                              C.byref(out), _lib.stream_ptr(dev)))
+        if sync:
+            check_flags(res['flags'].cpu(), 'CEM rollouts')
+        return res
+
+    def _flat_state_to_p0(self, state: Tensor) -> Tensor:
+        n_s = self._ssm.num_states
+        state = state.reshape(1, -1) if state.dim() == 1 else state
+        assert_shape(state, (state.shape[0], self._state_dimen))
+        if bool((state[:, n_s:] != 0).any()):
+            raise NotImplementedError('the fused CEM path starts from point states (q = 0), as CemSafeMPC.get_action does')
+        return state[:, :n_s]
+
+    def _rollouts_of(self, res, inst: int = 0) -> List[Rollouts]:
+        out = []
+        for i in range(self._num_iterations):
+            out.append(Rollouts(res['trajectories'][i, inst] if 'trajectories' in res else None,
+                                res['rollout_actions'][i, inst] if 'rollout_actions' in res else None,
+                                res['objective'][i, inst] if 'objective' in res else None,
+                                res['constraint'][i, inst] if 'constraint' in res else None))
+        return out
+
+    def optimize_trajectories(self, initial_state: Tensor, noise: Optional[Tensor] = None) -> List[Rollouts]:
+        """constrained_cem_mpc.py:222-239 -> rollouts of every iteration (final one last)."""
+        res = self.solve(self._flat_state_to_p0(initial_state), None if noise is None else noise.unsqueeze(1))
+        self.last_info = res
+        return self._rollouts_of(res)
+
+    def get_actions(self, state: Tensor, noise: Optional[Tensor] = None
+                    ) -> Tuple[Union[Tensor, None], List[Rollouts]]:
+        """constrained_cem_mpc.py:259-280: (actions [T, n_u] of a feasible rollout of the last iteration | None,
+        rollouts by iteration).  `noise` [I, N, T, n_u] fixes the candidates (parity tests)."""
+        res = self.solve(self._flat_state_to_p0(state), None if noise is None else noise.unsqueeze(1))
+        self.last_info = res
+        actions = res['actions'][0] if int(res['found'][0]) == 1 else None
+        return actions, self._rollouts_of(res)
+
+    def get_actions_batch(self, states: Tensor, noise: Optional[Tensor] = None):
+        """M independent MPC problems side by side (BASELINE config "batched independent MPC solves").
+        :param states: [M, n_s] point states -> actions [M, T, n_u], found [M] (bool)"""
+        res = self.solve(states, noise)
+        self.last_info = res
+        return res['actions'], res['found'].bool()
+
+
+def select_elites_refit(objective_costs: Tensor, constraint_costs: Tensor, actions: Tensor, num_elites: int):
+    """ConstrainedCemMpc._select_elites + the refit of optimize_trajectories (constrained_cem_mpc.py:234-257) on given
+    costs, evaluated by the same device kernel the solver uses.  -> elite_ids [E] (int32), mean [T, n_u], std [T, n_u]"""
+    _lib.require_cuda(objective_costs, 'objective_costs')
+    lib = _lib.load()
+    N, T, n_u = actions.shape
+    dt, dev = actions.dtype, actions.device
+    code = _lib.dtype_code(dt)
+    obj = objective_costs.detach().to(dt).contiguous()
+    con = constraint_costs.detach().to(dt).contiguous()
+    act = actions.detach().contiguous()
+    ids = torch.empty((num_elites,), dtype=torch.int32, device=dev)
+    mean = torch.empty((T, n_u), dtype=dt, device=dev)
+    std = torch.empty((T, n_u), dtype=dt, device=dev)
+    with torch.cuda.device(dev):
+        _lib.check(lib.se_cem_select_refit(code, _lib.ptr(obj), _lib.ptr(con), _lib.ptr(act), N, T, n_u, num_elites,
+                                           _lib.ptr(ids), _lib.ptr(mean), _lib.ptr(std), _lib.stream_ptr(dev)))
+    return ids, mean, std
+
+
+def sample_noise(seed: int, iteration: int, num_instances: int, num_rollouts: int, first: int, count: int, T: int,
+                 n_u: int, dtype=torch.float64, device='cuda:0') -> Tensor:
+    """The candidate noise `solve` draws on the device (Philox4x32-10) -> [M, count, T, n_u]."""
+    lib = _lib.load()
+    out = torch.empty((num_instances, count, T, n_u), dtype=dtype, device=device)
+    with torch.cuda.device(out.device):
+        _lib.check(lib.se_cem_noise(_lib.dtype_code(dtype), C.c_uint64(seed), iteration, num_instances, num_rollouts,
+                                    first, count, T, n_u, _lib.ptr(out), _lib.stream_ptr(out.device)))
+    return out

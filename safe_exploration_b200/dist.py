@@ -1,0 +1,77 @@
+"""Multi-GPU plumbing: one process per GPU, `torch.distributed` for the rendezvous, the data path's one
+collective (all-gather of per-candidate costs) issued by libsecem.so itself on the solve stream through NCCL.
+
+Two ways to use W GPUs:
+  * population sharding  -- rank r owns candidates [r N/W, (r+1) N/W) of every MPC instance; one all-gather of
+    (objective, constraint) per CEM iteration; every rank takes the same elite decision and regenerates the elites'
+    action sequences from the counter-based RNG, so nothing else is exchanged.  `attach_population_sharding`.
+  * instance sharding    -- independent MPC problems are dealt out to the ranks, no communication on the data path.
+    `shard_instances`.
+The GP training set and its factors are replicated on every rank.
+"""
+import ctypes as C
+from typing import Optional, Tuple
+
+import torch
+import torch.distributed as dist
+
+from . import _lib
+
+
+def shard_range(total: int, rank: int, world_size: int) -> Tuple[int, int]:
+    """Contiguous even split used for the population: (first, count).  `total` must be divisible by `world_size`."""
+    if total % world_size != 0:
+        raise ValueError(f'{total} candidates cannot be split evenly over {world_size} ranks')
+    count = total // world_size
+    return rank * count, count
+
+
+def shard_instances(num_instances: int, rank: int, world_size: int) -> Tuple[int, int]:
+    """Instance-parallel split (first, count); the remainder goes to the lowest ranks."""
+    base, rem = divmod(num_instances, world_size)
+    count = base + (1 if rank < rem else 0)
+    first = rank * base + min(rank, rem)
+    return first, count
+
+
+def owner_of(global_id: int, total: int, world_size: int) -> Tuple[int, int]:
+    """(rank, local index) of a global candidate id under `shard_range`."""
+    count = total // world_size
+    return global_id // count, global_id % count
+
+
+def create_nccl_comm(group: Optional[dist.ProcessGroup] = None, device: Optional[torch.device] = None) -> int:
+    """Create an ncclComm_t for libsecem.so over the ranks of `group` (default: the world).  Rank 0 makes the unique
+    id, torch.distributed carries its 128 bytes to the other ranks (any backend), every rank calls ncclCommInitRank."""
+    lib = _lib.load()
+    rank, world = dist.get_rank(group), dist.get_world_size(group)
+    buf = C.create_string_buffer(128)
+    if rank == 0:
+        _lib.check(lib.se_nccl_unique_id(buf))
+    backend = dist.get_backend(group)
+    t = torch.frombuffer(bytearray(buf.raw), dtype=torch.uint8).clone()
+    if backend == 'nccl':
+        dev = device if device is not None else torch.device('cuda', torch.cuda.current_device())
+        t = t.to(dev)
+    dist.broadcast(t, src=dist.get_global_rank(group, 0) if group is not None else 0, group=group)
+    uid = bytes(t.cpu().numpy().tobytes())
+    comm = C.c_void_p(None)
+    _lib.check(lib.se_nccl_comm_init(C.byref(comm), world, uid, rank))
+    return comm.value
+
+
+def destroy_nccl_comm(comm: Optional[int]) -> None:
+    if comm:
+        _lib.load().se_nccl_comm_destroy(C.c_void_p(comm))
+
+
+def attach_population_sharding(mpc, group: Optional[dist.ProcessGroup] = None) -> int:
+    """Shard `mpc`'s population over the ranks of `group`; returns the communicator (keep it alive, destroy it with
+    `destroy_nccl_comm`)."""
+    rank, world = dist.get_rank(group), dist.get_world_size(group)
+    if world == 1:
+        mpc.set_comm(None, 0, 1)
+        return 0
+    comm = create_nccl_comm(group, mpc._ssm.device)
+    mpc.set_comm(comm, rank, world)
+    return comm

@@ -1,0 +1,330 @@
+"""`B200CemSafeMPC`: drop-in for the reference's `CemSafeMPC` (safe_exploration/safempc_cem.py:159-344) -- same
+constructor arguments, same `get_action` state machine (FOUND_SOLUTION -> PREVIOUS_SOLUTION -> SAFE_CONTROLLER), same
+`update_model` prior subtraction -- with the optimisation delegated to `B200ConstrainedCemMpc`.
+"""
+from abc import ABC, abstractmethod
+from enum import Enum
+from functools import lru_cache
+from typing import Callable, Dict, List, Optional, Sequence, Tuple, Union
+
+import numpy as np
+import scipy.linalg
+import torch
+from numpy import ndarray
+from torch import Tensor
+
+from . import _lib
+from .cem import ActionConstraint, B200ConstrainedCemMpc, Constraint, DynamicsFunc, TorchPolytope, box2torchpoly
+from .reachability import SafeProblem, is_ellipsoid_inside_polytope, onestep_reachability
+from .ssm import B200GpCemSSM, assert_shape
+
+
+class MpcResult(Enum):
+    """safempc_cem.py:23-27."""
+    FOUND_SOLUTION = 1
+    PREVIOUS_SOLUTION = 2
+    SAFE_CONTROLLER = 3
+
+
+class SafeMPC(ABC):
+    """safe_exploration/safempc.py:8-77 (the subset of abstract members CemSafeMPC implements)."""
+
+    @property
+    @abstractmethod
+    def state_dimen(self) -> int:
+        pass
+
+    @property
+    @abstractmethod
+    def action_dimen(self) -> int:
+        pass
+
+    @abstractmethod
+    def get_action(self, state: ndarray):
+        pass
+
+    @abstractmethod
+    def update_model(self, x: ndarray, y: ndarray, opt_hyp=False, replace_old=True, reinitialize_solver=True) -> None:
+        pass
+
+    @abstractmethod
+    def collect_metrics(self) -> Dict[str, float]:
+        pass
+
+
+class PQFlattener:
+    """[p | vec(q)] <-> (p, q) (safempc_cem.py:30-76); an all-zero q for the whole batch means point states."""
+
+    def __init__(self, state_dimen: int):
+        self._state_dimen = state_dimen
+
+    def flatten(self, p: Tensor, q: Optional[Tensor]) -> Tensor:
+        N = p.size(0)
+        if q is None:
+            q = torch.zeros((N, self._state_dimen, self._state_dimen), dtype=p.dtype, device=p.device)
+        assert_shape(p, (N, self._state_dimen,))
+        assert_shape(q, (N, self._state_dimen, self._state_dimen))
+        return torch.cat((p.reshape(N, -1), q.reshape(N, -1)), dim=1)
+
+    def unflatten(self, flat: Tensor) -> Tuple[Tensor, Optional[Tensor]]:
+        N = flat.size(0)
+        assert_shape(flat, (N, self.get_flat_state_dimen(),))
+        p = flat[:, 0:self._state_dimen]
+        q = flat[:, self._state_dimen:].reshape(N, self._state_dimen, self._state_dimen)
+        if not bool((q != 0).any()):
+            q = None
+        return p, q
+
+    def get_flat_state_dimen(self):
+        return self._state_dimen + (self._state_dimen * self._state_dimen)
+
+
+class EllipsoidStateConstraint(Constraint):
+    """safempc_cem.py:116-132.  NOTE (quirk Q1): like the reference, only the LAST ellipsoid of the trajectory is
+    checked; pass `all_states=True` for the intended all-states semantics."""
+
+    def __init__(self, state_dimen: int, safe_polytope_a: np.ndarray, safe_polytope_b: np.ndarray, device: str = None,
+                 all_states: bool = False):
+        self._pq_flattener = PQFlattener(state_dimen)
+        self._polytope_a = torch.as_tensor(np.asarray(safe_polytope_a, dtype=np.float64), device=device)
+        self._polytope_b = torch.as_tensor(np.asarray(safe_polytope_b, dtype=np.float64), device=device).reshape(-1, 1)
+        self.all_states = all_states
+
+    def __call__(self, trajectory, actions) -> float:
+        states = trajectory[1:] if self.all_states else trajectory[-1:]
+        p, q = self._pq_flattener.unflatten(states)
+        inside = is_ellipsoid_inside_polytope(p, q, self._polytope_a.to(p), self._polytope_b.to(p))
+        return (inside.size(0) - inside.sum()) * 10
+
+
+class EllipsoidTerminalConstraint(Constraint):
+    """safempc_cem.py:102-113."""
+
+    def __init__(self, state_dimen: int, safe_polytope_a: np.ndarray, safe_polytope_b: np.ndarray, device: str = None):
+        self._constraint = EllipsoidStateConstraint(state_dimen, safe_polytope_a, safe_polytope_b, device)
+        self._polytope_a = self._constraint._polytope_a
+        self._polytope_b = self._constraint._polytope_b
+
+    def __call__(self, trajectory, actions) -> float:
+        return self._constraint(trajectory[-1:, :], actions[-1:, :])
+
+
+def construct_constraints(conf, env) -> List[Constraint]:
+    """safempc_cem.py:135-146: [ActionConstraint(normalised action box), Ellipsoid{State|Terminal}Constraint]."""
+    h_mat_safe, h_safe, _, _ = env.get_safety_constraints(normalize=True)
+    boxes = np.array([np.array(xs) for xs in zip(env.u_min_norm, env.u_max_norm)])
+    action_constraint = ActionConstraint(box2torchpoly(boxes))
+    if conf.use_state_constraint:
+        constraint = EllipsoidStateConstraint(env.n_s, h_mat_safe, h_safe)
+    else:
+        constraint = EllipsoidTerminalConstraint(env.n_s, h_mat_safe, h_safe)
+    return [action_constraint, constraint]
+
+
+class B200SafeDynamics(DynamicsFunc):
+    """The dynamics plug-in of CemSafeMPC (safempc_cem.py:288-302) as an object the fused kernels understand: it holds
+    the GP and the constants of one ellipsoid step.  Calling it performs one batched step on the device, so it also
+    works as a plain `DynamicsFunc`."""
+
+    def __init__(self, ssm: B200GpCemSSM, problem: SafeProblem):
+        self.ssm = ssm
+        self.problem = problem
+        self._pq = PQFlattener(ssm.num_states)
+
+    def __call__(self, states: Tensor, actions: Tensor) -> Tuple[Tensor, Tensor]:
+        pr = self.problem
+        ps, qs = self._pq.unflatten(states)
+        dev, dt = states.device, states.dtype
+        t = lambda x: torch.as_tensor(x, dtype=dt, device=dev)
+        p_next, q_next, sigma = onestep_reachability(ps.contiguous(), self.ssm, actions, t(pr.l_mu), t(pr.l_sigma), qs,
+                                                     k_fb=t(pr.k_fb), a=t(pr.a), b=t(pr.b), verbose=0,
+                                                     c_safety=pr.c_safety)
+        if pr.objective == _lib.SE_OBJ_NEG_VARIANCE:
+            cost = -torch.sum(sigma, dim=1)
+        elif pr.objective == _lib.SE_OBJ_ABS_STATE1:
+            cost = torch.abs(pr.objective_theta - p_next[:, 1])
+        else:
+            cost = -p_next[:, -1]
+        return self._pq.flatten(p_next, q_next), cost
+
+
+def fold_constraints(problem: SafeProblem, constraints: Sequence[Constraint]) -> SafeProblem:
+    """Translate the reference's constraint objects into the device-side problem description."""
+    kw = {}
+    for c in constraints:
+        if isinstance(c, ActionConstraint):
+            kw.update(act_a=c._self_region._A.cpu().numpy(), act_b=c._self_region._b.cpu().numpy(),
+                      act_penalty=float(c._penalty))
+        elif isinstance(c, EllipsoidTerminalConstraint):
+            kw.update(h_mat=c._polytope_a.cpu().numpy(), h_vec=c._polytope_b.cpu().numpy().reshape(-1),
+                      all_states_constraint=False)
+        elif isinstance(c, EllipsoidStateConstraint):
+            kw.update(h_mat=c._polytope_a.cpu().numpy(), h_vec=c._polytope_b.cpu().numpy().reshape(-1),
+                      all_states_constraint=c.all_states)
+        else:
+            raise TypeError(f'{type(c).__name__} cannot be evaluated inside the fused CEM kernels; supported: '
+                            f'ActionConstraint, EllipsoidTerminalConstraint, EllipsoidStateConstraint')
+    return problem.with_(**kw)
+
+
+def dlqr(a, b, q, r):
+    """Infinite-horizon discrete LQR gain, u = -K x (safe_exploration/utils.py:23-38)."""
+    a, b, q, r = (np.atleast_2d(np.asarray(m, dtype=np.float64)) for m in (a, b, q, r))
+    x = scipy.linalg.solve_discrete_are(a, b, q, r)
+    k = np.linalg.solve(b.T @ x @ b + r, b.T @ x @ a)
+    return k, x, np.linalg.eigvals(a - b @ k)
+
+
+class LqrFeedbackController:
+    """safempc_simple.py:1105-1129: cached k_fb = -K_lqr."""
+
+    def __init__(self, wx_feedback_cost, wu_feedback_cost, n_s: int, n_u: int, linearized_model_a, linearized_model_b,
+                 conf=None):
+        self._args = (linearized_model_a, linearized_model_b, wx_feedback_cost, wu_feedback_cost)
+
+    @lru_cache()
+    def get_control_matrix(self):
+        k_lqr, _, _ = dlqr(*self._args)
+        return -k_lqr
+
+    def get_control_matrix_pytorch(self):
+        return torch.as_tensor(self.get_control_matrix())
+
+
+class B200CemSafeMPC(SafeMPC):
+    """Safe MPC on constrained CEM, evaluated on the B200.  Constructor arguments as CemSafeMPC (safempc_cem.py:162-200);
+    `env` needs n_s, n_u, l_mu, l_sigm, objective_cost_function (and optionally `objective_spec`), `conf` needs
+    mpc_time_horizon, cem_num_rollouts, cem_num_elites, cem_num_iterations, use_prior_model."""
+
+    def __init__(self, ssm: B200GpCemSSM, constraints: Sequence[Constraint], env, conf, opt_env, wx_feedback_cost,
+                 wu_feedback_cost, beta_safety: float, safe_policy: Callable[[ndarray], ndarray],
+                 lqr: Optional[LqrFeedbackController] = None, mpc: Optional[B200ConstrainedCemMpc] = None,
+                 verbose: bool = True) -> None:
+        super().__init__()
+        self._state_dimen = env.n_s
+        self._action_dimen = env.n_u
+        self._pq_flattener = PQFlattener(env.n_s)
+        self._ssm = ssm
+        self._mpc_time_horizon = conf.mpc_time_horizon
+        self._beta_safety = beta_safety
+        self._safe_policy = safe_policy
+        self._use_prior_model = conf.use_prior_model
+        self._verbose = verbose
+        a_lin, b_lin = opt_env['lin_model']
+        self.lin_model = opt_env['lin_model']
+        self._linearized_model_a = np.asarray(a_lin, dtype=np.float64).reshape(env.n_s, env.n_s)
+        self._linearized_model_b = np.asarray(b_lin, dtype=np.float64).reshape(env.n_s, env.n_u)
+        if lqr is None:
+            lqr = LqrFeedbackController(wx_feedback_cost, wu_feedback_cost, env.n_s, env.n_u, self._linearized_model_a,
+                                        self._linearized_model_b, conf=conf)
+        self._lqr = lqr
+        # safempc_cem.py:291-296: zeros (not identity) when the prior is disabled (quirk Q9)
+        a = self._linearized_model_a if self._use_prior_model else np.zeros_like(self._linearized_model_a)
+        b = self._linearized_model_b if self._use_prior_model else np.zeros_like(self._linearized_model_b)
+        objective, theta = self._objective_of(env)
+        k_fb = lqr.get_control_matrix_pytorch() if hasattr(lqr, 'get_control_matrix_pytorch') else lqr
+        problem = SafeProblem(env.n_s, env.n_u, env.l_mu, env.l_sigm, k_fb=k_fb, a=a, b=b, c_safety=beta_safety,
+                              objective=objective, objective_theta=theta)
+        self._dynamics = B200SafeDynamics(ssm, problem)
+        if mpc is None:
+            mpc = B200ConstrainedCemMpc(self._dynamics, constraints=constraints,
+                                        state_dimen=self._pq_flattener.get_flat_state_dimen(), action_dimen=env.n_u,
+                                        time_horizon=self._mpc_time_horizon, num_rollouts=conf.cem_num_rollouts,
+                                        num_elites=conf.cem_num_elites, num_iterations=conf.cem_num_iterations,
+                                        record=getattr(conf, 'cem_record', 'costs'))
+        self._mpc = mpc
+        self._last_mpc_actions = np.empty((0, self.action_dimen))
+        self._mpc_actions_executed = 0
+
+    @staticmethod
+    def _objective_of(env) -> Tuple[int, float]:
+        """safempc_cem.py:304-312: the env's objective if it has one, else -sum(variance).  Environments describe
+        theirs declaratively through `objective_spec = (kind, theta)` so it can run inside the kernel."""
+        spec = getattr(env, 'objective_spec', None)
+        if spec is None:
+            probe = env.objective_cost_function(torch.zeros((1, env.n_s), dtype=torch.float64)) \
+                if hasattr(env, 'objective_cost_function') else None
+            if probe is not None:
+                raise TypeError('env.objective_cost_function is an arbitrary Python function; give the environment an '
+                                '`objective_spec` = ("abs_state1", theta) | ("neg_last_state", 0) | None instead')
+            return _lib.SE_OBJ_NEG_VARIANCE, 0.0
+        kind, theta = spec
+        return {'neg_variance': _lib.SE_OBJ_NEG_VARIANCE, 'abs_state1': _lib.SE_OBJ_ABS_STATE1,
+                'neg_last_state': _lib.SE_OBJ_NEG_LAST_STATE}[kind], float(theta)
+
+    @property
+    def state_dimen(self) -> int:
+        return self._state_dimen
+
+    @property
+    def action_dimen(self) -> int:
+        return self._action_dimen
+
+    @property
+    def safety_trajectory_length(self) -> int:
+        return self._mpc_time_horizon
+
+    @property
+    def performance_trajectory_length(self) -> int:
+        return 0
+
+    @property
+    def x_train(self) -> ndarray:
+        x_train = self._ssm.x_train
+        if x_train is None:
+            return np.empty((0, self._state_dimen + self._action_dimen))
+        return x_train.detach().cpu().numpy()
+
+    def init_solver(self, cost_func=None):
+        pass
+
+    def get_action(self, state: ndarray) -> Tuple[ndarray, MpcResult]:
+        """safempc_cem.py:231-263."""
+        assert_shape(state, (self._state_dimen,))
+        state_batch = torch.tensor(state, dtype=self._ssm.dtype, device=self._ssm.device).unsqueeze(0)
+        mpc_actions, _ = self._mpc.get_actions(self._pq_flattener.flatten(state_batch, None))
+        mpc_actions = mpc_actions.detach().cpu().numpy() if mpc_actions is not None else mpc_actions
+        if mpc_actions is not None:
+            self._say('Found solution')
+            action = mpc_actions[0]
+            self._last_mpc_actions = mpc_actions
+            self._mpc_actions_executed = 1
+            result = MpcResult.FOUND_SOLUTION
+        elif self._mpc_actions_executed < self._last_mpc_actions.shape[0]:
+            self._say('Using existing solution')
+            action = self._last_mpc_actions[self._mpc_actions_executed]
+            self._mpc_actions_executed += 1
+            result = MpcResult.PREVIOUS_SOLUTION
+        else:
+            self._say('Using safe controller')
+            action = self._safe_policy(state)
+            result = MpcResult.SAFE_CONTROLLER
+        return action, result
+
+    def _say(self, msg: str) -> None:
+        if self._verbose:
+            print(msg)
+
+    def get_action_verbose(self, state: ndarray):
+        raise NotImplementedError
+
+    def update_model(self, x: ndarray, y: ndarray, opt_hyp=False, replace_old=True, reinitialize_solver=True) -> None:
+        """safempc_cem.py:314-327: the SSM learns the residual of the prior linear model."""
+        x_s = x[:, :self.state_dimen]
+        x_u = x[:, self.state_dimen:]
+        y_error = y - self.eval_prior(x_s, x_u) if self._use_prior_model else y
+        dev = self._ssm.device
+        self._ssm.update_model(torch.tensor(x, device=dev), torch.tensor(y_error, device=dev), opt_hyp, replace_old)
+
+    def information_gain(self) -> Union[ndarray, List[None]]:
+        return [None] * self.state_dimen
+
+    def ssm_predict(self, z: ndarray) -> Tuple[ndarray, ndarray]:
+        mean, sigma = self._ssm.predict_raw(torch.tensor(z, device=self._ssm.device))
+        return mean.detach().cpu().numpy(), sigma.detach().cpu().numpy()
+
+    def eval_prior(self, states: ndarray, actions: ndarray):
+        return np.dot(states, self._linearized_model_a.T) + np.dot(actions, self._linearized_model_b.T)
+
+    def collect_metrics(self) -> Dict[str, float]:
+        return self._ssm.collect_metrics()

@@ -1,0 +1,271 @@
+"""State-space models behind the reference's `CemSSM` interface (safe_exploration/ssm_cem/ssm_cem.py:11-131).
+
+`B200GpCemSSM` is the drop-in for `GpCemSSM` (safe_exploration/ssm_cem/gp_ssm_cem.py:17-133, rbf kernel): same five
+methods, same shapes, same error behaviour (`ValueError` on a shape mismatch); the posterior itself is evaluated by
+libsecem.so (csrc/gp_kernels.cuh).  PyTorch only owns device memory here and, at `update_model` time, factorises the
+training covariance (torch.linalg -> cuSOLVER), which is off the hot path.
+"""
+import ctypes as C
+import math
+from abc import ABC, abstractmethod
+from typing import Any, Dict, Optional, Tuple
+
+import torch
+from torch import Tensor
+
+from . import _lib
+
+
+def assert_shape(x, shape: tuple, ignore_if_none=False) -> None:
+    """safe_exploration/utils.py:640-648."""
+    if x is None:
+        if ignore_if_none:
+            return
+        raise ValueError(f'Wanted shape {shape}, got None')
+    if tuple(x.shape) != tuple(shape):
+        raise ValueError(f'Wanted shape {shape}, got {x.shape}')
+
+
+class CemSSM(ABC):
+    """Mirror of the reference ABC (ssm_cem.py:11-131): same attributes, same method contract."""
+
+    def __init__(self, state_dimen: int, action_dimen: int):
+        self.num_states = state_dimen
+        self.num_actions = action_dimen
+        self._x_train = None
+        self._y_train = None
+
+    @property
+    def x_train(self) -> Optional[Tensor]:
+        return self._x_train
+
+    @property
+    def y_train(self) -> Optional[Tensor]:
+        return self._y_train
+
+    @abstractmethod
+    def predict_with_jacobians(self, states: Tensor, actions: Tensor) -> Tuple[Tensor, Tensor, Tensor]:
+        """-> mean [N, n_s], variance [N, n_s], d mean / d (state, action) [N, n_s, n_s + n_u]."""
+
+    @abstractmethod
+    def predict_without_jacobians(self, states: Tensor, actions: Tensor) -> Tuple[Tensor, Tensor]:
+        """-> mean [N, n_s], variance [N, n_s]."""
+
+    @abstractmethod
+    def predict_raw(self, z: Tensor) -> Tuple[Tensor, Tensor]:
+        """Predict from stacked [state | action] inputs."""
+
+    def update_model(self, train_x: Tensor, train_y: Tensor, opt_hyp=False, replace_old=False) -> None:
+        """ssm_cem.py:72-99: replace or append the training data, rebuild the model, optionally train."""
+        N = train_x.size(0)
+        assert_shape(train_x, (N, self.num_states + self.num_actions))
+        assert_shape(train_y, (N, self.num_states))
+        if replace_old or self._x_train is None or self._y_train is None:
+            x_new, y_new = train_x, train_y
+        else:
+            x_new = torch.cat((self._x_train, train_x), dim=0)
+            y_new = torch.cat((self._y_train, train_y), dim=0)
+        self._x_train = x_new
+        self._y_train = y_new
+        self._update_model(x_new, y_new)
+        if self.parametric or opt_hyp:
+            self._train_model(x_new, y_new)
+
+    @abstractmethod
+    def _update_model(self, x_train: Tensor, y_train: Tensor) -> None:
+        pass
+
+    @abstractmethod
+    def _train_model(self, x_train: Tensor, y_train: Tensor) -> None:
+        pass
+
+    def _join_states_actions(self, states: Tensor, actions: Tensor) -> Tensor:
+        N = states.size(0)
+        assert_shape(states, (N, self.num_states))
+        assert_shape(actions, (N, self.num_actions))
+        return torch.cat((states, actions), dim=1)
+
+    @abstractmethod
+    def collect_metrics(self) -> Dict[str, Any]:
+        pass
+
+    @property
+    @abstractmethod
+    def parametric(self) -> bool:
+        pass
+
+
+def _rbf_ard(xa: Tensor, xb: Tensor, lengthscale: Tensor, outputscale: Tensor) -> Tensor:
+    """[n_s, A, B] covariance of ScaleKernel(RBFKernel(ard)) (gp_ssm_cem.py:45-57); fp64, used for the factors."""
+    sa = xa.unsqueeze(0) / lengthscale.unsqueeze(1)  # [n_s, A, d]
+    sb = xb.unsqueeze(0) / lengthscale.unsqueeze(1)
+    d2 = None
+    for dd in range(xa.size(1)):  # explicit differences (no a^2 + b^2 - 2ab cancellation), O(n_s A B) memory
+        diff = sa[:, :, dd].unsqueeze(2) - sb[:, :, dd].unsqueeze(1)
+        d2 = diff * diff if d2 is None else d2.addcmul_(diff, diff)
+    return outputscale.view(-1, 1, 1) * torch.exp(-0.5 * d2)
+
+
+class B200GpCemSSM(CemSSM):
+    """Exact-GP state-space model evaluated by hand-written sm_100a kernels.
+
+    Hyper-parameters cross the boundary as materialised values (lengthscale [n_s, d], outputscale [n_s],
+    noise [n_s]), never as GPyTorch raw parameters.  Defaults are GPyTorch's untrained values softplus(0) = ln 2,
+    which is what the reference's tests run with (test_gp_reachability_pytorch.py:96-97).
+
+    :param conf: optional config object; `exact_gp_training_iterations` and `exact_gp_kernel` are read if present
+                 (only 'rbf' is accelerated; the reference's 'linear' / 'nn' kernels stay on GPyTorch).
+    :param dtype: torch.float64 (reference precision, default) or torch.float32
+    """
+
+    def __init__(self, conf, state_dimen: int, action_dimen: int, lengthscale=None, outputscale=None, noise=None,
+                 dtype: torch.dtype = torch.float64, device: Optional[str] = None, gemm_impl: int = _lib.SE_GEMM_AUTO,
+                 workspace_bytes: Optional[int] = None):
+        super().__init__(state_dimen, action_dimen)
+        kernel = getattr(conf, 'exact_gp_kernel', 'rbf') if conf is not None else 'rbf'
+        if kernel != 'rbf':
+            raise ValueError(f'Unknown kernel {kernel}: the B200 path implements the rbf (ARD) kernel')
+        self._training_iterations = getattr(conf, 'exact_gp_training_iterations', 1000) if conf is not None else 1000
+        self._lib = _lib.load()
+        self.dtype = dtype
+        self._code = _lib.dtype_code(dtype)
+        self.device = torch.device(device if device is not None else 'cuda:0')
+        d = state_dimen + action_dimen
+        ln2 = math.log(2.0)
+        f64 = dict(dtype=torch.float64, device='cpu')
+        self.lengthscale = torch.full((state_dimen, d), ln2, **f64) if lengthscale is None else \
+            torch.as_tensor(lengthscale, **f64).reshape(state_dimen, d).clone()
+        self.outputscale = torch.full((state_dimen,), ln2, **f64) if outputscale is None else \
+            torch.as_tensor(outputscale, **f64).reshape(state_dimen).clone()
+        self.noise = torch.full((state_dimen,), ln2, **f64) if noise is None else \
+            torch.as_tensor(noise, **f64).reshape(state_dimen).clone()
+        self._gemm_impl = gemm_impl
+        self._workspace_bytes = workspace_bytes
+        self._handle = C.c_void_p(None)
+        self._last_training_losses = []
+
+    # ---- handle management -------------------------------------------------------------------------------------
+    @property
+    def handle(self) -> C.c_void_p:
+        if not self._handle:
+            raise _lib.SecemError('the model holds no training data yet: call update_model first')
+        return self._handle
+
+    def _destroy(self):
+        if getattr(self, '_handle', None):
+            self._lib.se_gp_destroy(self._handle)
+            self._handle = C.c_void_p(None)
+
+    def __del__(self):
+        try:
+            self._destroy()
+        except Exception:
+            pass
+
+    def set_gemm_impl(self, impl: int) -> None:
+        self._gemm_impl = impl
+        if self._handle:
+            _lib.check(self._lib.se_gp_set_gemm_impl(self._handle, impl))
+
+    # ---- CemSSM ------------------------------------------------------------------------------------------------
+    def _update_model(self, x_train: Tensor, y_train: Tensor) -> None:
+        """gp_ssm_cem.py:96-101.  Builds alpha = (K + noise I)^-1 y and L^-1 in fp64 and uploads them."""
+        x = x_train.detach().to(device=self.device, dtype=torch.float64)
+        y = y_train.detach().to(device=self.device, dtype=torch.float64)
+        n = x.size(0)
+        ls = self.lengthscale.to(self.device)
+        k = _rbf_ard(x, x, ls, self.outputscale.to(self.device))
+        k.diagonal(dim1=1, dim2=2).add_(self.noise.to(self.device).view(-1, 1))
+        chol = torch.linalg.cholesky(k)
+        del k
+        alpha = torch.cholesky_solve(y.t().unsqueeze(-1), chol).squeeze(-1)
+        eye = torch.eye(n, dtype=torch.float64, device=self.device).expand(self.num_states, -1, -1)
+        linv = torch.linalg.solve_triangular(chol, eye, upper=False).tril_()
+        del chol
+        xs = x.to(self.dtype).contiguous()
+        al = alpha.to(self.dtype).contiguous()
+        li = linv.to(self.dtype).contiguous()
+        _, p_ls = _lib.host_doubles(self.lengthscale.numpy())
+        _, p_os = _lib.host_doubles(self.outputscale.numpy())
+        _, p_nz = _lib.host_doubles(self.noise.numpy())
+        self._destroy()
+        handle = C.c_void_p(None)
+        with torch.cuda.device(self.device):
+            _lib.check(self._lib.se_gp_create(C.byref(handle), self.num_states, self.num_actions, n, self._code,
+                                              _lib.ptr(xs), _lib.ptr(al), _lib.ptr(li), p_ls, p_os, p_nz,
+                                              _lib.stream_ptr(self.device)))
+            torch.cuda.current_stream(self.device).synchronize()  # xs / al / li may be freed after this
+        self._handle = handle
+        if self._gemm_impl != _lib.SE_GEMM_AUTO:
+            _lib.check(self._lib.se_gp_set_gemm_impl(handle, self._gemm_impl))
+        if self._workspace_bytes is not None:
+            _lib.check(self._lib.se_gp_set_workspace_limit(handle, int(self._workspace_bytes)))
+
+    def _train_model(self, x_train: Tensor, y_train: Tensor) -> None:
+        """gp_ssm_cem.py:103-129: Adam(lr=0.01) on the exact marginal log likelihood, softplus-parametrised like
+        GPyTorch.  Host-side torch autograd (not part of the accelerated path yet)."""
+        x = x_train.detach().to(device=self.device, dtype=torch.float64)
+        y = y_train.detach().to(device=self.device, dtype=torch.float64).t()
+        inv_softplus = lambda v: torch.log(torch.expm1(v))
+        raw = [inv_softplus(t.to(self.device)).requires_grad_(True)
+               for t in (self.lengthscale, self.outputscale, self.noise)]
+        opt = torch.optim.Adam(raw, lr=0.01)
+        n = x.size(0)
+        losses = []
+        for _ in range(self._training_iterations):
+            opt.zero_grad()
+            ls, os_, nz = (torch.nn.functional.softplus(r) for r in raw)
+            k = _rbf_ard(x, x, ls, os_) + torch.diag_embed(nz.view(-1, 1).expand(-1, n))
+            chol = torch.linalg.cholesky(k)
+            a = torch.cholesky_solve(y.unsqueeze(-1), chol).squeeze(-1)
+            mll = -0.5 * (y * a).sum(-1) - chol.diagonal(dim1=1, dim2=2).log().sum(-1) - 0.5 * n * math.log(2 * math.pi)
+            loss = -(mll / n).sum()  # GPyTorch's ExactMarginalLogLikelihood divides by the number of data points
+            loss.backward()
+            losses.append(loss.item())
+            opt.step()
+        self._last_training_losses = losses
+        with torch.no_grad():
+            self.lengthscale, self.outputscale, self.noise = (torch.nn.functional.softplus(r).cpu() for r in raw)
+        self._update_model(x_train, y_train)
+
+    def _prep(self, t: Tensor, name: str) -> Tensor:
+        _lib.require_cuda(t, name)
+        return t.detach().to(self.dtype).contiguous()
+
+    def _predict_z(self, z: Tensor, want_jac: bool):
+        N = z.size(0)
+        z = self._prep(z, 'z')
+        mean = torch.empty((N, self.num_states), dtype=self.dtype, device=z.device)
+        var = torch.empty_like(mean)
+        jac = torch.empty((N, self.num_states, self.num_states + self.num_actions), dtype=self.dtype,
+                          device=z.device) if want_jac else None
+        if N > 0:
+            with torch.cuda.device(z.device):
+                _lib.check(self._lib.se_gp_predict(self.handle, _lib.ptr(z), N, _lib.ptr(mean), _lib.ptr(var),
+                                                   _lib.ptr(jac), _lib.stream_ptr(z.device)))
+        return mean, var, jac
+
+    def predict_with_jacobians(self, states: Tensor, actions: Tensor) -> Tuple[Tensor, Tensor, Tensor]:
+        """gp_ssm_cem.py:59-73 (one fused pass instead of two forwards + one backward)."""
+        z = self._join_states_actions(states, actions)
+        return self._predict_z(z, True)
+
+    def predict_without_jacobians(self, states: Tensor, actions: Tensor) -> Tuple[Tensor, Tensor]:
+        """gp_ssm_cem.py:75-77."""
+        z = self._join_states_actions(states, actions)
+        mean, var, _ = self._predict_z(z, False)
+        return mean, var
+
+    def predict_raw(self, z: Tensor) -> Tuple[Tensor, Tensor]:
+        """gp_ssm_cem.py:90-94: [n_s, N] mean and variance (the GPyTorch batch layout)."""
+        N = z.size(0)
+        assert_shape(z, (N, self.num_states + self.num_actions))
+        mean, var, _ = self._predict_z(z, False)
+        return mean.t(), var.t()
+
+    def collect_metrics(self) -> Dict[str, Any]:
+        return {'losses': self._last_training_losses}
+
+    @property
+    def parametric(self) -> bool:
+        return False

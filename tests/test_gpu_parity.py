@@ -1,0 +1,492 @@
+"""GPU parity tests: the CUDA path (through the C ABI) against the oracle and the reference-generated golden vectors.
+
+Tolerances (BASELINE.json north_star): float64 -- 1e-9 relative on GP mean / variance / Jacobian and on ellipsoid
+centres / shapes (the reference computes in float64; "tighter in fp64"); float32 -- 1e-4 relative, where "relative"
+for the GP variance is relative to the prior scale outputscale + noise (the variance is a difference of two numbers of
+that size, so its absolute fp32 error is set by that scale); integer work (elite indices, constraint costs, picks) --
+bit-exact.
+"""
+import numpy as np
+import pytest
+import torch
+
+import safe_exploration_b200 as se
+from oracle import oracle
+from safe_exploration_b200 import _lib, workloads
+
+pytestmark = pytest.mark.gpu
+DEV = 'cuda:0'
+T = lambda x: torch.as_tensor(np.asarray(x, dtype=np.float64))
+G = lambda x, dt=torch.float64: torch.as_tensor(np.asarray(x, dtype=np.float64)).to(device=DEV, dtype=dt)
+RTOL64 = 1e-9
+RTOL32 = 1e-4
+IMPLS = [_lib.SE_GEMM_SIMT, _lib.SE_GEMM_MMA]
+
+
+def rel_err(a, b, scale=None):
+    a, b = np.asarray(a, dtype=np.float64), np.asarray(b, dtype=np.float64)
+    den = np.maximum(np.abs(b), 0 if scale is None else scale)
+    den = np.where(den == 0, 1.0, den)
+    return float(np.max(np.abs(a - b) / den)) if a.size else 0.0
+
+
+def make_gp(x, y, ls, os_, nz, dtype=torch.float64, impl=_lib.SE_GEMM_AUTO, workspace=None):
+    gp = se.B200GpCemSSM(None, y.shape[1], x.shape[1] - y.shape[1], ls, os_, nz, dtype=dtype, device=DEV,
+                         gemm_impl=impl, workspace_bytes=workspace)
+    gp.update_model(G(x), G(y), replace_old=True)
+    return gp
+
+
+def make_oracle_gp(x, y, ls, os_, nz):
+    gp = oracle.OracleGpCemSSM(y.shape[1], x.shape[1] - y.shape[1], ls, os_, nz)
+    gp.update_model(T(x), T(y), replace_old=True)
+    return gp
+
+
+# ---- GP posterior ------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize('impl', IMPLS)
+@pytest.mark.parametrize('tag', ['untrained', 'trained'])
+def test_gp_predict_matches_golden_fp64(golden_onestep, tag, impl):
+    g = golden_onestep
+    gp = make_gp(g['x_train'], g['y_train'], g[f'{tag}_lengthscale'], g[f'{tag}_outputscale'], g[f'{tag}_noise'],
+                 impl=impl)
+    mean, var, jac = gp.predict_with_jacobians(G(g['p']), G(g['u']))
+    assert mean.shape == (34, 2) and var.shape == (34, 2) and jac.shape == (34, 2, 3)
+    assert rel_err(mean.cpu(), g[f'{tag}_mean'], 1e-3 * np.abs(g[f'{tag}_mean']).max()) < RTOL64
+    assert rel_err(var.cpu(), g[f'{tag}_var']) < RTOL64
+    assert rel_err(jac.cpu(), g[f'{tag}_jac'], 1e-3 * np.abs(g[f'{tag}_jac']).max()) < RTOL64
+    m2, v2 = gp.predict_without_jacobians(G(g['p']), G(g['u']))
+    assert torch.equal(m2, mean) and torch.equal(v2, var)
+    mr, vr = gp.predict_raw(torch.cat((G(g['p']), G(g['u'])), dim=1))  # [n_s, N] layout (gp_ssm_cem.py:90-94)
+    assert mr.shape == (2, 34) and torch.equal(mr.t(), mean) and torch.equal(vr.t(), var)
+
+
+@pytest.mark.parametrize('dtype,impl', [(torch.float64, _lib.SE_GEMM_SIMT), (torch.float64, _lib.SE_GEMM_MMA),
+                                        (torch.float32, _lib.SE_GEMM_SIMT)])
+@pytest.mark.parametrize('n_s,n_u,n,N', [(2, 1, 300, 1000), (4, 1, 700, 513), (6, 2, 130, 257), (1, 3, 64, 5),
+                                         (3, 2, 129, 128)])
+def test_gp_predict_matches_oracle_random(dtype, impl, n_s, n_u, n, N):
+    """Ragged sizes: n and N not multiples of the 128 tile; every compiled (n_s, n_u) family."""
+    rng = np.random.default_rng(n + N)
+    d = n_s + n_u
+    x = rng.uniform(-1, 1, (n, d))
+    y = 0.1 * np.sin(x @ rng.standard_normal((d, n_s)))
+    ls = rng.uniform(0.6, 1.4, (n_s, d))
+    os_ = rng.uniform(0.02, 0.08, n_s)
+    nz = rng.uniform(1e-3, 3e-3, n_s)
+    z = rng.uniform(-1.2, 1.2, (N, d))
+    gp = make_gp(x, y, ls, os_, nz, dtype=dtype, impl=impl)
+    ref = make_oracle_gp(x, y, ls, os_, nz)
+    mean, var, jac = gp.predict_with_jacobians(G(z[:, :n_s], dtype), G(z[:, n_s:], dtype))
+    m0, v0, j0 = ref.predict_with_jacobians(T(z[:, :n_s]), T(z[:, n_s:]))
+    rtol = RTOL64 if dtype == torch.float64 else RTOL32
+    prior = (os_ + nz)[None, :]
+    assert rel_err(mean.cpu(), m0, np.abs(m0.numpy()).max()) < rtol
+    assert rel_err(var.cpu(), v0, prior if dtype == torch.float32 else None) < rtol
+    assert rel_err(jac.cpu(), j0, np.abs(j0.numpy()).max()) < rtol
+
+
+def test_gp_predict_chunked_workspace_is_identical():
+    """A tiny workspace forces the candidate batch through many K* chunks; results must not change."""
+    rng = np.random.default_rng(3)
+    x, y = rng.uniform(-1, 1, (200, 3)), rng.standard_normal((200, 2)) * 0.05
+    ls, os_, nz = np.full((2, 3), 0.8), np.full(2, 0.05), np.full(2, 1e-3)
+    z = G(rng.uniform(-1, 1, (1000, 3)))
+    big = make_gp(x, y, ls, os_, nz)
+    small = make_gp(x, y, ls, os_, nz, workspace=2 * 256 * 256 * 8)  # 256 rows per chunk
+    a = big.predict_with_jacobians(z[:, :2].contiguous(), z[:, 2:].contiguous())
+    b = small.predict_with_jacobians(z[:, :2].contiguous(), z[:, 2:].contiguous())
+    for s, t in zip(a, b):
+        assert torch.equal(s, t)
+
+
+def test_gp_empty_batch_and_shape_errors(golden_onestep):
+    g = golden_onestep
+    gp = make_gp(g['x_train'], g['y_train'], g['trained_lengthscale'], g['trained_outputscale'], g['trained_noise'])
+    mean, var = gp.predict_without_jacobians(torch.empty((0, 2), device=DEV), torch.empty((0, 1), device=DEV))
+    assert mean.shape == (0, 2) and var.shape == (0, 2)
+    with pytest.raises(ValueError):
+        gp.predict_without_jacobians(torch.zeros((3, 3), device=DEV), torch.zeros((3, 1), device=DEV))
+    # update_model(replace_old=False) appends (ssm_cem.py:86-91)
+    gp.update_model(G(g['x_train'][:5]), G(g['y_train'][:5]))
+    assert gp.x_train.shape == (80, 3) and gp.y_train.shape == (80, 2)
+
+
+# ---- one-step reachability against the verbatim reference ---------------------------------------------------------
+@pytest.mark.parametrize('impl', IMPLS)
+@pytest.mark.parametrize('tag', ['untrained', 'trained'])
+@pytest.mark.parametrize('lin', ['lin', 'nolin'])
+@pytest.mark.parametrize('branch', ['ell', 'pt'])
+def test_onestep_matches_reference_golden(golden_onestep, tag, lin, branch, impl):
+    g = golden_onestep
+    gp = make_gp(g['x_train'], g['y_train'], g[f'{tag}_lengthscale'], g[f'{tag}_outputscale'], g[f'{tag}_noise'],
+                 impl=impl)
+    a, b = (G(g['a']), G(g['b'])) if lin == 'lin' else (None, None)
+    q = G(g['q']) if branch == 'ell' else None
+    p1, q1, sig = se.onestep_reachability(G(g['p']), gp, G(g['u']), G(g['l_mu']), G(g['l_sigma']), q, G(g['k_fb']),
+                                          float(g['c_safety']), verbose=0, a=a, b=b)
+    key = f'{tag}_{lin}_{branch}'
+    assert rel_err(p1.cpu(), g[f'{key}_p1'], 1e-3) < RTOL64
+    assert rel_err(q1.cpu(), g[f'{key}_q1'], 1e-3 * np.abs(g[f'{key}_q1']).max()) < RTOL64
+    assert rel_err(sig.cpu(), g[f'{key}_sigma']) < RTOL64
+
+
+def test_onestep_fp32_within_stated_tolerance(golden_onestep):
+    g = golden_onestep
+    gp = make_gp(g['x_train'], g['y_train'], g['trained_lengthscale'], g['trained_outputscale'], g['trained_noise'],
+                 dtype=torch.float32)
+    f = torch.float32
+    p1, q1, sig = se.onestep_reachability(G(g['p'], f), gp, G(g['u'], f), G(g['l_mu'], f), G(g['l_sigma'], f),
+                                          G(g['q'], f), G(g['k_fb'], f), float(g['c_safety']), verbose=0,
+                                          a=G(g['a'], f), b=G(g['b'], f))
+    assert p1.dtype == torch.float32
+    assert rel_err(p1.cpu(), g['trained_lin_ell_p1'], 1e-2) < RTOL32
+    assert rel_err(q1.cpu(), g['trained_lin_ell_q1'], np.abs(g['trained_lin_ell_q1']).max()) < RTOL32
+    prior = (g['trained_outputscale'] + g['trained_noise'])[None, :]
+    assert rel_err(sig.cpu(), g['trained_lin_ell_sigma'], prior) < RTOL32
+
+
+def test_onestep_shape_errors(golden_onestep):
+    g = golden_onestep
+    gp = make_gp(g['x_train'], g['y_train'], g['trained_lengthscale'], g['trained_outputscale'], g['trained_noise'])
+    with pytest.raises(ValueError):  # assert_shape, gp_reachability_pytorch.py:49-56
+        se.onestep_reachability(G(g['p']), gp, G(g['u'][:3]), G(g['l_mu']), G(g['l_sigma']))
+    with pytest.raises(ValueError):
+        se.onestep_reachability(G(g['p']), gp, G(g['u']), G(g['l_mu']), G(g['l_sigma']), G(g['q'][:, :1]))
+
+
+@pytest.mark.parametrize('n_s', [3, 4, 5, 6])
+def test_onestep_higher_dimensions_match_oracle(n_s):
+    """n_s >= 3 exercises the Jacobi eigenvalue path for lambda_max(q B)."""
+    rng = np.random.default_rng(40 + n_s)
+    n_u, n, N = 2 if n_s == 6 else 1, 90, 200
+    d = n_s + n_u
+    x = rng.uniform(-1, 1, (n, d))
+    y = 0.05 * np.cos(x @ rng.standard_normal((d, n_s)))
+    ls, os_, nz = rng.uniform(0.7, 1.3, (n_s, d)), rng.uniform(0.01, 0.05, n_s), np.full(n_s, 1e-4)
+    gp, ref = make_gp(x, y, ls, os_, nz), make_oracle_gp(x, y, ls, os_, nz)
+    p, u = 0.3 * rng.standard_normal((N, n_s)), rng.uniform(-1, 1, (N, n_u))
+    m = rng.standard_normal((N, n_s, n_s))
+    q = 0.02 * (m @ m.transpose(0, 2, 1) / n_s + 0.1 * np.eye(n_s))
+    a = np.eye(n_s) + 0.05 * rng.standard_normal((n_s, n_s))
+    b, k_fb = 0.1 * rng.standard_normal((n_s, n_u)), rng.uniform(-1, 0, (n_u, n_s))
+    l_mu, l_sigma = np.full(n_s, 0.05), np.full(n_s, 0.03)
+    p1, q1, sig = se.onestep_reachability(G(p), gp, G(u), G(l_mu), G(l_sigma), G(q), G(k_fb), 2.0, 0, G(a), G(b))
+    p0, q0, s0 = oracle.onestep_reachability(T(p), ref, T(u), T(l_mu), T(l_sigma), T(q), T(k_fb), 2.0, T(a), T(b))
+    assert rel_err(p1.cpu(), p0, 1e-3) < RTOL64
+    assert rel_err(q1.cpu(), q0, 1e-3 * float(q0.abs().max())) < RTOL64
+    assert rel_err(sig.cpu(), s0) < RTOL64
+
+
+def test_remainder_bound_with_nonsymmetric_q_matches_reference(golden_algebra, golden_onestep):
+    """test_utils.py:35-59 through the kernel: with l_mu = 0-free constants the q_1 of one step exposes r^2; here the
+    closed-form 2x2 eigenvalue path is checked on the reference's (non-symmetric) q via a crafted step."""
+    g, go = golden_algebra, golden_onestep
+    gp = make_gp(go['x_train'], go['y_train'], go['trained_lengthscale'], go['trained_outputscale'],
+                 go['trained_noise'])
+    ref = make_oracle_gp(go['x_train'], go['y_train'], go['trained_lengthscale'], go['trained_outputscale'],
+                         go['trained_noise'])
+    for i in range(2):
+        q = g['rem_q'][i:i + 1]
+        k_fb = g['rem_k_fb'][i][:1]  # n_u = 1: first row of the test's gain
+        p, u = np.zeros((1, 2)), np.zeros((1, 1))
+        args = (g['rem_l_mu'], g['rem_l_sigma'])
+        p1, q1, _ = se.onestep_reachability(G(p), gp, G(u), G(args[0]), G(args[1]), G(q), G(k_fb), 1.5, 0)
+        p0, q0, _ = oracle.onestep_reachability(T(p), ref, T(u), T(args[0]), T(args[1]), T(q), T(k_fb), 1.5)
+        assert rel_err(q1.cpu(), q0, 1e-3 * float(q0.abs().max())) < RTOL64
+
+
+# ---- multi-step -----------------------------------------------------------------------------------------------------
+def test_multistep_matches_reference_numpy_golden(golden_multistep):
+    g = golden_multistep
+    gp = make_gp(g['x_train'], g['y_train'], g['lengthscale'], g['outputscale'], g['noise'])
+    pT, qT, p_all, q_all, s_all = se.multistep_reachability(G(g['p0']), gp, G(g['k_fb']), G(g['k_ff']), g['l_mu'],
+                                                            g['l_sigma'], None, float(g['c_safety']), g['a'], g['b'])
+    assert rel_err(p_all.cpu(), g['p_all'], 1e-3) < RTOL64
+    assert rel_err(q_all.cpu(), g['q_all'], 1e-3 * np.abs(g['q_all']).max()) < RTOL64
+    assert torch.equal(pT, p_all[:, -1]) and torch.equal(qT, q_all[:, -1])
+
+
+def test_multistep_equals_repeated_onestep():
+    w = workloads.pendulum_workload(n_train=150, num_rollouts=64, time_horizon=4)
+    gp = make_gp(w.x_train, w.y_train, w.lengthscale, w.outputscale, w.noise)
+    rng = np.random.default_rng(0)
+    N, Tn = 300, 4
+    p0, u = G(0.05 * rng.standard_normal((N, 2))), G(rng.uniform(-0.5, 0.5, (N, Tn, 1)))
+    pT, qT, p_all, q_all, s_all = se.multistep_reachability(p0, gp, G(w.k_fb), u, w.l_mu, w.l_sigma, None,
+                                                            w.beta_safety, w.a, w.b)
+    p, q = p0, None
+    for t in range(Tn):
+        p, q, s = se.onestep_reachability(p, gp, u[:, t].contiguous(), G(w.l_mu), G(w.l_sigma), q, G(w.k_fb),
+                                          w.beta_safety, 0, G(w.a), G(w.b))
+        assert torch.equal(p, p_all[:, t]) and torch.equal(q, q_all[:, t]) and torch.equal(s, s_all[:, t])
+    assert torch.equal(pT, p) and torch.equal(qT, q)
+
+
+# ---- polytope checks ------------------------------------------------------------------------------------------------
+def test_safety_distance_matches_reference_golden(golden_algebra):
+    g = golden_algebra
+    d = se.lin_ellipsoid_safety_distance(G(g['sd_p']), G(g['sd_q']), G(g['sd_h_mat']), G(g['sd_h_vec']))
+    assert d.shape == (5, 4) and rel_err(d.cpu(), g['sd_d'], 1e-6) < 1e-12
+    inside = se.is_ellipsoid_inside_polytope(G(g['sd_p']), G(g['sd_q']), G(g['sd_h_mat']), G(g['sd_h_vec']))
+    assert inside.dtype == torch.bool and np.array_equal(inside.cpu().numpy(), g['sd_inside'])
+    assert bool(inside[3]) and not bool(inside[0]) and not bool(inside[4])  # test_gp_reachability_pytorch.py:183-219
+    assert se.is_ellipsoid_inside_polytope(torch.empty((0, 2), device=DEV), torch.empty((0, 2, 2), device=DEV),
+                                           G(g['sd_h_mat']), G(g['sd_h_vec'])).shape == (0,)
+
+
+# ---- CEM: integer work is bit-exact -----------------------------------------------------------------------------------
+@pytest.mark.parametrize('dtype', [torch.float64, torch.float32])
+@pytest.mark.parametrize('N,E,ties', [(4, 2, False), (96, 12, True), (5000, 64, True), (65536, 1024, True),
+                                      (1000, 1000, True), (777, 1, False)])
+def test_select_elites_bit_exact_against_oracle(N, E, ties, dtype):
+    rng = np.random.default_rng(N + E)
+    Tn, n_u = 3, 2
+    obj = rng.standard_normal(N)
+    if ties:
+        obj = np.round(obj, 1)  # plenty of equal objectives
+    for frac_feasible in (0.0, 0.3, 1.0):
+        cc = rng.choice([3., 6., 10., 13., 16.], size=N)
+        cc[rng.random(N) < frac_feasible] = 0.0
+        act = rng.standard_normal((N, Tn, n_u))
+        obj_t, cc_t, act_t = G(obj, dtype), G(cc, dtype), G(act, dtype)
+        ids, mean, std = se.select_elites_refit(obj_t, cc_t, act_t, E)
+        ref_ids = oracle.select_elites(obj_t.cpu().double(), cc_t.cpu().double(), E)
+        assert np.array_equal(ids.cpu().numpy().astype(np.int64), ref_ids.numpy()), (N, E, frac_feasible)
+        m0, s0 = oracle.refit(act_t.cpu().double(), ref_ids)
+        tol = 1e-12 if dtype == torch.float64 else 1e-6
+        assert np.allclose(mean.cpu().double().numpy(), m0.numpy(), rtol=tol, atol=tol)
+        if E > 1:
+            assert np.allclose(std.cpu().double().numpy(), s0.numpy(), rtol=tol, atol=tol)
+        else:
+            assert torch.isnan(std).all()  # torch.std of one sample (quirk Q5)
+
+
+def test_select_elites_reference_known_answers():
+    """constrained_cem_mpc_test.py:230-301."""
+    ids, mean, std = se.select_elites_refit(G([1., 1., 1., 1.]), G([1., 5., 2., 9.]), G([[[1.]], [[5.]], [[3.]], [[7.]]]), 2)
+    assert ids.tolist() == [0, 2] and mean.item() == 2.0 and np.isclose(std.item(), np.std([1, 3], ddof=1))
+    ids, mean, std = se.select_elites_refit(G([1., .5, 2., 9.]), G([0., 3., 0., 0.]), G([[[10.]], [[4.]], [[2.]], [[8.]]]), 2)
+    assert ids.tolist() == [0, 2] and mean.item() == 6.0 and np.isclose(std.item(), np.std([10, 2], ddof=1))
+
+
+def test_device_sampler_matches_philox_restatement():
+    z = se.sample_noise(seed=0x1234567890ABCDEF, iteration=3, num_instances=2, num_rollouts=1000, first=200, count=300,
+                        T=5, n_u=1, device=DEV)
+    for inst in range(2):
+        ref = oracle.philox_normal_noise(0x1234567890ABCDEF, 3, inst * 1000 + 200, 300, 5, 1)
+        assert np.allclose(z[inst].cpu().numpy(), ref, rtol=1e-12, atol=1e-14)
+    big = se.sample_noise(7, 0, 1, 1 << 18, 0, 1 << 18, 4, 2, device=DEV)
+    assert abs(float(big.mean())) < 5e-3 and abs(float(big.std()) - 1.0) < 5e-3
+
+
+def _golden_mpc(g, dtype=torch.float64, impl=_lib.SE_GEMM_AUTO, **kw):
+    gp = make_gp(g['x_train'], g['y_train'], g['lengthscale'], g['outputscale'], g['noise_var'], dtype=dtype, impl=impl)
+    prob = se.SafeProblem(2, 1, g['l_mu'], g['l_sigma'], k_fb=g['k_fb'], a=g['a'], b=g['b'], c_safety=float(g['beta']))
+    cons = [se.ActionConstraint(se.TorchPolytope((g['act_a'], g['act_b']))),
+            se.EllipsoidStateConstraint(2, g['h_mat'], g['h_vec'])]
+    num_iter, n_roll, t_len, _ = g['eps'].shape
+    return se.B200ConstrainedCemMpc(se.B200SafeDynamics(gp, prob), cons, 6, 1, t_len, n_roll, int(g['num_elites']),
+                                    num_iter, **kw), gp
+
+
+@pytest.mark.parametrize('impl', IMPLS)
+def test_cem_get_actions_matches_verbatim_reference(golden_cem, impl):
+    """The verbatim CemSafeMPC + ConstrainedCemMpc run (tests/golden/make_golden.py) with RNG-fixed candidates."""
+    g = golden_cem
+    mpc, gp = _golden_mpc(g, impl=impl)
+    state = se.PQFlattener(2).flatten(G(g['p0']).unsqueeze(0), None)
+    actions, rollouts = mpc.get_actions(state, noise=G(g['eps']))
+    info = mpc.last_info
+    assert len(rollouts) == g['eps'].shape[0]
+    for i, r in enumerate(rollouts):
+        assert np.array_equal(r.constraint_costs.cpu().numpy(), g['constraint'][i])  # small integers: exact
+        assert rel_err(r.actions.cpu(), g['rollout_actions'][i], 1e-3) < RTOL64
+        assert rel_err(r.objective_costs.cpu(), g['objective'][i]) < RTOL64
+        assert rel_err(r.trajectories.cpu(), g['trajectories'][i], 1e-4) < 1e-8
+    assert np.array_equal(info['elite_ids'][:, 0].cpu().numpy(), g['elite_ids'])  # identical elites, every iteration
+    assert rel_err(info['means'][:, 0].cpu(), g['means'], 1e-3) < RTOL64
+    assert rel_err(info['stds'][:, 0].cpu(), g['stds'], 1e-3) < RTOL64
+    assert bool(g['found']) and actions is not None
+    assert int(info['best_id'][0]) == int(g['best_id'])  # first feasible rollout (quirk Q3)
+    assert rel_err(actions.cpu(), g['actions'], 1e-3) < RTOL64
+
+
+def test_cem_fp32_same_decisions_outside_margin(golden_cem):
+    """fp32: identical safe/unsafe decisions for every candidate whose safety distance is outside a 1e-4 margin band
+    (here: all of them), costs within tolerance."""
+    g = golden_cem
+    mpc, gp = _golden_mpc(g, dtype=torch.float32)
+    f = torch.float32
+    actions, rollouts = mpc.get_actions(se.PQFlattener(2).flatten(G(g['p0'], f).unsqueeze(0), None),
+                                        noise=G(g['eps'], f))
+    h_mat, h_vec = T(g['h_mat']), T(g['h_vec'])
+    r0 = rollouts[0]  # iteration 0: same candidates in both precisions
+    traj = T(g['trajectories'][0][:, -1])
+    d = oracle.lin_ellipsoid_safety_distance(traj[:, :2], traj[:, 2:].reshape(-1, 2, 2), h_mat, h_vec.reshape(-1, 1))
+    clear = (d.abs().min(dim=1)[0] > 1e-4).numpy()
+    assert clear.sum() >= 0.9 * len(clear)
+    assert np.array_equal(r0.constraint_costs.cpu().numpy()[clear], g['constraint'][0][clear])
+    assert rel_err(r0.objective_costs.cpu(), g['objective'][0]) < 5e-3  # sums of variances near the noise floor
+
+
+def test_cem_pick_best_and_all_states_switches(golden_cem):
+    g = golden_cem
+    mpc, gp = _golden_mpc(g, pick_best=True)
+    actions, rollouts = mpc.get_actions(se.PQFlattener(2).flatten(G(g['p0']).unsqueeze(0), None), noise=G(g['eps']))
+    last_obj, last_cc = T(g['objective'][-1]), T(g['constraint'][-1])
+    assert int(mpc.last_info['best_id'][0]) == oracle.pick_best_feasible(last_obj, last_cc)
+    # intended semantics of the state constraint: every ellipsoid is checked -> costs can only grow
+    gp2 = gp
+    prob = se.SafeProblem(2, 1, g['l_mu'], g['l_sigma'], k_fb=g['k_fb'], a=g['a'], b=g['b'], c_safety=float(g['beta']))
+    cons = [se.ActionConstraint(se.TorchPolytope((g['act_a'], g['act_b']))),
+            se.EllipsoidStateConstraint(2, g['h_mat'], g['h_vec'], all_states=True)]
+    num_iter, n_roll, t_len, _ = g['eps'].shape
+    mpc2 = se.B200ConstrainedCemMpc(se.B200SafeDynamics(gp2, prob), cons, 6, 1, t_len, n_roll, int(g['num_elites']),
+                                    num_iter)
+    _, r2 = mpc2.get_actions(se.PQFlattener(2).flatten(G(g['p0']).unsqueeze(0), None), noise=G(g['eps']))
+    assert (r2[0].constraint_costs.cpu().numpy() >= g['constraint'][0]).all()
+    traj = r2[0].trajectories.cpu()
+    ins = oracle.is_ellipsoid_inside_polytope(traj[:, 1:, :2].reshape(-1, 2), traj[:, 1:, 2:].reshape(-1, 2, 2),
+                                              T(g['h_mat']), T(g['h_vec']).reshape(-1, 1)).reshape(n_roll, t_len)
+    expect = 10.0 * (~ins).sum(dim=1).double() + oracle.action_constraint_costs(r2[0].actions.cpu(), T(g['act_a']),
+                                                                                 T(g['act_b']))
+    assert np.array_equal(r2[0].constraint_costs.cpu().numpy(), expect.numpy())
+
+
+def test_cem_none_when_nothing_feasible(golden_cem):
+    """constrained_cem_mpc_test.py:303-330: get_actions returns None if no rollout of the last iteration is feasible."""
+    g = golden_cem
+    gp = make_gp(g['x_train'], g['y_train'], g['lengthscale'], g['outputscale'], g['noise_var'])
+    prob = se.SafeProblem(2, 1, g['l_mu'], g['l_sigma'], k_fb=g['k_fb'], a=g['a'], b=g['b'], c_safety=float(g['beta']))
+    tiny = 1e-3 * g['h_vec']  # a polytope no ellipsoid fits into
+    cons = [se.ActionConstraint(se.TorchPolytope((g['act_a'], g['act_b']))),
+            se.EllipsoidTerminalConstraint(2, g['h_mat'], tiny)]
+    mpc = se.B200ConstrainedCemMpc(se.B200SafeDynamics(gp, prob), cons, 6, 1, 4, 96, 12, 3)
+    actions, rollouts = mpc.get_actions(se.PQFlattener(2).flatten(G(g['p0']).unsqueeze(0), None))
+    assert actions is None and len(rollouts) == 3 and int(mpc.last_info['best_id'][0]) == -1
+    assert (rollouts[-1].constraint_costs >= 10).all()
+
+
+def test_cem_on_device_rng_solve_matches_oracle_replay():
+    """On-device Philox candidates: replay the same noise through the oracle and compare the whole solve."""
+    w = workloads.pendulum_workload(n_train=100, num_rollouts=500, time_horizon=5, num_elites=20, num_iterations=4,
+                                    name='C1')
+    ssm, mpc = workloads.build_solver(w, record='full', seed=42)
+    res = mpc.solve(G(w.p0).unsqueeze(0), seed=42)
+    noise = np.stack([oracle.philox_normal_noise(42, i, 0, w.num_rollouts, w.time_horizon, 1)
+                      for i in range(w.num_iterations)])
+    ref_gp = make_oracle_gp(w.x_train, w.y_train, w.lengthscale, w.outputscale, w.noise)
+    prob = oracle.SafeCemProblem(ref_gp, w.l_mu, w.l_sigma, w.k_fb, w.a, w.b, w.beta_safety, w.h_mat, w.h_vec,
+                                 w.act_a, w.act_b)
+    ref = oracle.cem_solve(prob, T(w.p0), T(noise), w.num_elites)
+    assert np.array_equal(res['elite_ids'][:, 0].cpu().numpy(), ref['elite_ids'].numpy())
+    for i, r in enumerate(ref['rollouts']):
+        assert np.array_equal(res['constraint'][i, 0].cpu().numpy(), r.constraint_costs.numpy())
+        assert rel_err(res['objective'][i, 0].cpu(), r.objective_costs) < 1e-8
+        assert rel_err(res['trajectories'][i, 0].cpu(), r.trajectories, 1e-4) < 1e-8
+    assert rel_err(res['means'][:, 0].cpu(), ref['means'], 1e-3) < 1e-8
+    assert int(res['best_id'][0]) == ref['best_id']
+    # feasibility must actually be exercised by this workload
+    assert (ref['rollouts'][-1].constraint_costs == 0).sum() > 0
+
+
+def test_cem_batched_instances_equal_single_solves():
+    """C4-shaped: M independent problems in one call == M separate calls (same seeds -> same candidates)."""
+    w = workloads.pendulum_workload(n_train=64, num_rollouts=256, time_horizon=4, num_elites=16, num_iterations=3)
+    ssm, mpc = workloads.build_solver(w, record='costs', num_instances=3)
+    rng = np.random.default_rng(5)
+    p0 = G(0.02 * rng.standard_normal((3, 2)))
+    noise = G(rng.standard_normal((3, 3, 256, 4, 1)))  # [I, M, N, T, n_u]
+    res = mpc.solve(p0, noise=noise)
+    for m in range(3):
+        one = workloads.build_solver(w, record='costs')[1]
+        r1 = one.solve(p0[m:m + 1].contiguous(), noise=noise[:, m:m + 1].contiguous())
+        assert torch.equal(r1['elite_ids'][:, 0], res['elite_ids'][:, m])
+        assert torch.equal(r1['constraint'][:, 0], res['constraint'][:, m])
+        assert torch.allclose(r1['objective'][:, 0], res['objective'][:, m], rtol=1e-12, atol=0)
+        assert torch.allclose(r1['actions'][0], res['actions'][m], rtol=1e-12, atol=1e-15)
+
+
+def test_safempc_get_action_state_machine(golden_cem):
+    """test_safempc_cem.py:74-148: FOUND_SOLUTION -> PREVIOUS_SOLUTION (replay the stored plan) -> SAFE_CONTROLLER."""
+    g = golden_cem
+
+    class Env:
+        n_s, n_u = 2, 1
+        l_mu, l_sigm = g['l_mu'], g['l_sigma']
+        objective_spec = None
+
+        @staticmethod
+        def objective_cost_function(ps):
+            return None
+
+    class Conf:
+        mpc_time_horizon, cem_num_rollouts, cem_num_elites, cem_num_iterations = 2, 64, 8, 2
+        use_prior_model = True
+
+    gp = make_gp(g['x_train'], g['y_train'], g['lengthscale'], g['outputscale'], g['noise_var'])
+    cons = [se.ActionConstraint(se.TorchPolytope((g['act_a'], g['act_b']))),
+            se.EllipsoidTerminalConstraint(2, g['h_mat'], g['h_vec'])]
+    solver = se.B200CemSafeMPC(gp, cons, Env, Conf, {'lin_model': (g['a'], g['b'])}, np.diag([1., 2.]),
+                               25 * np.eye(1), beta_safety=2.0, safe_policy=lambda s: np.array([-7.0]), verbose=False)
+    assert np.allclose(solver._lqr.get_control_matrix(), g['k_fb'])
+    action, result = solver.get_action(g['p0'])
+    assert result == se.MpcResult.FOUND_SOLUTION and action.shape == (1,)
+    plan = solver._last_mpc_actions.copy()
+    # make every later solve infeasible: shrink the polytope through a fresh mpc
+    cons_bad = [cons[0], se.EllipsoidTerminalConstraint(2, g['h_mat'], 1e-3 * g['h_vec'])]
+    solver._mpc = se.B200ConstrainedCemMpc(solver._dynamics, cons_bad, 6, 1, 2, 64, 8, 2)
+    action, result = solver.get_action(g['p0'])
+    assert result == se.MpcResult.PREVIOUS_SOLUTION and np.array_equal(action, plan[1])
+    action, result = solver.get_action(g['p0'])
+    assert result == se.MpcResult.SAFE_CONTROLLER and action[0] == -7.0
+    # update_model subtracts the prior (safempc_cem.py:314-327)
+    x, y = g['x_train'][:10], g['y_train'][:10]
+    solver.update_model(x, y + x[:, :2] @ g['a'].T + x[:, 2:] @ g['b'].T, replace_old=True)
+    assert np.allclose(gp.y_train.cpu().numpy(), y, atol=1e-12) and solver.x_train.shape == (10, 3)
+    mean, var = solver.ssm_predict(x[:3])
+    assert mean.shape == (2, 3) and var.shape == (2, 3)
+
+
+# ---- full-size, size-independent properties -----------------------------------------------------------------------
+def test_full_size_c2_properties():
+    """BASELINE config C2 (pendulum, n = 2000, T = 10, N = 16384): properties that need no oracle run."""
+    w = workloads.pendulum_workload()
+    ssm, mpc = workloads.build_solver(w, record='costs', seed=1)
+    res = mpc.solve(G(w.p0).unsqueeze(0), seed=1)
+    cc, obj = res['constraint'][:, 0], res['objective'][:, 0]
+    assert torch.isfinite(obj).all() and int(res['flags'][0]) == 0
+    allowed = torch.tensor([3.0 * k + 10.0 * j for k in range(w.time_horizon + 1) for j in (0, 1)], device=DEV)
+    assert torch.isin(cc, allowed).all()  # constraint costs are 3 k + 10 j (hard parts)
+    # posterior variance bounds: noise <= var <= outputscale + noise  =>  -T sum(s + noise) <= obj <= -T sum(noise)
+    lo = -w.time_horizon * float((w.outputscale + w.noise).sum())
+    hi = -w.time_horizon * float(w.noise.sum())
+    assert float(obj.min()) >= lo * (1 + 1e-9) and float(obj.max()) <= hi * (1 - 1e-9)
+    # elites are sorted by (cost, index) and drawn from the right class
+    for i in range(w.num_iterations):
+        ids = res['elite_ids'][i, 0].long()
+        feasible = cc[i] == 0
+        if int(feasible.sum()) >= w.num_elites:
+            assert feasible[ids].all()
+            key = obj[i][ids]
+        else:
+            key = cc[i][ids]
+        assert (key[1:] >= key[:-1]).all() and ids.unique().numel() == w.num_elites
+        ref_ids = oracle.select_elites(obj[i].cpu(), cc[i].cpu(), w.num_elites)  # identical indices given these costs
+        assert np.array_equal(ids.cpu().numpy(), ref_ids.numpy())
+    # idempotence: same seed -> bit-identical solve
+    res2 = mpc.solve(G(w.p0).unsqueeze(0), seed=1)
+    for k in ('actions', 'objective', 'constraint', 'elite_ids', 'means', 'stds'):
+        assert torch.equal(res[k], res2[k]), k
+    # spot-check 64 random candidates of the last iteration against the oracle at full n = 2000
+    full = workloads.build_solver(w, record='full', seed=1)[1].solve(G(w.p0).unsqueeze(0), seed=1)
+    pick = np.random.default_rng(0).choice(w.num_rollouts, 64, replace=False)
+    acts = full['rollout_actions'][-1, 0].cpu()[pick]
+    ref_gp = make_oracle_gp(w.x_train, w.y_train, w.lengthscale, w.outputscale, w.noise)
+    prob = oracle.SafeCemProblem(ref_gp, w.l_mu, w.l_sigma, w.k_fb, w.a, w.b, w.beta_safety, w.h_mat, w.h_vec,
+                                 w.act_a, w.act_b)
+    ref = oracle.perform_rollouts(prob, T(w.p0), acts)
+    assert np.array_equal(full['constraint'][-1, 0].cpu().numpy()[pick], ref.constraint_costs.numpy())
+    assert rel_err(full['objective'][-1, 0].cpu().numpy()[pick], ref.objective_costs) < 1e-7
+    assert rel_err(full['trajectories'][-1, 0].cpu().numpy()[pick], ref.trajectories, 1e-4) < 1e-7

@@ -1,0 +1,157 @@
+"""CPU: the C-ABI library loads and exports every symbol include/secem.h declares (no compute calls without a GPU),
+and the host-side mirror of the reference's interfaces behaves like the reference's own unit tests say."""
+import ctypes
+import os
+import re
+
+import numpy as np
+import pytest
+import torch
+
+import safe_exploration_b200 as se
+from safe_exploration_b200 import _lib, workloads
+from safe_exploration_b200.safempc import fold_constraints
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _declared_symbols():
+    text = open(os.path.join(ROOT, 'include', 'secem.h')).read()
+    text = re.sub(r'/\*.*?\*/', '', text, flags=re.S)
+    return sorted(set(re.findall(r'\b(se_[a-z0-9_]+)\s*\(', text)))
+
+
+def test_library_exports_every_declared_symbol():
+    lib = _lib.load()
+    declared = _declared_symbols()
+    assert len(declared) >= 20
+    for name in declared:
+        assert hasattr(lib, name), f'{name} declared in include/secem.h but not exported by libsecem.so'
+        assert name in _lib.SIGNATURES, f'{name} has no ctypes signature'
+    assert lib.se_version() == 100
+
+
+def test_struct_layouts_match_header():
+    # se_problem: 2 ints, 5 pointers, double, int, 2 pointers, int, 2 pointers, 2 doubles, int, double, int
+    assert ctypes.sizeof(_lib.SeProblem) == 144
+    assert ctypes.sizeof(_lib.SeCemConfig) == 32
+    assert ctypes.sizeof(_lib.SeCemOutputs) == 11 * 8
+
+
+def test_argument_errors_are_reported_without_a_gpu():
+    lib = _lib.load()
+    out = ctypes.c_void_p(None)
+    rc = lib.se_gp_create(ctypes.byref(out), 9, 1, 10, _lib.SE_F64, None, None, None, None, None, None, None)
+    assert rc != 0 and b'n_s' in lib.se_last_error()
+    with pytest.raises(_lib.SecemError):
+        _lib.check(rc)
+
+
+def test_no_cpu_fallback():
+    ssm = se.B200GpCemSSM(None, 2, 1)
+    with pytest.raises(_lib.SecemError):
+        ssm.predict_without_jacobians(torch.zeros(1, 2), torch.zeros(1, 1))  # no model / not on a CUDA device
+    with pytest.raises(_lib.SecemError):
+        se.is_ellipsoid_inside_polytope(torch.zeros(1, 2), torch.eye(2).unsqueeze(0), torch.eye(2), torch.ones(2, 1))
+
+
+def test_pq_flattener_round_trip():
+    """test_safempc_cem.py:23-42."""
+    f = se.PQFlattener(3)
+    p, q = torch.rand(4, 3), torch.rand(4, 3, 3)
+    flat = f.flatten(p, q)
+    assert flat.shape == (4, 12) and f.get_flat_state_dimen() == 12
+    p2, q2 = f.unflatten(flat)
+    assert torch.equal(p, p2) and torch.equal(q, q2)
+    p3, q3 = f.unflatten(f.flatten(p, None))
+    assert torch.equal(p, p3) and q3 is None
+
+
+def test_torch_polytope_and_action_constraint():
+    """constrained_cem_mpc_test.py:60-136 + test_safempc_cem.py:59-71."""
+    poly = se.box2torchpoly([[0., 10.], [0., 10.]])
+    assert torch.tensor([5., 5.]) in poly and torch.tensor([10., 0.]) in poly and torch.tensor([11., 5.]) not in poly
+    assert poly.contains_points(torch.tensor([[1., 1.], [20., 1.], [5., -1.], [10., 10.]])) == 2
+    assert np.allclose(poly.chebXc.numpy(), [5., 5.])
+    c = se.ActionConstraint(se.box2torchpoly([[-0.5, 0.5]]))
+    assert c(None, torch.tensor([[0.2], [-5.], [6.]])) == 6
+
+
+def test_construct_constraints_and_folding():
+    class Env:
+        n_s, n_u = 4, 1
+        u_min_norm, u_max_norm = np.array([-0.5]), np.array([0.5])
+
+        def get_safety_constraints(self, normalize=True):
+            h, v = workloads.cartpole_polytope()
+            return h, v[:, None], None, None
+
+    class Conf:
+        use_state_constraint = True
+
+    cs = se.construct_constraints(Conf(), Env())
+    assert isinstance(cs[0], se.ActionConstraint) and isinstance(cs[1], se.EllipsoidStateConstraint)
+    Conf.use_state_constraint = False
+    cs = se.construct_constraints(Conf(), Env())
+    assert isinstance(cs[1], se.EllipsoidTerminalConstraint)
+    prob = fold_constraints(se.SafeProblem(4, 1, np.ones(4), np.ones(4)), cs)
+    st = prob.c_struct()
+    assert st.m_safe == 9 and st.m_act == 2 and st.act_penalty == 3.0 and st.state_penalty == 10.0
+    assert st.all_states_constraint == 0  # quirk Q1: "state" constraint is terminal-only by default
+    with pytest.raises(TypeError):
+        fold_constraints(prob, [object()])
+
+
+def test_workload_constants_match_reference_environments():
+    """Values printed by the verbatim reference environments in the build container (make_golden.py)."""
+    a, b = workloads.pendulum_linear_model()
+    assert np.allclose(a, [[1.02465061, 0.99005578], [0.05041017, 1.02465061]], atol=1e-8)
+    assert np.allclose(b, [[1.34427126], [0.03346995]], atol=1e-8)
+    h, v = workloads.pendulum_polytope(True)
+    assert sorted(np.round(v, 8)) == sorted(np.round([0.34906585, 0.8, 0.8, 0.34906585], 8))
+    ac, bc = workloads.cartpole_linear_model()
+    assert np.allclose(ac[0], [1.0, 1.66666667e-01, 4.19847224e-03, -5.25453321e-04], atol=1e-8)
+    assert np.allclose(bc[:, 0], [0.02653238, 0.31886176, 0.29942205, 0.35589813], atol=1e-8)
+    hc, vc = workloads.cartpole_polytope()
+    assert hc.shape == (9, 4) and vc.shape == (9,)
+
+
+def test_golden_cem_constants_equal_workload_restatement(golden_cem):
+    g = golden_cem  # a, b, k_fb, polytope come from the verbatim reference environment
+    w = workloads.pendulum_workload(n_train=8, num_rollouts=8)
+    assert np.allclose(w.a, g['a']) and np.allclose(w.b, g['b']) and np.allclose(w.k_fb, g['k_fb'])
+    order = lambda h, v: sorted(map(tuple, np.round(np.hstack((h, v[:, None])), 9).tolist()))
+    assert order(w.h_mat, w.h_vec) == order(g['h_mat'], g['h_vec'])
+    assert np.allclose(w.act_a, g['act_a']) and np.allclose(w.act_b, g['act_b'])
+
+
+def test_dlqr_matches_riccati():
+    a, b = workloads.pendulum_linear_model()
+    k, x, eig = se.dlqr(a, b, np.diag([1., 2.]), 25 * np.eye(1))
+    assert np.all(np.abs(eig) < 1)
+    resid = a.T @ x @ a - x - a.T @ x @ b @ np.linalg.solve(b.T @ x @ b + 25, b.T @ x @ a) + np.diag([1., 2.])
+    assert np.abs(resid).max() < 1e-8
+
+
+def test_cem_constructor_contract():
+    ssm = se.B200GpCemSSM(None, 2, 1)
+    dyn = se.B200SafeDynamics(ssm, se.SafeProblem(2, 1, [.1, .1], [.1, .1], k_fb=np.zeros((1, 2)), a=np.eye(2),
+                                                  b=np.zeros((2, 1))))
+    cons = [se.ActionConstraint(se.box2torchpoly([[-1., 1.]])),
+            se.EllipsoidTerminalConstraint(2, *workloads.pendulum_polytope())]
+    mpc = se.B200ConstrainedCemMpc(dyn, cons, 6, 1, 5, 64, 8, 3)
+    assert mpc._num_iterations == 3 and mpc._rollout_function._constraints[1] is cons[1]  # safempc_cem.py:270, 280
+    with pytest.raises(ValueError):
+        se.B200ConstrainedCemMpc(dyn, cons, 5, 1, 5, 64, 8, 3)
+    with pytest.raises(TypeError):
+        se.B200ConstrainedCemMpc(lambda s, a: (s, a), cons, 6, 1, 5, 64, 8, 3)
+    with pytest.raises(_lib.SecemError):
+        mpc.get_actions(torch.zeros(1, 6))  # no training data -> loud failure, no fallback
+
+
+def test_update_model_shape_errors():
+    ssm = se.B200GpCemSSM(None, 2, 1)
+    with pytest.raises(ValueError):  # ssm_cem.py:83-84
+        ssm.update_model(torch.zeros(5, 4), torch.zeros(5, 2))
+    with pytest.raises(ValueError):
+        ssm.update_model(torch.zeros(5, 3), torch.zeros(5, 3))
