@@ -75,3 +75,18 @@ def attach_population_sharding(mpc, group: Optional[dist.ProcessGroup] = None) -
     comm = create_nccl_comm(group, mpc._ssm.device)
     mpc.set_comm(comm, rank, world)
     return comm
+
+
+def pack_costs(objective: torch.Tensor, constraint: torch.Tensor) -> torch.Tensor:
+    """Local costs [M, N_local] x2 -> the send buffer layout of the device path: [2, M, N_local]
+    (plane 0 = objective, plane 1 = constraint; csrc/cem_kernels.cuh `cem_pack_costs_kernel`)."""
+    return torch.stack((objective, constraint), dim=0).contiguous()
+
+
+def unpack_costs(pack_all: torch.Tensor, world_size: int, num_instances: int, n_local: int):
+    """Gathered buffer [W, 2, M, N_local] -> (objective [M, N], constraint [M, N]) in GLOBAL candidate order
+    (global id g lives on rank g // N_local at local index g % N_local; `CostView::get` in csrc/cem_kernels.cuh)."""
+    v = pack_all.reshape(world_size, 2, num_instances, n_local)
+    obj = v[:, 0].permute(1, 0, 2).reshape(num_instances, world_size * n_local)
+    con = v[:, 1].permute(1, 0, 2).reshape(num_instances, world_size * n_local)
+    return obj, con
