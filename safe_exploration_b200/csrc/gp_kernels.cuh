@@ -261,28 +261,59 @@ __device__ __forceinline__ void cp_async_wait() {
   asm volatile("cp.async.wait_group %0;\n" ::"n"(N));
 }
 
+// Work-item order.  rc = row tiles per "L2 chunk": all items of rc consecutive row tiles are issued before the next
+// chunk starts, so the K* rows of a chunk (rc * 128 * n_pad * ns elements) stay L2-resident while every column block
+// re-reads them; inside a chunk items go heaviest (deepest column block) first.
+struct TriOrder {
+  int nb, rt_count, ns, rc;
+};
+__device__ __forceinline__ TriItem decode_item_chunked(int idx, const TriOrder& od) {
+  const int per_chunk = od.rc * od.ns * od.nb;
+  const int chunk = idx / per_chunk;
+  const int rt0 = chunk * od.rc;
+  const int rc_here = min(od.rc, od.rt_count - rt0);
+  // the last chunk may hold fewer row tiles; its items follow all full chunks
+  const int local = idx - chunk * per_chunk;
+  const int per_ib = rc_here * od.ns;
+  TriItem it;
+  it.ib = od.nb - 1 - local / per_ib;
+  const int rem = local % per_ib;
+  it.rt = rt0 + rem / od.ns;
+  it.o = rem % od.ns;
+  return it;
+}
+__host__ __device__ inline int tri_total_items(int nb, int rt_count, int ns) { return nb * rt_count * ns; }
+
+template <int WM_, int WN_, int BK_, int STAGES_, int BM_ = 128, int MINB_ = 1>
 struct DmmaCfg {
-  static constexpr int BM = 128, BN = 128, BK = 16, LDS = 20 /* doubles per smem row: conflict-free LDS.64 */,
-                       STAGES = 3, THREADS = 256;
+  static constexpr int BM = BM_, BN = 128, BK = BK_, STAGES = STAGES_, WM = WM_, WN = WN_, MINB = MINB_;
+  static constexpr int LDS = BK + 4;  // doubles per smem row: (BK + 4) mod 16 == 4 -> conflict-free LDS.64 fragments
+  static constexpr int THREADS = WM * WN * 32;
+  static constexpr int MI = BM / WM / 8, NI = BN / WN / 8;  // m8n8 tiles per warp
   static constexpr int STAGE_DOUBLES = (BM + BN) * LDS;
-  static constexpr int SMEM_BYTES = STAGES * STAGE_DOUBLES * 8 + 4 * BM * 8 + 16;
+  static constexpr int SMEM_BYTES = STAGES * STAGE_DOUBLES * 8 + WN * BM * 8 + 16;
+  static constexpr int CHUNKS_A = BM * (BK / 2) / THREADS;  // 16-byte cp.async chunks per thread, K* tile
+  static constexpr int CHUNKS_B = BN * (BK / 2) / THREADS;  // ... and L^-1 tile
+  static_assert(BM * (BK / 2) % THREADS == 0 && BN * (BK / 2) % THREADS == 0, "tile / thread mismatch");
 };
 
-static __global__ void __launch_bounds__(DmmaCfg::THREADS, 1)
+template <typename C, bool SKIP_DIAG>
+static __global__ void __launch_bounds__(C::THREADS, C::MINB)
 gp_trisumsq_dmma_kernel(const double* __restrict__ kst, const double* __restrict__ w, int n_pad, int rows_pad,
-                        int ns, double* __restrict__ partial, int* __restrict__ counter) {
-  using C = DmmaCfg;
+                        TriOrder od, double* __restrict__ partial, int* __restrict__ counter) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   double* stages = reinterpret_cast<double*>(smem_raw);
-  double* red = stages + C::STAGES * C::STAGE_DOUBLES;  // [4][BM]
-  int* s_item = reinterpret_cast<int*>(red + 4 * C::BM);
+  double* red = stages + C::STAGES * C::STAGE_DOUBLES;  // [WN][BM]
+  int* s_item = reinterpret_cast<int*>(red + C::WN * C::BM);
 
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  const int wm = warp >> 2, wn = warp & 3;  // 2 x 4 warps, warp tile 64 x 32
+  const int wm = warp / C::WN;
+  // warp w runs on SM sub-partition w % 4 (each has its own DMMA unit): odd warp rows take the column groups in
+  // reverse so that the triangular skip below removes the same amount of work from every sub-partition
+  const int wn = (SKIP_DIAG && (wm & 1)) ? C::WN - 1 - warp % C::WN : warp % C::WN;
   const int g = lane >> 2, q = lane & 3;
-  const int nb = n_pad / C::BN;
-  const int rt_count = rows_pad / C::BM;
-  const int total = nb * rt_count * ns;
+  constexpr int WTM = C::BM / C::WM, WTN = C::BN / C::WN;  // warp tile
+  const int total = tri_total_items(od.nb, od.rt_count, od.ns);
 
   while (true) {
     if (tid == 0) *s_item = atomicAdd(counter, 1);
@@ -290,29 +321,35 @@ gp_trisumsq_dmma_kernel(const double* __restrict__ kst, const double* __restrict
     const int idx = *s_item;
     __syncthreads();
     if (idx >= total) break;
-    const TriItem it = decode_item(idx, nb, rt_count, ns);
+    const TriItem it = decode_item_chunked(idx, od);
     const double* a_base = kst + ((int64_t)it.o * rows_pad + (int64_t)it.rt * C::BM) * n_pad;
     const double* b_base = w + ((int64_t)it.o * n_pad + (int64_t)it.ib * C::BN) * n_pad;
     const int ktiles = (it.ib + 1) * C::BN / C::BK;
+    const int diag_kt = it.ib * C::BN / C::BK;  // first k-tile of the diagonal block (negative offsets never skip)
 
     auto issue_stage = [&](int kt) {
       double* sa = stages + (kt % C::STAGES) * C::STAGE_DOUBLES;
       double* sb = sa + C::BM * C::LDS;
       const int k0 = kt * C::BK;
 #pragma unroll
-      for (int c = 0; c < 4; ++c) {
-        const int id = tid + C::THREADS * c;  // 1024 16-byte chunks per operand
-        const int row = id >> 3, kc = (id & 7) * 2;
+      for (int c = 0; c < C::CHUNKS_A; ++c) {
+        const int id = tid + C::THREADS * c;
+        const int row = id / (C::BK / 2), kc = (id % (C::BK / 2)) * 2;
         cp_async16(sa + row * C::LDS + kc, a_base + (int64_t)row * n_pad + k0 + kc);
+      }
+#pragma unroll
+      for (int c = 0; c < C::CHUNKS_B; ++c) {
+        const int id = tid + C::THREADS * c;
+        const int row = id / (C::BK / 2), kc = (id % (C::BK / 2)) * 2;
         cp_async16(sb + row * C::LDS + kc, b_base + (int64_t)row * n_pad + k0 + kc);
       }
     };
 
-    double acc[8][4][2];
+    double acc[C::MI][C::NI][2];
 #pragma unroll
-    for (int mi = 0; mi < 8; ++mi)
+    for (int mi = 0; mi < C::MI; ++mi)
 #pragma unroll
-      for (int ni = 0; ni < 4; ++ni) acc[mi][ni][0] = acc[mi][ni][1] = 0.0;
+      for (int ni = 0; ni < C::NI; ++ni) acc[mi][ni][0] = acc[mi][ni][1] = 0.0;
 
 #pragma unroll
     for (int s = 0; s < C::STAGES - 1; ++s) {
@@ -324,37 +361,45 @@ gp_trisumsq_dmma_kernel(const double* __restrict__ kst, const double* __restrict
       __syncthreads();
       if (kt + C::STAGES - 1 < ktiles) issue_stage(kt + C::STAGES - 1);
       cp_async_commit();
-      const double* sa = stages + (kt % C::STAGES) * C::STAGE_DOUBLES + (wm * 64 + g) * C::LDS + q;
-      const double* sb = stages + (kt % C::STAGES) * C::STAGE_DOUBLES + C::BM * C::LDS + (wn * 32 + g) * C::LDS + q;
+      const double* sa = stages + (kt % C::STAGES) * C::STAGE_DOUBLES + (wm * WTM + g) * C::LDS + q;
+      const double* sb =
+          stages + (kt % C::STAGES) * C::STAGE_DOUBLES + C::BM * C::LDS + (wn * WTN + g) * C::LDS + q;
+      // Diagonal block: W[i][j] = 0 for j > i, so a warp whose 32 columns all have i < k0 has nothing to add.  The
+      // predicate is warp-uniform and tile-granular (BK divides the warp-tile width); the warp -> column mapping above
+      // pairs column groups s and WN-1-s on the same SM sub-partition, so the skipped DMMAs shorten the critical path.
+      if (!SKIP_DIAG || (kt - diag_kt) * C::BK < (wn + 1) * WTN) {
 #pragma unroll
-      for (int kk = 0; kk < C::BK; kk += 4) {
-        double a[8], b[4];
+        for (int kk = 0; kk < C::BK; kk += 4) {
+          double a[C::MI], b[C::NI];
 #pragma unroll
-        for (int mi = 0; mi < 8; ++mi) a[mi] = sa[mi * 8 * C::LDS + kk];
+          for (int mi = 0; mi < C::MI; ++mi) a[mi] = sa[mi * 8 * C::LDS + kk];
 #pragma unroll
-        for (int ni = 0; ni < 4; ++ni) b[ni] = sb[ni * 8 * C::LDS + kk];
+          for (int ni = 0; ni < C::NI; ++ni) b[ni] = sb[ni * 8 * C::LDS + kk];
 #pragma unroll
-        for (int mi = 0; mi < 8; ++mi)
+          for (int mi = 0; mi < C::MI; ++mi)
 #pragma unroll
-          for (int ni = 0; ni < 4; ++ni) dmma_m8n8k4(acc[mi][ni][0], acc[mi][ni][1], a[mi], b[ni]);
+            for (int ni = 0; ni < C::NI; ++ni) dmma_m8n8k4(acc[mi][ni][0], acc[mi][ni][1], a[mi], b[ni]);
+        }
       }
     }
     cp_async_wait<0>();
 
     // epilogue: accumulator fragment (mi, ni) holds row g (+8 mi) and columns 2q, 2q+1 (+8 ni)
 #pragma unroll
-    for (int mi = 0; mi < 8; ++mi) {
+    for (int mi = 0; mi < C::MI; ++mi) {
       double s = 0.0;
 #pragma unroll
-      for (int ni = 0; ni < 4; ++ni) s += acc[mi][ni][0] * acc[mi][ni][0] + acc[mi][ni][1] * acc[mi][ni][1];
+      for (int ni = 0; ni < C::NI; ++ni) s += acc[mi][ni][0] * acc[mi][ni][0] + acc[mi][ni][1] * acc[mi][ni][1];
       s += __shfl_xor_sync(0xffffffffu, s, 1);
       s += __shfl_xor_sync(0xffffffffu, s, 2);
-      if (q == 0) red[wn * C::BM + wm * 64 + mi * 8 + g] = s;
+      if (q == 0) red[wn * C::BM + wm * WTM + mi * 8 + g] = s;
     }
     __syncthreads();
     if (tid < C::BM) {
-      const double s = red[tid] + red[C::BM + tid] + red[2 * C::BM + tid] + red[3 * C::BM + tid];
-      partial[((int64_t)it.o * nb + it.ib) * rows_pad + (int64_t)it.rt * C::BM + tid] = s;
+      double s = 0.0;
+#pragma unroll
+      for (int x = 0; x < C::WN; ++x) s += red[x * C::BM + tid];
+      partial[((int64_t)it.o * od.nb + it.ib) * rows_pad + (int64_t)it.rt * C::BM + tid] = s;
     }
     // the __syncthreads at the top of the loop orders these reads of `red` before the next item's writes
   }

@@ -1,4 +1,6 @@
 // inst_gemm.cu -- variance GEMM launchers, model packing and the pipe-peak micro-benchmarks
+#include <cstdlib>
+
 #include "gp_kernels.cuh"
 #include "launchers.cuh"
 
@@ -28,21 +30,61 @@ int launch_trisumsq<double>(se_gemm_impl impl, const double* kst, const double* 
                             double* partial, int* counter, int sm_count, int* nb_out, cudaStream_t stream) {
   if (impl == SE_GEMM_SIMT)
     return launch_trisumsq_simt<double>(kst, w, n_pad, rows_pad, ns, partial, counter, sm_count, nb_out, stream);
-  using C = DmmaCfg;
-  static bool attr_set = false;
-  if (!attr_set) {
-    SE_CUDA(cudaFuncSetAttribute(gp_trisumsq_dmma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                 C::SMEM_BYTES));
-    attr_set = true;
-  }
-  const int nb = n_pad / C::BN;
-  const int64_t items = (int64_t)nb * (rows_pad / C::BM) * ns;
-  const int grid = (int)(items < sm_count ? items : sm_count);
+  // variant / order knobs (defaults = the tuned configuration; the environment variables exist for tools/gemm_bench.py)
+  static const int variant = getenv("SE_DMMA_VARIANT") ? atoi(getenv("SE_DMMA_VARIANT")) : 5;
+  static const int skip = getenv("SE_DMMA_SKIP") ? atoi(getenv("SE_DMMA_SKIP")) : 1;
+  static const int64_t l2_budget = getenv("SE_DMMA_L2MB") ? atoll(getenv("SE_DMMA_L2MB")) << 20 : (48ll << 20);
+  const int bm = (variant == 5 || variant == 6) ? 64 : 128;
+  TriOrder od;
+  od.nb = n_pad / 128;
+  od.rt_count = rows_pad / bm;
+  od.ns = ns;
+  int64_t rc = l2_budget / ((int64_t)bm * n_pad * 8 * ns);
+  if (l2_budget <= 0 || rc > od.rt_count) rc = od.rt_count;
+  if (rc < 1) rc = 1;
+  od.rc = (int)rc;
+  const int64_t items = (int64_t)od.nb * od.rt_count * ns;
+  const int64_t ctas = (int64_t)sm_count * (bm == 64 ? 2 : 1);
+  const int grid = (int)(items < ctas ? items : ctas);
   SE_CUDA(cudaMemsetAsync(counter, 0, sizeof(int), stream));
-  SE_LAUNCH(gp_trisumsq_dmma_kernel, grid, C::THREADS, C::SMEM_BYTES, stream, kst, w, n_pad, rows_pad, ns, partial,
-            counter);
-  *nb_out = nb;
-  return 0;
+  *nb_out = od.nb;
+#define SE_DMMA_LAUNCH(CFG, SKIP)                                                                                  \
+  do {                                                                                                             \
+    static bool attr_set = false;                                                                                  \
+    if (!attr_set) {                                                                                               \
+      SE_CUDA(cudaFuncSetAttribute((gp_trisumsq_dmma_kernel<CFG, SKIP>), cudaFuncAttributeMaxDynamicSharedMemorySize, \
+                                   CFG::SMEM_BYTES));                                                              \
+      attr_set = true;                                                                                             \
+    }                                                                                                              \
+    SE_LAUNCH((gp_trisumsq_dmma_kernel<CFG, SKIP>), grid, CFG::THREADS, CFG::SMEM_BYTES, stream, kst, w, n_pad,    \
+              rows_pad, od, partial, counter);                                                                     \
+    return 0;                                                                                                      \
+  } while (0)
+  using V0 = DmmaCfg<2, 4, 16, 3>;
+  using V1 = DmmaCfg<4, 4, 16, 3>;
+  using V2 = DmmaCfg<2, 4, 32, 3>;
+  using V3 = DmmaCfg<4, 4, 32, 3>;
+  using V4 = DmmaCfg<2, 4, 16, 4>;
+  using V5 = DmmaCfg<2, 4, 16, 3, 64, 2>;  // 64 x 128 tile, 2 CTAs / SM
+  using V6 = DmmaCfg<2, 4, 32, 2, 64, 2>;
+  switch (variant * 2 + (skip ? 1 : 0)) {
+    case 0: SE_DMMA_LAUNCH(V0, false);
+    case 1: SE_DMMA_LAUNCH(V0, true);
+    case 2: SE_DMMA_LAUNCH(V1, false);
+    case 3: SE_DMMA_LAUNCH(V1, true);
+    case 4: SE_DMMA_LAUNCH(V2, false);
+    case 5: SE_DMMA_LAUNCH(V2, true);
+    case 6: SE_DMMA_LAUNCH(V3, false);
+    case 7: SE_DMMA_LAUNCH(V3, true);
+    case 8: SE_DMMA_LAUNCH(V4, false);
+    case 9: SE_DMMA_LAUNCH(V4, true);
+    case 10: SE_DMMA_LAUNCH(V5, false);
+    case 11: SE_DMMA_LAUNCH(V5, true);
+    case 12: SE_DMMA_LAUNCH(V6, false);
+    case 13: SE_DMMA_LAUNCH(V6, true);
+  }
+#undef SE_DMMA_LAUNCH
+  return fail("unknown SE_DMMA_VARIANT %d", variant);
 }
 
 template <typename T>
