@@ -141,8 +141,13 @@ def pendulum_workload(n_train=2000, time_horizon=10, num_rollouts=16384, num_eli
 
 
 def cartpole_workload(n_train=5000, time_horizon=15, num_rollouts=65536, num_elites=None, num_iterations=8, seed=2,
-                      name='C3') -> Workload:
-    """C3: CartPole (4 states) safe CEM-MPC, GP on n_train points."""
+                      name='C3', lipschitz=0.01) -> Workload:
+    """C3: CartPole (4 states) safe CEM-MPC, GP on n_train points.
+
+    l_mu = l_sigma = 0.01 instead of the environment's 0.05 (environments.py:936-941): with 0.05 the remainder term
+    l_mu * lambda_max(q (I + k_fb^T k_fb)) squares the ellipsoid every step and the shape matrices of the initial
+    (std = 1) candidates overflow float64 around step 11 of 15 -- in the reference's own arithmetic too (the oracle
+    fails the same way), where `_fix_zeros_nans` then raises.  The reference runs this environment with horizons 2-5."""
     rng = np.random.default_rng(seed)
     a, b = cartpole_linear_model()
     k_lqr, _, _ = dlqr(a, b, np.diag([2., 6., 12., 4.]), 40.0 * np.eye(1))  # defaultconfig_episode.py:69-71
@@ -154,7 +159,7 @@ def cartpole_workload(n_train=5000, time_horizon=15, num_rollouts=65536, num_eli
     ls = np.tile(np.array([0.6, 0.35, 0.3, 0.3, 0.6]), (4, 1)) * np.array([[1.0], [1.1], [0.9], [1.2]])
     return Workload(
         name=name, n_s=4, n_u=1, x_train=x, y_train=y, lengthscale=ls, outputscale=np.full(4, 0.02 ** 2 * 4),
-        noise=np.full(4, 2e-6), a=a, b=b, k_fb=-k_lqr, l_mu=np.full(4, 0.05), l_sigma=np.full(4, 0.05), h_mat=h_mat,
+        noise=np.full(4, 2e-6), a=a, b=b, k_fb=-k_lqr, l_mu=np.full(4, lipschitz), l_sigma=np.full(4, lipschitz), h_mat=h_mat,
         h_vec=h_vec, act_a=act_a, act_b=act_b, beta_safety=2.0, time_horizon=time_horizon, num_rollouts=num_rollouts,
         num_elites=num_elites if num_elites is not None else max(3, num_rollouts // 64),
         num_iterations=num_iterations, p0=np.zeros(4), meta=dict(env='CartPole', seed=seed))
