@@ -38,7 +38,8 @@ def parse_args():
     ap.add_argument('--impl', default='b200', choices=['b200', 'reference'])
     ap.add_argument('--dtype', default='f64', choices=['f64', 'f32'])
     ap.add_argument('--config', default='C2', choices=['C1', 'C2', 'C3'])
-    ap.add_argument('--gemm', default='auto', choices=['auto', 'simt', 'mma'])
+    ap.add_argument('--gemm', default='auto', choices=['auto', 'simt', 'mma', 'tc'])
+    ap.add_argument('--tc-digits', type=int, default=7, choices=[5, 6, 7])
     ap.add_argument('--cpu-sample', type=int, default=2048, help='candidates in the CPU-baseline sample')
     ap.add_argument('--no-cpu-baseline', action='store_true')
     return ap.parse_args()
@@ -176,10 +177,12 @@ def run_b200(args):
         dist.init_process_group('nccl', device_id=torch.device(dev))
     lib = se.load_library()
     dtype = torch.float64 if args.dtype == 'f64' else torch.float32
-    gemm = {'auto': _lib.SE_GEMM_AUTO, 'simt': _lib.SE_GEMM_SIMT, 'mma': _lib.SE_GEMM_MMA}[args.gemm]
+    gemm = {'auto': _lib.SE_GEMM_AUTO, 'simt': _lib.SE_GEMM_SIMT, 'mma': _lib.SE_GEMM_MMA, 'tc': _lib.SE_GEMM_TC}[args.gemm]
 
     w = make_workload(args.config, world)
     ssm, mpc = workloads.build_solver(w, dtype=dtype, device=dev, record='none', seed=1234, gemm_impl=gemm)
+    if args.gemm == 'tc':
+        _lib.check(lib.se_gp_set_tc_digits(ssm.handle, args.tc_digits))
     comm = sedist.attach_population_sharding(mpc) if world > 1 else 0
     p0 = torch.as_tensor(w.p0, device=dev, dtype=dtype).unsqueeze(0)
     cand_steps = w.num_rollouts * w.time_horizon * w.num_iterations  # whole job, all ranks

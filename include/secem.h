@@ -44,7 +44,9 @@ typedef enum {
 typedef enum {
   SE_GEMM_AUTO = 0,
   SE_GEMM_SIMT = 1, /* FP32 FFMA / FP64 DFMA register-tiled */
-  SE_GEMM_MMA = 2   /* FP64: DMMA m8n8k4; FP32: 3xTF32 mma.sync */
+  SE_GEMM_MMA = 2,  /* FP64: DMMA m8n8k4 (mma.sync) */
+  SE_GEMM_TC = 3    /* FP64 models on the 5th-gen tensor cores: tcgen05.mma kind::i8 over 7-bit digit planes of both
+                       operands with exact int32 accumulation in TMEM (Ozaki scheme), recombined in int64 / double */
 } se_gemm_impl;
 
 typedef struct se_gp_s* se_gp_t;
@@ -73,6 +75,9 @@ int se_gp_destroy(se_gp_t gp);
 /* workspace cap (bytes) for the materialised kernel rows K*[n_s, N_chunk, n]; default 6 GiB */
 int se_gp_set_workspace_limit(se_gp_t gp, uint64_t bytes);
 int se_gp_set_gemm_impl(se_gp_t gp, se_gemm_impl impl);
+/* digit planes per operand of SE_GEMM_TC: 7 (default; variance within ~1e-9 relative of the float64 evaluation on the
+ * bench workload), 6 (~5e-8, 25 % fewer MMAs) or 5 (~7e-6) */
+int se_gp_set_tc_digits(se_gp_t gp, int digits);
 
 /* mean [N, n_s], variance [N, n_s] (likelihood noise INCLUDED, gp_ssm_cem.py:93) and, if dev_jac != NULL, the
  * Jacobian of the mean w.r.t. z, [N, n_s, d].  Replaces GpCemSSM.predict_without_jacobians / predict_with_jacobians
@@ -217,6 +222,13 @@ int se_measure_peak(int kind, double* flops_out);
 int se_gp_timing_enable(se_gp_t gp, int enable);
 int se_gp_timing_read(se_gp_t gp, double* gemm_ms, int64_t* gemm_launches, double* kstar_ms,
                       int64_t* kstar_launches, void* stream);
+
+/* Test hook: runs the tcgen05 tile primitive of SE_GEMM_TC on one 128 x 64 tile.  dev_a_img [nk][digits][128 x 32 B],
+ * dev_b_img [nk][digits][64 x 32 B] are int8 digit planes in the shared-memory operand order (8-row x 16-byte core
+ * matrices; lbo / sbo = the two strides of the UMMA descriptor); dev_out [digits][128][64] int32 receives the level sums
+ * D_l = sum_{t+u=l} A_t B_u^T. */
+int se_debug_tc_probe(const int8_t* dev_a_img, const int8_t* dev_b_img, int nk, int digits, int lbo, int sbo,
+                      int32_t* dev_out, void* stream);
 
 #ifdef __cplusplus
 }

@@ -12,7 +12,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libsecem.so")
 
 SE_F32, SE_F64 = 0, 1
-SE_GEMM_AUTO, SE_GEMM_SIMT, SE_GEMM_MMA = 0, 1, 2
+SE_GEMM_AUTO, SE_GEMM_SIMT, SE_GEMM_MMA, SE_GEMM_TC = 0, 1, 2, 3
 SE_OBJ_NEG_VARIANCE, SE_OBJ_ABS_STATE1, SE_OBJ_NEG_LAST_STATE = 0, 1, 2
 SE_MAX_NS, SE_MAX_NU, SE_MAX_FACES, SE_MAX_ACT_FACES, SE_MAX_T = 6, 3, 16, 8, 64
 MAX_ELITES = 4096
@@ -52,6 +52,8 @@ SIGNATURES = {
     "se_gp_destroy": (_i, [_vp]),
     "se_gp_set_workspace_limit": (_i, [_vp, _u64]),
     "se_gp_set_gemm_impl": (_i, [_vp, _i]),
+    "se_gp_set_tc_digits": (_i, [_vp, _i]),
+    "se_debug_tc_probe": (_i, [_vp, _vp, _i, _i, _i, _i, _vp, _vp]),
     "se_gp_predict": (_i, [_vp, _vp, _i64, _vp, _vp, _vp, _vp]),
     "se_reach_onestep": (_i, [_vp, C.POINTER(SeProblem), _vp, _vp, _vp, _i64, _vp, _vp, _vp, _vp, _vp]),
     "se_reach_multistep": (_i, [_vp, C.POINTER(SeProblem), _vp, _vp, _vp, _i64, _i, _dbl_p, _vp, _vp, _vp, _vp, _vp,

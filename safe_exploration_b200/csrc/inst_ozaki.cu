@@ -1,0 +1,108 @@
+// inst_ozaki.cu -- launchers of the tcgen05 (kind::i8) digit-sliced variance GEMM and of the kernels feeding it
+#include <cstdlib>
+
+#include "launchers.cuh"
+#include "ozaki_kernels.cuh"
+
+namespace se {
+
+int oz_image_bytes_b(int n_pad, int ns, int S, size_t* out) {
+  *out = (size_t)ns * n_pad * (size_t)n_pad * S;
+  return 0;
+}
+
+// exp_a[o] = exponent with outputscale_o < 2^exp_a; per-row exponents / scales of L^-1; digit image of L^-1
+int launch_oz_pack_model(const double* w, int n_pad, int ns, const double* host_outputscale, int S, int* exp_a,
+                         int* exp_b, double* scale_b, int8_t* b_img, cudaStream_t stream) {
+  SE_REQUIRE(S >= 3 && S <= oz::MAX_S, "digit planes S = %d outside [3, %d]", S, oz::MAX_S);
+  int ea[SE_MAX_NS] = {};
+  for (int o = 0; o < ns; ++o) {
+    SE_REQUIRE(host_outputscale[o] > 0.0, "outputscale[%d] must be > 0", o);
+    frexp(host_outputscale[o], &ea[o]);
+  }
+  SE_CUDA(cudaMemcpyAsync(exp_a, ea, ns * sizeof(int), cudaMemcpyHostToDevice, stream));
+  const int64_t rows = (int64_t)ns * n_pad;
+  SE_LAUNCH(oz::oz_row_scale_kernel, (int)ceil_div(rows * 32, 256), 256, 0, stream, w, n_pad, ns, exp_a, exp_b, scale_b);
+  dim3 grid((unsigned)ceil_div(n_pad / 4, 128), (unsigned)n_pad, (unsigned)ns);
+  SE_LAUNCH(oz::oz_pack_b_kernel, grid, 128, 0, stream, w, n_pad, exp_b, S, b_img);
+  return 0;
+}
+
+int launch_kstar_slices(const GpDev<double>& gp, const double* p, int64_t p_stride, const double* u, int64_t u_stride,
+                        int64_t row0, int nrows, int rows_pad, const int* exp_a, int S, int8_t* a_img, double* mean,
+                        double* jac, cudaStream_t stream) {
+  const int warps = rows_pad / 2;
+  const int grid = (int)ceil_div(warps, 8);
+  const bool want_jac = jac != nullptr;
+#define SE_CASE(NS_, NU_)                                                                                        \
+  if (gp.ns == NS_ && gp.nu == NU_) {                                                                            \
+    if (want_jac)                                                                                                \
+      SE_LAUNCH((oz::gp_kstar_slices_kernel<NS_, NS_ + NU_, true>), grid, 256, 0, stream, gp, p, p_stride, u,    \
+                u_stride, row0, nrows, rows_pad, exp_a, S, a_img, mean, jac);                                    \
+    else                                                                                                         \
+      SE_LAUNCH((oz::gp_kstar_slices_kernel<NS_, NS_ + NU_, false>), grid, 256, 0, stream, gp, p, p_stride, u,   \
+                u_stride, row0, nrows, rows_pad, exp_a, S, a_img, mean, jac);                                    \
+    return 0;                                                                                                    \
+  }
+  SE_FOR_NS_NU(SE_CASE)
+#undef SE_CASE
+  return fail("unsupported (n_s, n_u) = (%d, %d)", gp.ns, gp.nu);
+}
+
+template <int S>
+static int launch_oz_gemm_s(const int8_t* a_img, const int8_t* b_img, const double* scale_b, int n_pad, int rows_pad,
+                            const TriOrder& od, int grid, double* partial, cudaStream_t stream) {
+  using C = oz::Cfg<S>;
+  static bool attr_set = false;
+  if (!attr_set) {
+    SE_CUDA(cudaFuncSetAttribute((oz::gp_trisumsq_ozaki_kernel<S>), cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                 C::SMEM_BYTES));
+    attr_set = true;
+  }
+  SE_LAUNCH((oz::gp_trisumsq_ozaki_kernel<S>), grid, oz::THREADS, C::SMEM_BYTES, stream, a_img, b_img, scale_b, n_pad,
+            rows_pad, od, partial);
+  return 0;
+}
+
+int launch_trisumsq_ozaki(const int8_t* a_img, const int8_t* b_img, const double* scale_b, int n_pad, int rows_pad,
+                          int ns, int S, double* partial, int sm_count, int* nb_out, cudaStream_t stream) {
+  static const int64_t l2_budget = getenv("SE_OZ_L2MB") ? atoll(getenv("SE_OZ_L2MB")) << 20 : (64ll << 20);
+  TriOrder od;
+  od.nb = n_pad / oz::TN;
+  od.rt_count = rows_pad / oz::TM;
+  od.ns = ns;
+  int64_t rc = l2_budget / ((int64_t)oz::TM * n_pad * S * ns);
+  if (l2_budget <= 0 || rc > od.rt_count) rc = od.rt_count;
+  if (rc < 1) rc = 1;
+  od.rc = (int)rc;
+  const int64_t items = (int64_t)od.nb * od.rt_count * ns;
+  const int grid = (int)(items < sm_count ? items : sm_count);
+  *nb_out = od.nb;
+  switch (S) {
+    case 5: return launch_oz_gemm_s<5>(a_img, b_img, scale_b, n_pad, rows_pad, od, grid, partial, stream);
+    case 6: return launch_oz_gemm_s<6>(a_img, b_img, scale_b, n_pad, rows_pad, od, grid, partial, stream);
+    case 7: return launch_oz_gemm_s<7>(a_img, b_img, scale_b, n_pad, rows_pad, od, grid, partial, stream);
+  }
+  return fail("tcgen05 variance GEMM: digit planes S = %d not compiled (5, 6, 7)", S);
+}
+
+template <int S>
+static int launch_probe_s(const int8_t* a_img, const int8_t* b_img, int nk, uint32_t lbo, uint32_t sbo, int32_t* out,
+                          cudaStream_t stream) {
+  const int smem = S * (oz::A_BLK + oz::B_BLK) + 1024 + 64;
+  SE_CUDA(cudaFuncSetAttribute((oz::oz_probe_kernel<S>), cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+  SE_LAUNCH((oz::oz_probe_kernel<S>), 1, 128, smem, stream, a_img, b_img, nk, lbo, sbo, out);
+  return 0;
+}
+
+int launch_oz_probe(const int8_t* a_img, const int8_t* b_img, int nk, int S, int lbo, int sbo, int32_t* out,
+                    cudaStream_t stream) {
+  switch (S) {
+    case 5: return launch_probe_s<5>(a_img, b_img, nk, lbo, sbo, out, stream);
+    case 6: return launch_probe_s<6>(a_img, b_img, nk, lbo, sbo, out, stream);
+    case 7: return launch_probe_s<7>(a_img, b_img, nk, lbo, sbo, out, stream);
+  }
+  return fail("probe: S = %d not compiled", S);
+}
+
+}  // namespace se

@@ -1,0 +1,500 @@
+// ozaki_kernels.cuh -- FP64-accurate variance GEMM on the 5th-generation tensor cores (tcgen05, kind::i8).
+//
+// The variance of the exact GP (gp_ssm_cem.py:93 via gpytorch) needs  q_c = || L^-1 k*_c ||^2  to ~1e-10 of the prior
+// scale (the result is a difference of two numbers 10^3 apart), which rules out every fp32-accumulating tensor-core
+// format.  tcgen05 has no f64 kind, but its s8 x s8 -> s32 path is EXACT, so the product is evaluated error-free from
+// 7-bit signed digits (Ozaki scheme I):
+//
+//     k*_cj   = 2^eA   sum_t dA_t[c][j] 2^(-6-7t)        dA_t in [-64, 64]   (S digits, written by gp_kstar_slices)
+//     W_ij    = 2^eB_i sum_u dB_u[i][j] 2^(-6-7u)        dB_u in [-64, 64]   (S digits, packed once per model)
+//     v_ci    = sum_j W_ij k*_cj = 2^(eA+eB_i-12) sum_l 2^(-7l) D_l[c][i],   D_l = sum_{t+u=l} dA_t dB_u^T   (int32, exact)
+//
+// Only the digit pairs with t + u <= S - 1 are formed (S (S + 1) / 2 int8 GEMMs); the dropped pairs are below
+// 2^(-7S) of the row scales.  All S levels D_l of a 128 x 64 output tile live in TMEM at once (S x 64 columns), so every
+// digit tile that the bulk-copy engine brings into shared memory is used by up to S MMAs.  The epilogue recombines the
+// levels in int64 (exact), converts once to double, squares and row-sums: partial[o][ib][c] like the DMMA kernel.
+//
+// Shared-memory operand images are the no-swizzle K-major canonical UMMA layout (8 rows x 16 bytes core matrices,
+// LBO = 128 B between the two K halves of a K = 32 instruction, SBO = 256 B between 8-row groups); the global-memory
+// images are stored in exactly that order, so one contiguous cp.async.bulk per operand fills a pipeline stage.
+#pragma once
+#include "common.cuh"
+#include "gp_kernels.cuh"
+
+namespace se {
+namespace oz {
+
+constexpr int TM = 128;          // candidates per tile  (UMMA M)
+constexpr int TN = 64;           // L^-1 rows per tile   (UMMA N)
+constexpr int KB = 32;           // K elements per kind::i8 instruction
+constexpr int A_BLK = TM * KB;   // bytes of one digit plane of one K step, candidates
+constexpr int B_BLK = TN * KB;   // ... L^-1 rows
+constexpr int MAX_S = 7;
+constexpr int THREADS = 192;     // warp 0: bulk-copy producer, warp 1: MMA issuer, warps 2-5: epilogue
+constexpr int TMEM_COLS = 512;
+constexpr uint32_t LBO = 128, SBO = 256;
+
+// byte offset of element (row r, k index c < 32) inside a digit-plane block of a K step
+__host__ __device__ __forceinline__ int blk_off(int r, int c) {
+  return (r >> 3) * 256 + (c >> 4) * 128 + (r & 7) * 16 + (c & 15);
+}
+
+template <int S>
+struct Cfg {
+  static constexpr int STAGE_BYTES = S * (A_BLK + B_BLK);
+  static constexpr int STAGES = (220 * 1024) / STAGE_BYTES;
+  static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*alignment slack*/ + 256 /*barriers*/;
+  static constexpr int PAIRS = S * (S + 1) / 2;
+};
+
+// ---- PTX wrappers ---------------------------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return static_cast<uint32_t>(__cvta_generic_to_shared(p)); }
+
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;\n" ::"r"(bar), "r"(count));
+}
+__device__ __forceinline__ void mbar_fence_init() { asm volatile("fence.mbarrier_init.release.cluster;\n" ::: "memory"); }
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;\n" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];\n" ::"r"(bar) : "memory");
+}
+// Bounded wait: a protocol bug must end in a trap (launch failure), never in a hung GPU.
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+  uint32_t done = 0;
+  const long long t0 = clock64();
+  while (true) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}\n"
+        : "=r"(done)
+        : "r"(bar), "r"(parity)
+        : "memory");
+    if (done) break;
+    if (clock64() - t0 > 4000000000ll) __trap();
+  }
+}
+__device__ __forceinline__ void bulk_g2s(uint32_t dst, const void* src, uint32_t bytes, uint32_t bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];\n" ::"r"(dst),
+               "l"(src), "r"(bytes), "r"(bar)
+               : "memory");
+}
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;\n" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;\n" ::: "memory"); }
+__device__ __forceinline__ void tmem_alloc(uint32_t dst_smem, uint32_t cols) {  // whole warp
+  asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;\n" ::"r"(dst_smem), "r"(cols) : "memory");
+  asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;\n" ::: "memory");
+}
+__device__ __forceinline__ void tmem_dealloc(uint32_t taddr, uint32_t cols) {  // whole warp
+  asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;\n" ::"r"(taddr), "r"(cols) : "memory");
+}
+__device__ __forceinline__ void tc_commit(uint32_t bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];\n" ::"r"(bar) : "memory");
+}
+// D[tmem] (+)= A[smem] * B[smem]^T, s8 x s8 -> s32, M = 128, N = 64, K = 32; issued by ONE thread
+__device__ __forceinline__ void mma_i8(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::i8 [%0], %1, %2, %3, p;\n\t}\n" ::"r"(d_tmem),
+      "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+__device__ __forceinline__ void tmem_ld8(uint32_t taddr, int32_t (&v)[8]) {
+  asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];\n"
+               : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7])
+               : "r"(taddr));
+}
+__device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;\n" ::: "memory"); }
+
+// K-major, no swizzle: start address, LBO (between the two 16-byte K halves), SBO (between 8-row groups), version 1
+__device__ __forceinline__ uint64_t make_desc(uint32_t smem_addr, uint32_t lbo, uint32_t sbo) {
+  return (uint64_t)((smem_addr >> 4) & 0x3FFFu) | ((uint64_t)((lbo >> 4) & 0x3FFFu) << 16) |
+         ((uint64_t)((sbo >> 4) & 0x3FFFu) << 32) | (1ull << 46);
+}
+// instruction descriptor: c = s32 (2 << 4), a = b = signed 8 bit (1 << 7, 1 << 10), both K-major, N >> 3, M >> 4
+__host__ __device__ constexpr uint32_t make_idesc(int m, int n) {
+  return (2u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(n >> 3) << 17) | ((uint32_t)(m >> 4) << 24);
+}
+
+// signed 7-bit digits of a fixed-point integer q = sum_t d_t 2^(7 (S-1-t)), |d_t| <= 64; word[t] byte `e` <- d_t
+template <int S>
+__device__ __forceinline__ void push_digits(long long q, int e, uint32_t (&word)[S]) {
+#pragma unroll
+  for (int t = S - 1; t >= 1; --t) {
+    const int d = (int)((q + 64) & 127) - 64;
+    q = (q - d) >> 7;
+    word[t] |= (uint32_t)(d & 0xFF) << (8 * e);
+  }
+  word[0] |= (uint32_t)((int)q & 0xFF) << (8 * e);
+}
+
+// ---------------------------------------------------------------------------------------------------------------------
+// model packing: per-row exponents of L^-1, scale factors of the epilogue, digit image of L^-1
+// ---------------------------------------------------------------------------------------------------------------------
+// scale_b[o][i] = 2^(eA_o + eB_oi - 12 - 21); exp_b[o][i] = eB_oi.  One warp per row.
+__global__ void oz_row_scale_kernel(const double* __restrict__ w, int n_pad, int ns, const int* __restrict__ exp_a,
+                                    int* __restrict__ exp_b, double* __restrict__ scale_b) {
+  const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+  if (warp >= ns * n_pad) return;
+  const int o = warp / n_pad, i = warp % n_pad;
+  const double* row = w + ((int64_t)o * n_pad + i) * n_pad;
+  double mx = 0.0;
+  for (int j = lane; j <= i; j += 32) mx = fmax(mx, fabs(row[j]));
+#pragma unroll
+  for (int s = 16; s > 0; s >>= 1) mx = fmax(mx, __shfl_xor_sync(0xffffffffu, mx, s));
+  if (lane == 0) {
+    int e = 0;
+    if (mx > 0.0) frexp(mx, &e);  // mx = m 2^e, m in [0.5, 1)  =>  |w| / 2^e < 1
+    exp_b[warp] = e;
+    scale_b[warp] = ldexp(1.0, exp_a[o] + e - 33);
+  }
+}
+
+// Digits are always taken from the 48-bit fixed-point value (7 digits); a model / workspace with S < 7 planes keeps the
+// S most significant ones (the dropped balanced digits are at most half a unit of the last kept digit).
+__global__ void oz_pack_b_kernel(const double* __restrict__ w, int n_pad, const int* __restrict__ exp_b, int S,
+                                 int8_t* __restrict__ b_img) {
+  // one thread per 4 consecutive j of one row
+  const int j0 = (blockIdx.x * blockDim.x + threadIdx.x) * 4;
+  const int i = blockIdx.y, o = blockIdx.z;
+  if (j0 >= n_pad) return;
+  const double* row = w + ((int64_t)o * n_pad + i) * n_pad;
+  const double sc = ldexp(1.0, 7 * MAX_S - 1 - exp_b[o * n_pad + i]);
+  uint32_t word[MAX_S];
+#pragma unroll
+  for (int t = 0; t < MAX_S; ++t) word[t] = 0;
+#pragma unroll
+  for (int e = 0; e < 4; ++e) push_digits<MAX_S>(__double2ll_rn(row[j0 + e] * sc), e, word);
+  const int nb = n_pad / TN, nkb = n_pad / KB;
+  const int ib = i / TN, il = i % TN, kb = j0 / KB, c = j0 % KB;
+  int8_t* dst = b_img + (((int64_t)o * nb + ib) * nkb + kb) * (int64_t)(S * B_BLK) + blk_off(il, c);
+#pragma unroll
+  for (int t = 0; t < MAX_S; ++t)
+    if (t < S) *reinterpret_cast<uint32_t*>(dst + t * B_BLK) = word[t];
+}
+
+// ---------------------------------------------------------------------------------------------------------------------
+// K1 (Ozaki flavour): kernel rows as S digit planes in the UMMA image layout + mean + mean-Jacobian.
+// One warp owns R = 2 candidate rows (an even/odd pair shares every 32-byte sector of the image); a lane owns 4
+// consecutive training points per 128-point block, so each digit plane is written with one 32-bit store per lane.
+// ---------------------------------------------------------------------------------------------------------------------
+template <int NS, int D, bool JAC>
+__global__ void __launch_bounds__(256)
+gp_kstar_slices_kernel(GpDev<double> gp, const double* __restrict__ p, int64_t p_stride, const double* __restrict__ u,
+                       int64_t u_stride, int64_t row0, int nrows, int rows_pad, const int* __restrict__ exp_a, int S,
+                       int8_t* __restrict__ a_img, double* __restrict__ mean, double* __restrict__ jac) {
+  constexpr int R = 2;
+  const int lane = threadIdx.x & 31;
+  const int64_t warp = blockIdx.x * (int64_t)(blockDim.x >> 5) + (threadIdx.x >> 5);
+  const int64_t r0 = warp * R;
+  if (r0 >= rows_pad) return;
+  const int n_pad = gp.n_pad;
+  const int nkb = n_pad / KB, rt_count = rows_pad / TM;
+
+  double z[R][D];
+  bool rvalid[R];
+#pragma unroll
+  for (int r = 0; r < R; ++r) {
+    rvalid[r] = (r0 + r) < nrows;
+    const int64_t c = row0 + r0 + r;
+#pragma unroll
+    for (int dd = 0; dd < D; ++dd) {
+      double v = 0.0;
+      if (rvalid[r]) v = dd < NS ? p[c * p_stride + dd] : u[c * u_stride + (dd - NS)];
+      z[r][dd] = v;
+    }
+  }
+  double qscale[NS];
+#pragma unroll
+  for (int o = 0; o < NS; ++o) qscale[o] = ldexp(1.0, 7 * MAX_S - 1 - exp_a[o]);
+
+  double m_acc[R][NS];
+  double j_acc[R][NS][JAC ? D : 1];
+#pragma unroll
+  for (int r = 0; r < R; ++r)
+#pragma unroll
+    for (int o = 0; o < NS; ++o) {
+      m_acc[r][o] = 0.0;
+#pragma unroll
+      for (int dd = 0; dd < (JAC ? D : 1); ++dd) j_acc[r][o][dd] = 0.0;
+    }
+
+  for (int jb = 0; jb < n_pad; jb += 128) {
+    const int j0 = jb + 4 * lane;
+    double x[D][4], al[NS][4];
+#pragma unroll
+    for (int dd = 0; dd < D; ++dd) {
+      const double2 t0 = *reinterpret_cast<const double2*>(gp.xt + (int64_t)dd * n_pad + j0);
+      const double2 t1 = *reinterpret_cast<const double2*>(gp.xt + (int64_t)dd * n_pad + j0 + 2);
+      x[dd][0] = t0.x, x[dd][1] = t0.y, x[dd][2] = t1.x, x[dd][3] = t1.y;
+    }
+#pragma unroll
+    for (int o = 0; o < NS; ++o) {
+      const double2 t0 = *reinterpret_cast<const double2*>(gp.alpha + (int64_t)o * n_pad + j0);
+      const double2 t1 = *reinterpret_cast<const double2*>(gp.alpha + (int64_t)o * n_pad + j0 + 2);
+      al[o][0] = t0.x, al[o][1] = t0.y, al[o][2] = t1.x, al[o][3] = t1.y;
+    }
+    const int kb = j0 / KB, c = j0 % KB;
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+      const int rc = (int)(r0 + r);  // row inside this chunk
+      const int ct = rc / TM, rl = rc % TM;
+#pragma unroll
+      for (int o = 0; o < NS; ++o) {
+        uint32_t word[MAX_S];
+#pragma unroll
+        for (int t = 0; t < MAX_S; ++t) word[t] = 0;
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+          double diff[D];
+          double ee = 0.0;
+#pragma unroll
+          for (int dd = 0; dd < D; ++dd) {
+            diff[dd] = z[r][dd] - x[dd][e];
+            ee += diff[dd] * diff[dd] * gp.inv_l2[o][dd];
+          }
+          const double k = (rvalid[r] && (j0 + e) < gp.n) ? gp.outputscale[o] * exp(-0.5 * ee) : 0.0;
+          push_digits<MAX_S>(__double2ll_rn(k * qscale[o]), e, word);
+          const double wk = al[o][e] * k;
+          m_acc[r][o] += wk;
+          if (JAC) {
+#pragma unroll
+            for (int dd = 0; dd < D; ++dd) j_acc[r][o][dd] -= wk * diff[dd] * gp.inv_l2[o][dd];
+          }
+        }
+        int8_t* dst = a_img + (((int64_t)o * rt_count + ct) * nkb + kb) * (int64_t)(S * A_BLK) + blk_off(rl, c);
+#pragma unroll
+        for (int t = 0; t < MAX_S; ++t)
+          if (t < S) *reinterpret_cast<uint32_t*>(dst + t * A_BLK) = word[t];
+      }
+    }
+  }
+
+#pragma unroll
+  for (int r = 0; r < R; ++r)
+#pragma unroll
+    for (int o = 0; o < NS; ++o) {
+      double v = m_acc[r][o];
+#pragma unroll
+      for (int s = 16; s > 0; s >>= 1) v += __shfl_xor_sync(0xffffffffu, v, s);
+      if (lane == 0 && rvalid[r]) mean[(row0 + r0 + r) * NS + o] = v;
+      if (JAC) {
+#pragma unroll
+        for (int dd = 0; dd < D; ++dd) {
+          double g = j_acc[r][o][dd];
+#pragma unroll
+          for (int s = 16; s > 0; s >>= 1) g += __shfl_xor_sync(0xffffffffu, g, s);
+          if (lane == 0 && rvalid[r]) jac[((row0 + r0 + r) * NS + o) * D + dd] = g;
+        }
+      }
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------------------------
+// K2 (Ozaki flavour): partial[o][ib][c] = sum_{i in 64-row block ib} ( sum_{j <= i} W_o[i][j] K*_o[c][j] )^2
+// Persistent, warp-specialised: bulk-copy producer / single-thread tcgen05.mma issuer / 4 epilogue warps.
+// ---------------------------------------------------------------------------------------------------------------------
+// item sequence of CTA b: round r -> position r * G + (r odd ? G - 1 - b : b)  (snake, so heavy/light items alternate)
+__device__ __forceinline__ bool next_item(int round, const TriOrder& od, int total, TriItem* it) {
+  const int G = gridDim.x, b = blockIdx.x;
+  const int idx = round * G + ((round & 1) ? G - 1 - b : b);
+  if (idx >= total) return false;
+  *it = decode_item_chunked(idx, od);
+  return true;
+}
+
+template <int S>
+__global__ void __launch_bounds__(THREADS, 1)
+gp_trisumsq_ozaki_kernel(const int8_t* __restrict__ a_img, const int8_t* __restrict__ b_img,
+                         const double* __restrict__ scale_b, int n_pad, int rows_pad, TriOrder od,
+                         double* __restrict__ partial) {
+  using C = Cfg<S>;
+  extern __shared__ unsigned char smem_raw[];
+  const uint32_t raw = smem_u32(smem_raw);
+  const uint32_t base = (raw + 1023u) & ~1023u;                    // stage 0
+  const uint32_t bars = base + C::STAGES * C::STAGE_BYTES;         // full[STAGES], empty[STAGES], tmem_full, tmem_empty
+  const uint32_t tmem_slot = bars + (2 * C::STAGES + 2) * 8;
+  auto full_bar = [&](int s) { return bars + 8u * s; };
+  auto empty_bar = [&](int s) { return bars + 8u * (C::STAGES + s); };
+  const uint32_t tmem_full = bars + 8u * (2 * C::STAGES), tmem_empty = tmem_full + 8u;
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int total = tri_total_items(od.nb, od.rt_count, od.ns);
+  const int rounds = (total + gridDim.x - 1) / gridDim.x;
+  const int nkb = n_pad / KB;
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < C::STAGES; ++s) {
+      mbar_init(full_bar(s), 1);
+      mbar_init(empty_bar(s), 1);
+    }
+    mbar_init(tmem_full, 1);
+    mbar_init(tmem_empty, 128);
+    mbar_fence_init();
+  }
+  if (warp == 1) tmem_alloc(tmem_slot, TMEM_COLS);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  uint32_t tmem_base;
+  asm volatile("ld.shared.u32 %0, [%1];\n" : "=r"(tmem_base) : "r"(tmem_slot));
+
+  if (warp == 0) {
+    // ===== producer: one elected lane streams (A digits | B digits) of every K step into the stage ring =====
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int r = 0; r < rounds; ++r) {
+        TriItem it;
+        if (!next_item(r, od, total, &it)) continue;
+        const int8_t* a_src = a_img + ((int64_t)it.o * od.rt_count + it.rt) * nkb * (int64_t)(S * A_BLK);
+        const int8_t* b_src = b_img + ((int64_t)it.o * od.nb + it.ib) * nkb * (int64_t)(S * B_BLK);
+        const int nk = (it.ib + 1) * (TN / KB);
+        for (int kb = 0; kb < nk; ++kb) {
+          mbar_wait(empty_bar(stage), phase ^ 1u);
+          mbar_expect_tx(full_bar(stage), C::STAGE_BYTES);
+          const uint32_t dst = base + stage * C::STAGE_BYTES;
+          bulk_g2s(dst, a_src + (int64_t)kb * (S * A_BLK), S * A_BLK, full_bar(stage));
+          bulk_g2s(dst + S * A_BLK, b_src + (int64_t)kb * (S * B_BLK), S * B_BLK, full_bar(stage));
+          if (++stage == C::STAGES) stage = 0, phase ^= 1u;
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===== MMA issuer: S (S + 1) / 2 int8 MMAs per K step into S level accumulators (64 TMEM columns each) =====
+    if (lane == 0) {
+      constexpr uint32_t idesc = make_idesc(TM, TN);
+      int stage = 0;
+      uint32_t phase = 0, tphase = 0;
+      for (int r = 0; r < rounds; ++r) {
+        TriItem it;
+        if (!next_item(r, od, total, &it)) continue;
+        const int nk = (it.ib + 1) * (TN / KB);
+        mbar_wait(tmem_empty, tphase ^ 1u);  // the epilogue has drained the previous item's accumulators
+        tc_fence_after();
+        for (int kb = 0; kb < nk; ++kb) {
+          mbar_wait(full_bar(stage), phase);
+          tc_fence_after();
+          const uint32_t sa = base + stage * C::STAGE_BYTES, sb = sa + S * A_BLK;
+#pragma unroll
+          for (int t = 0; t < S; ++t) {
+            const uint64_t ad = make_desc(sa + t * A_BLK, LBO, SBO);
+#pragma unroll
+            for (int uu = 0; uu + t < S; ++uu) {
+              const uint64_t bd = make_desc(sb + uu * B_BLK, LBO, SBO);
+              // level t + uu is first written by the pair (0, t + uu) of K step 0
+              mma_i8(tmem_base + (uint32_t)((t + uu) * TN), ad, bd, idesc, (kb > 0 || t > 0) ? 1u : 0u);
+            }
+          }
+          tc_commit(empty_bar(stage));  // frees the stage once these MMAs have read it
+          if (++stage == C::STAGES) stage = 0, phase ^= 1u;
+        }
+        tc_commit(tmem_full);
+        tphase ^= 1u;
+      }
+    }
+  } else {
+    // ===== epilogue: exact int64 recombination of the levels, one double conversion, square, row sum =====
+    const int quad = warp & 3;  // TMEM lanes a warp may touch: 32 (warp % 4) ..
+    const int row = quad * 32 + lane;
+    const double lo_scale = S > 4 ? ldexp(1.0, 21 - 7 * (S - 1)) : 0.0;
+    uint32_t tphase = 0;
+    for (int r = 0; r < rounds; ++r) {
+      TriItem it;
+      if (!next_item(r, od, total, &it)) continue;
+      mbar_wait(tmem_full, tphase);
+      tc_fence_after();
+      const double* sbp = scale_b + (int64_t)it.o * n_pad + (int64_t)it.ib * TN;
+      const uint32_t tlane = tmem_base + ((uint32_t)(quad * 32) << 16);
+      double sum = 0.0;
+#pragma unroll 1
+      for (int c8 = 0; c8 < TN; c8 += 8) {
+        int32_t d[S][8];
+#pragma unroll
+        for (int l = 0; l < S; ++l) tmem_ld8(tlane + (uint32_t)(l * TN + c8), d[l]);
+        tmem_ld_wait();
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          long long hi = 0, lo = 0;
+#pragma unroll
+          for (int l = 0; l < S && l < 4; ++l) hi += (long long)d[l][j] << (7 * (3 - l));
+#pragma unroll
+          for (int l = 4; l < S; ++l) lo += (long long)d[l][j] << (7 * (S - 1 - l));
+          const double v = ((double)hi + (double)lo * lo_scale) * __ldg(sbp + c8 + j);
+          sum += v * v;
+        }
+      }
+      tc_fence_before();
+      mbar_arrive(tmem_empty);
+      partial[((int64_t)it.o * od.nb + it.ib) * rows_pad + (int64_t)it.rt * TM + row] = sum;
+      tphase ^= 1u;
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) tmem_dealloc(tmem_base, TMEM_COLS);
+}
+
+// ---------------------------------------------------------------------------------------------------------------------
+// Probe (tests): one CTA, nk K steps of a single 128 x 64 tile; dumps every level accumulator.  out[S][128][64] int32.
+// lbo / sbo are parameters so the descriptor convention is pinned by a test and not by a comment.
+// ---------------------------------------------------------------------------------------------------------------------
+template <int S>
+__global__ void __launch_bounds__(128, 1)
+oz_probe_kernel(const int8_t* __restrict__ a_img, const int8_t* __restrict__ b_img, int nk, uint32_t lbo, uint32_t sbo,
+                int32_t* __restrict__ out) {
+  extern __shared__ unsigned char smem_raw[];
+  const uint32_t raw = smem_u32(smem_raw);
+  const uint32_t base = (raw + 1023u) & ~1023u;
+  const uint32_t bars = base + S * (A_BLK + B_BLK);
+  const uint32_t full = bars, done = bars + 8, tmem_slot = bars + 16;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  if (threadIdx.x == 0) {
+    mbar_init(full, 1);
+    mbar_init(done, 1);
+    mbar_fence_init();
+  }
+  if (warp == 0) tmem_alloc(tmem_slot, TMEM_COLS);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  uint32_t tmem_base;
+  asm volatile("ld.shared.u32 %0, [%1];\n" : "=r"(tmem_base) : "r"(tmem_slot));
+  constexpr uint32_t idesc = make_idesc(TM, TN);
+  for (int kb = 0; kb < nk; ++kb) {
+    if (threadIdx.x == 0) {
+      mbar_expect_tx(full, S * (A_BLK + B_BLK));
+      bulk_g2s(base, a_img + (int64_t)kb * S * A_BLK, S * A_BLK, full);
+      bulk_g2s(base + S * A_BLK, b_img + (int64_t)kb * S * B_BLK, S * B_BLK, full);
+      mbar_wait(full, kb & 1);
+      tc_fence_after();
+      for (int t = 0; t < S; ++t)
+        for (int uu = 0; uu + t < S; ++uu)
+          mma_i8(tmem_base + (uint32_t)((t + uu) * TN), make_desc(base + t * A_BLK, lbo, sbo),
+                 make_desc(base + S * A_BLK + uu * B_BLK, lbo, sbo), idesc, (kb > 0 || t > 0) ? 1u : 0u);
+      tc_commit(done);
+      mbar_wait(done, kb & 1);  // single stage: the next K step overwrites the operands
+    }
+    __syncthreads();
+  }
+  tc_fence_after();
+  const int row = warp * 32 + lane;
+  const uint32_t tlane = tmem_base + ((uint32_t)(warp * 32) << 16);
+  for (int l = 0; l < S; ++l)
+    for (int c8 = 0; c8 < TN; c8 += 8) {
+      int32_t v[8];
+      tmem_ld8(tlane + (uint32_t)(l * TN + c8), v);
+      tmem_ld_wait();
+#pragma unroll
+      for (int j = 0; j < 8; ++j) out[((int64_t)l * TM + row) * TN + c8 + j] = v[j];
+    }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 0) tmem_dealloc(tmem_base, TMEM_COLS);
+}
+
+}  // namespace oz
+}  // namespace se

@@ -42,6 +42,12 @@ struct se_gp_s {
   int* counter = nullptr;
   se_gemm_impl impl = SE_GEMM_AUTO;
   int sm_count = 148;
+  // tcgen05 digit-sliced variance GEMM: digit image of L^-1, per-row scales (built on first use)
+  int tc_digits = 7;
+  int tc_ready_digits = 0;
+  int8_t* b_img = nullptr;
+  int* exp_ab = nullptr;  // [ns] exponents of the output scales, then [ns][n_pad] row exponents of L^-1
+  double* scale_b = nullptr;
   // timing
   bool timing = false;
   std::vector<cudaEvent_t> ev_gemm, ev_kstar;  // (start, stop) pairs
@@ -140,7 +146,8 @@ extern "C" int se_gp_create(se_gp_t* out, int n_s, int n_u, int n, se_dtype dtyp
 
 extern "C" int se_gp_destroy(se_gp_t g) {
   if (!g) return 0;
-  for (void* p : {g->xt, g->alpha, g->w, g->kst, g->partial, g->post_mean, g->post_var, g->post_jac, (void*)g->counter})
+  for (void* p : {g->xt, g->alpha, g->w, g->kst, g->partial, g->post_mean, g->post_var, g->post_jac, (void*)g->counter,
+                  (void*)g->b_img, (void*)g->exp_ab, (void*)g->scale_b})
     if (p) cudaFree(p);
   for (auto e : g->ev_gemm) cudaEventDestroy(e);
   for (auto e : g->ev_kstar) cudaEventDestroy(e);
@@ -155,9 +162,41 @@ extern "C" int se_gp_set_workspace_limit(se_gp_t g, uint64_t bytes) {
 }
 extern "C" int se_gp_set_gemm_impl(se_gp_t g, se_gemm_impl impl) {
   SE_REQUIRE(g, "NULL handle");
+  SE_REQUIRE(impl != SE_GEMM_TC || g->dtype == SE_F64, "SE_GEMM_TC evaluates float64 models");
   g->impl = impl;
   return 0;
 }
+extern "C" int se_gp_set_tc_digits(se_gp_t g, int digits) {
+  SE_REQUIRE(g, "NULL handle");
+  SE_REQUIRE(digits >= 5 && digits <= 7, "se_gp_set_tc_digits: %d outside [5, 7]", digits);
+  g->tc_digits = digits;
+  return 0;
+}
+
+// digit image of L^-1 for the tcgen05 path; rebuilt when the number of digit planes changes
+static int tc_prepare(se_gp_s* g, cudaStream_t st) {
+  if (g->tc_ready_digits == g->tc_digits) return 0;
+  SE_REQUIRE(g->dtype == SE_F64, "the tcgen05 variance GEMM evaluates float64 models");
+  SE_REQUIRE(g->n_pad <= 32768, "the tcgen05 variance GEMM holds int32 level sums: n_train must be <= 32768");
+  SE_CUDA(cudaStreamSynchronize(st));  // a previous image may still be in use
+  if (g->b_img) SE_CUDA(cudaFree(g->b_img));
+  g->b_img = nullptr;
+  const size_t np = (size_t)g->n_pad;
+  SE_CUDA(cudaMalloc(&g->b_img, (size_t)g->ns * np * np * g->tc_digits));
+  if (!g->exp_ab) SE_CUDA(cudaMalloc(&g->exp_ab, (size_t)(g->ns + g->ns * np) * sizeof(int)));
+  if (!g->scale_b) SE_CUDA(cudaMalloc(&g->scale_b, (size_t)g->ns * np * sizeof(double)));
+  SE_TRY(launch_oz_pack_model((const double*)g->w, g->n_pad, g->ns, g->outputscale, g->tc_digits, g->exp_ab,
+                              g->exp_ab + g->ns, g->scale_b, g->b_img, st));
+  g->tc_ready_digits = g->tc_digits;
+  return 0;
+}
+
+extern "C" int se_debug_tc_probe(const int8_t* dev_a_img, const int8_t* dev_b_img, int nk, int digits, int lbo, int sbo,
+                                 int32_t* dev_out, void* stream) {
+  SE_REQUIRE(dev_a_img && dev_b_img && dev_out && nk >= 1, "se_debug_tc_probe: bad arguments");
+  return launch_oz_probe(dev_a_img, dev_b_img, nk, digits, lbo, sbo, dev_out, static_cast<cudaStream_t>(stream));
+}
+
 extern "C" int se_gp_timing_enable(se_gp_t g, int enable) {
   SE_REQUIRE(g, "NULL handle");
   g->timing = enable != 0;
@@ -236,16 +275,29 @@ static int gp_posterior(se_gp_s* g, const T* p, int64_t p_stride, const T* u, in
   SE_TRY(gp_reserve(g, N));
   const GpDev<T> gd = gp_dev<T>(g);
   const int64_t rows_chunk = chunk_rows(g, N);
+  const bool tc = g->impl == SE_GEMM_TC;
+  if (tc) SE_TRY(tc_prepare(g, st));
   for (int64_t row0 = 0; row0 < N; row0 += rows_chunk) {
     const int nrows = (int)((N - row0) < rows_chunk ? (N - row0) : rows_chunk);
     const int rows_pad = (int)round_up(nrows, kTile);
     if (g->timing) SE_TRY(record_event(g->ev_kstar, st));
-    SE_TRY(launch_kstar<T>(gd, p, p_stride, u, u_stride, row0, nrows, rows_pad, (T*)g->kst, mean, jac, st));
+    if constexpr (sizeof(T) == 8) {
+      if (tc)  // kernel rows as int8 digit planes (the workspace holds <= 7 bytes per element instead of 8)
+        SE_TRY(launch_kstar_slices(gd, p, p_stride, u, u_stride, row0, nrows, rows_pad, g->exp_ab, g->tc_digits,
+                                   (int8_t*)g->kst, mean, jac, st));
+    }
+    if (!tc) SE_TRY(launch_kstar<T>(gd, p, p_stride, u, u_stride, row0, nrows, rows_pad, (T*)g->kst, mean, jac, st));
     if (g->timing) SE_TRY(record_event(g->ev_kstar, st));
     int nb = 0;
     if (g->timing) SE_TRY(record_event(g->ev_gemm, st));
-    SE_TRY(launch_trisumsq<T>(g->impl, (const T*)g->kst, gd.w, g->n_pad, rows_pad, g->ns, (T*)g->partial, g->counter,
-                              g->sm_count, &nb, st));
+    if constexpr (sizeof(T) == 8) {
+      if (tc)
+        SE_TRY(launch_trisumsq_ozaki((const int8_t*)g->kst, g->b_img, g->scale_b, g->n_pad, rows_pad, g->ns,
+                                     g->tc_digits, (double*)g->partial, g->sm_count, &nb, st));
+    }
+    if (!tc)
+      SE_TRY(launch_trisumsq<T>(g->impl, (const T*)g->kst, gd.w, g->n_pad, rows_pad, g->ns, (T*)g->partial,
+                                g->counter, g->sm_count, &nb, st));
     if (g->timing) SE_TRY(record_event(g->ev_gemm, st));
     SE_TRY(launch_var<T>(gd, (const T*)g->partial, nb, rows_pad, row0, nrows, var, st));
   }
