@@ -39,7 +39,7 @@ def parse_args():
     ap.add_argument('--dtype', default='f64', choices=['f64', 'f32'])
     ap.add_argument('--config', default='C2', choices=['C1', 'C2', 'C3'])
     ap.add_argument('--gemm', default='auto', choices=['auto', 'simt', 'mma', 'tc'])
-    ap.add_argument('--tc-digits', type=int, default=7, choices=[5, 6, 7])
+    ap.add_argument('--tc-digits', type=int, default=7, choices=[5, 6, 7, 8])
     ap.add_argument('--cpu-sample', type=int, default=2048, help='candidates in the CPU-baseline sample')
     ap.add_argument('--no-cpu-baseline', action='store_true')
     return ap.parse_args()

@@ -76,7 +76,7 @@ int se_gp_destroy(se_gp_t gp);
 int se_gp_set_workspace_limit(se_gp_t gp, uint64_t bytes);
 int se_gp_set_gemm_impl(se_gp_t gp, se_gemm_impl impl);
 /* digit planes per operand of SE_GEMM_TC: 7 (default; variance within ~1e-9 relative of the float64 evaluation on the
- * bench workload), 6 (~5e-8, 25 % fewer MMAs) or 5 (~7e-6) */
+ * bench workload), 8 (~1e-11: float64-equivalent, 29 % more MMAs), 6 (~1e-7, 25 % fewer MMAs) or 5 (~1e-5) */
 int se_gp_set_tc_digits(se_gp_t gp, int digits);
 
 /* mean [N, n_s], variance [N, n_s] (likelihood noise INCLUDED, gp_ssm_cem.py:93) and, if dev_jac != NULL, the

@@ -49,17 +49,17 @@ int launch_kstar_slices(const GpDev<double>& gp, const double* p, int64_t p_stri
   return fail("unsupported (n_s, n_u) = (%d, %d)", gp.ns, gp.nu);
 }
 
-template <int S>
+template <int S, bool REUSE>
 static int launch_oz_gemm_s(const int8_t* a_img, const int8_t* b_img, const double* scale_b, int n_pad, int rows_pad,
                             const TriOrder& od, int grid, double* partial, cudaStream_t stream) {
   using C = oz::Cfg<S>;
   static bool attr_set = false;
   if (!attr_set) {
-    SE_CUDA(cudaFuncSetAttribute((oz::gp_trisumsq_ozaki_kernel<S>), cudaFuncAttributeMaxDynamicSharedMemorySize,
+    SE_CUDA(cudaFuncSetAttribute((oz::gp_trisumsq_ozaki_kernel<S, REUSE>), cudaFuncAttributeMaxDynamicSharedMemorySize,
                                  C::SMEM_BYTES));
     attr_set = true;
   }
-  SE_LAUNCH((oz::gp_trisumsq_ozaki_kernel<S>), grid, oz::THREADS, C::SMEM_BYTES, stream, a_img, b_img, scale_b, n_pad,
+  SE_LAUNCH((oz::gp_trisumsq_ozaki_kernel<S, REUSE>), grid, oz::THREADS, C::SMEM_BYTES, stream, a_img, b_img, scale_b, n_pad,
             rows_pad, od, partial);
   return 0;
 }
@@ -77,21 +77,34 @@ int launch_trisumsq_ozaki(const int8_t* a_img, const int8_t* b_img, const double
   od.rc = (int)rc;
   const int64_t items = (int64_t)od.nb * od.rt_count * ns;
   const int grid = (int)(items < sm_count ? items : sm_count);
-  *nb_out = od.nb;
+  *nb_out = 2 * od.nb;  // the epilogue writes one partial block per 32 columns
+  static const int reuse = getenv("SE_OZ_REUSE") ? atoi(getenv("SE_OZ_REUSE")) : 1;
+#define SE_OZ_CASE(S_)                                                                                               \
+  case S_:                                                                                                           \
+    return reuse ? launch_oz_gemm_s<S_, true>(a_img, b_img, scale_b, n_pad, rows_pad, od, grid, partial, stream)     \
+                 : launch_oz_gemm_s<S_, false>(a_img, b_img, scale_b, n_pad, rows_pad, od, grid, partial, stream);
   switch (S) {
-    case 5: return launch_oz_gemm_s<5>(a_img, b_img, scale_b, n_pad, rows_pad, od, grid, partial, stream);
-    case 6: return launch_oz_gemm_s<6>(a_img, b_img, scale_b, n_pad, rows_pad, od, grid, partial, stream);
-    case 7: return launch_oz_gemm_s<7>(a_img, b_img, scale_b, n_pad, rows_pad, od, grid, partial, stream);
+    SE_OZ_CASE(5)
+    SE_OZ_CASE(6)
+    SE_OZ_CASE(7)
+    SE_OZ_CASE(8)
   }
-  return fail("tcgen05 variance GEMM: digit planes S = %d not compiled (5, 6, 7)", S);
+#undef SE_OZ_CASE
+  return fail("tcgen05 variance GEMM: digit planes S = %d not compiled (5 .. 8)", S);
 }
 
 template <int S>
 static int launch_probe_s(const int8_t* a_img, const int8_t* b_img, int nk, uint32_t lbo, uint32_t sbo, int32_t* out,
                           cudaStream_t stream) {
   const int smem = S * (oz::A_BLK + oz::B_BLK) + 1024 + 64;
-  SE_CUDA(cudaFuncSetAttribute((oz::oz_probe_kernel<S>), cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-  SE_LAUNCH((oz::oz_probe_kernel<S>), 1, 128, smem, stream, a_img, b_img, nk, lbo, sbo, out);
+  static const int reuse = getenv("SE_OZ_REUSE") ? atoi(getenv("SE_OZ_REUSE")) : 1;
+  if (reuse) {
+    SE_CUDA(cudaFuncSetAttribute((oz::oz_probe_kernel<S, true>), cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    SE_LAUNCH((oz::oz_probe_kernel<S, true>), 1, 128, smem, stream, a_img, b_img, nk, lbo, sbo, out);
+  } else {
+    SE_CUDA(cudaFuncSetAttribute((oz::oz_probe_kernel<S, false>), cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    SE_LAUNCH((oz::oz_probe_kernel<S, false>), 1, 128, smem, stream, a_img, b_img, nk, lbo, sbo, out);
+  }
   return 0;
 }
 
@@ -101,6 +114,7 @@ int launch_oz_probe(const int8_t* a_img, const int8_t* b_img, int nk, int S, int
     case 5: return launch_probe_s<5>(a_img, b_img, nk, lbo, sbo, out, stream);
     case 6: return launch_probe_s<6>(a_img, b_img, nk, lbo, sbo, out, stream);
     case 7: return launch_probe_s<7>(a_img, b_img, nk, lbo, sbo, out, stream);
+    case 8: return launch_probe_s<8>(a_img, b_img, nk, lbo, sbo, out, stream);
   }
   return fail("probe: S = %d not compiled", S);
 }

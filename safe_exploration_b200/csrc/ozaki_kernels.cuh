@@ -29,8 +29,9 @@ constexpr int TN = 64;           // L^-1 rows per tile   (UMMA N)
 constexpr int KB = 32;           // K elements per kind::i8 instruction
 constexpr int A_BLK = TM * KB;   // bytes of one digit plane of one K step, candidates
 constexpr int B_BLK = TN * KB;   // ... L^-1 rows
-constexpr int MAX_S = 7;
-constexpr int THREADS = 192;     // warp 0: bulk-copy producer, warp 1: MMA issuer, warps 2-5: epilogue
+constexpr int MAX_S = 8;         // 8 levels x 64 columns = all 512 TMEM columns
+constexpr int THREADS = 320;     // warp 0: bulk-copy producer, warp 1: MMA issuer, warps 2-9: epilogue
+constexpr int EPI_THREADS = 256;
 constexpr int TMEM_COLS = 512;
 constexpr uint32_t LBO = 128, SBO = 256;
 
@@ -46,6 +47,8 @@ struct Cfg {
   static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*alignment slack*/ + 256 /*barriers*/;
   static constexpr int PAIRS = S * (S + 1) / 2;
 };
+
+__device__ __forceinline__ uint64_t make_desc(uint32_t smem_addr, uint32_t lbo, uint32_t sbo);
 
 // ---- PTX wrappers ---------------------------------------------------------------------------------------------------
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return static_cast<uint32_t>(__cvta_generic_to_shared(p)); }
@@ -93,15 +96,65 @@ __device__ __forceinline__ void tmem_dealloc(uint32_t taddr, uint32_t cols) {  /
 __device__ __forceinline__ void tc_commit(uint32_t bar) {
   asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];\n" ::"r"(bar) : "memory");
 }
-// D[tmem] (+)= A[smem] * B[smem]^T, s8 x s8 -> s32, M = 128, N = 64, K = 32; issued by ONE thread
+// D[tmem] (+)= A[smem] * B[smem]^T, s8 x s8 -> s32, M = 128, N = 64, K = 32; issued by ONE thread.
+// COLL: A-operand collector usage.  Consecutive MMAs that multiply the same A digit tile keep it in the tensor core's
+// collector buffer (0 discard, 1 fill, 2 use, 3 lastuse), so shared memory is read for A once per digit, not per pair.
+template <int COLL>
 __device__ __forceinline__ void mma_i8(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc, uint32_t accumulate) {
-  asm volatile(
-      "{\n\t.reg .pred p;\n\t"
-      "setp.ne.b32 p, %4, 0;\n\t"
-      "tcgen05.mma.cta_group::1.kind::i8 [%0], %1, %2, %3, p;\n\t}\n" ::"r"(d_tmem),
-      "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate)
-      : "memory");
+#define SE_MMA_I8(QUAL)                                                                                        \
+  asm volatile(                                                                                                \
+      "{\n\t.reg .pred p;\n\t"                                                                                 \
+      "setp.ne.b32 p, %4, 0;\n\t"                                                                              \
+      "tcgen05.mma.cta_group::1.kind::i8" QUAL " [%0], %1, %2, %3, p;\n\t}\n" ::"r"(d_tmem),                   \
+      "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate)                                                    \
+      : "memory")
+  if constexpr (COLL == 1) SE_MMA_I8(".collector::a::fill");
+  else if constexpr (COLL == 2) SE_MMA_I8(".collector::a::use");
+  else if constexpr (COLL == 3) SE_MMA_I8(".collector::a::lastuse");
+  else SE_MMA_I8("");
+#undef SE_MMA_I8
 }
+
+// one lane of a converged warp (the async-issue idiom: the warp stays converged, so every operand stays uniform)
+__device__ __forceinline__ bool elect_one() {
+  uint32_t pred;
+  asm volatile("{\n\t.reg .pred P;\n\telect.sync _|P, 0xffffffff;\n\tselp.u32 %0, 1, 0, P;\n\t}\n" : "=r"(pred));
+  return pred != 0;
+}
+__device__ __forceinline__ uint64_t pack_desc(uint32_t lo, uint32_t hi) {
+  uint64_t d;
+  asm("mov.b64 %0, {%1, %2};\n" : "=l"(d) : "r"(lo), "r"(hi));
+  return d;
+}
+
+// All digit pairs (t, u), t + u <= S - 1, of one K step: level t + u accumulates A_t B_u^T.
+// a_lo / b_lo: low descriptor words of digit plane 0 (start address >> 4 | LBO); the other planes are a constant
+// number of 16-byte units further on, so a descriptor costs one add.  The issue rate matters: an N = 64 MMA occupies the
+// tensor core for only 32 cycles.
+template <int S, bool REUSE>
+__device__ __forceinline__ void issue_kstep(uint32_t tmem_base, uint32_t a_lo, uint32_t b_lo, uint32_t desc_hi,
+                                            uint32_t idesc, uint32_t not_first) {
+#pragma unroll
+  for (int t = 0; t < S; ++t) {
+    const uint64_t ad = pack_desc(a_lo + t * (A_BLK >> 4), desc_hi);
+#pragma unroll
+    for (int uu = 0; uu + t < S; ++uu) {
+      const uint64_t bd = pack_desc(b_lo + uu * (B_BLK >> 4), desc_hi);
+      // level t + uu is first written by the pair (0, t + uu) of K step 0
+      const uint32_t acc = t > 0 ? 1u : not_first;
+      const uint32_t dcol = tmem_base + (uint32_t)((t + uu) * TN);
+      const int uses = S - t;
+      if (!REUSE || uses == 1) mma_i8<0>(dcol, ad, bd, idesc, acc);
+      else if (uu == 0) mma_i8<1>(dcol, ad, bd, idesc, acc);
+      else if (uu == uses - 1) mma_i8<3>(dcol, ad, bd, idesc, acc);
+      else mma_i8<2>(dcol, ad, bd, idesc, acc);
+    }
+  }
+}
+__device__ __forceinline__ uint32_t desc_lo(uint32_t smem_addr, uint32_t lbo) {
+  return ((smem_addr >> 4) & 0x3FFFu) | (((lbo >> 4) & 0x3FFFu) << 16);
+}
+__device__ __forceinline__ uint32_t desc_hi(uint32_t sbo) { return ((sbo >> 4) & 0x3FFFu) | (1u << 14); }
 __device__ __forceinline__ void tmem_ld8(uint32_t taddr, int32_t (&v)[8]) {
   asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];\n"
                : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7])
@@ -149,7 +202,7 @@ __global__ void oz_row_scale_kernel(const double* __restrict__ w, int n_pad, int
     int e = 0;
     if (mx > 0.0) frexp(mx, &e);  // mx = m 2^e, m in [0.5, 1)  =>  |w| / 2^e < 1
     exp_b[warp] = e;
-    scale_b[warp] = ldexp(1.0, exp_a[o] + e - 33);
+    scale_b[warp] = ldexp(1.0, exp_a[o] + e - 33);  // 2^(eA + eB - 12) from the digit weights, 2^-21 from `hi`
   }
 }
 
@@ -306,7 +359,7 @@ __device__ __forceinline__ bool next_item(int round, const TriOrder& od, int tot
   return true;
 }
 
-template <int S>
+template <int S, bool REUSE>
 __global__ void __launch_bounds__(THREADS, 1)
 gp_trisumsq_ozaki_kernel(const int8_t* __restrict__ a_img, const int8_t* __restrict__ b_img,
                          const double* __restrict__ scale_b, int n_pad, int rows_pad, TriOrder od,
@@ -332,7 +385,7 @@ gp_trisumsq_ozaki_kernel(const int8_t* __restrict__ a_img, const int8_t* __restr
       mbar_init(empty_bar(s), 1);
     }
     mbar_init(tmem_full, 1);
-    mbar_init(tmem_empty, 128);
+    mbar_init(tmem_empty, EPI_THREADS);
     mbar_fence_init();
   }
   if (warp == 1) tmem_alloc(tmem_slot, TMEM_COLS);
@@ -365,40 +418,37 @@ gp_trisumsq_ozaki_kernel(const int8_t* __restrict__ a_img, const int8_t* __restr
     }
   } else if (warp == 1) {
     // ===== MMA issuer: S (S + 1) / 2 int8 MMAs per K step into S level accumulators (64 TMEM columns each) =====
-    if (lane == 0) {
-      constexpr uint32_t idesc = make_idesc(TM, TN);
-      int stage = 0;
-      uint32_t phase = 0, tphase = 0;
-      for (int r = 0; r < rounds; ++r) {
-        TriItem it;
-        if (!next_item(r, od, total, &it)) continue;
-        const int nk = (it.ib + 1) * (TN / KB);
-        mbar_wait(tmem_empty, tphase ^ 1u);  // the epilogue has drained the previous item's accumulators
+    // The whole warp walks the loop (so stage / phase / descriptors stay warp-uniform and live in uniform registers);
+    // one elected lane issues the tcgen05 instructions.
+    constexpr uint32_t idesc = make_idesc(TM, TN);
+    const uint32_t tb = __shfl_sync(0xffffffffu, tmem_base, 0);
+    const uint32_t a_lo0 = desc_lo(__shfl_sync(0xffffffffu, base, 0), LBO), dhi = desc_hi(SBO);
+    int stage = 0;
+    uint32_t phase = 0, tphase = 0;
+    for (int r = 0; r < rounds; ++r) {
+      TriItem it;
+      if (!next_item(r, od, total, &it)) continue;
+      const int nk = (it.ib + 1) * (TN / KB);
+      mbar_wait(tmem_empty, tphase ^ 1u);  // the epilogue has drained the previous item's accumulators
+      tc_fence_after();
+      for (int kb = 0; kb < nk; ++kb) {
+        mbar_wait(full_bar(stage), phase);
         tc_fence_after();
-        for (int kb = 0; kb < nk; ++kb) {
-          mbar_wait(full_bar(stage), phase);
-          tc_fence_after();
-          const uint32_t sa = base + stage * C::STAGE_BYTES, sb = sa + S * A_BLK;
-#pragma unroll
-          for (int t = 0; t < S; ++t) {
-            const uint64_t ad = make_desc(sa + t * A_BLK, LBO, SBO);
-#pragma unroll
-            for (int uu = 0; uu + t < S; ++uu) {
-              const uint64_t bd = make_desc(sb + uu * B_BLK, LBO, SBO);
-              // level t + uu is first written by the pair (0, t + uu) of K step 0
-              mma_i8(tmem_base + (uint32_t)((t + uu) * TN), ad, bd, idesc, (kb > 0 || t > 0) ? 1u : 0u);
-            }
-          }
+        const uint32_t a_lo = a_lo0 + stage * (C::STAGE_BYTES >> 4);
+        if (elect_one()) {
+          issue_kstep<S, REUSE>(tb, a_lo, a_lo + (S * A_BLK >> 4), dhi, idesc, kb > 0 ? 1u : 0u);
           tc_commit(empty_bar(stage));  // frees the stage once these MMAs have read it
-          if (++stage == C::STAGES) stage = 0, phase ^= 1u;
+          if (kb == nk - 1) tc_commit(tmem_full);
         }
-        tc_commit(tmem_full);
-        tphase ^= 1u;
+        __syncwarp();
+        if (++stage == C::STAGES) stage = 0, phase ^= 1u;
       }
+      tphase ^= 1u;
     }
   } else {
     // ===== epilogue: exact int64 recombination of the levels, one double conversion, square, row sum =====
     const int quad = warp & 3;  // TMEM lanes a warp may touch: 32 (warp % 4) ..
+    const int half = (warp - 2) >> 2;  // two warps per lane quadrant, 32 of the 64 columns each
     const int row = quad * 32 + lane;
     const double lo_scale = S > 4 ? ldexp(1.0, 21 - 7 * (S - 1)) : 0.0;
     uint32_t tphase = 0;
@@ -411,7 +461,7 @@ gp_trisumsq_ozaki_kernel(const int8_t* __restrict__ a_img, const int8_t* __restr
       const uint32_t tlane = tmem_base + ((uint32_t)(quad * 32) << 16);
       double sum = 0.0;
 #pragma unroll 1
-      for (int c8 = 0; c8 < TN; c8 += 8) {
+      for (int c8 = half * (TN / 2); c8 < (half + 1) * (TN / 2); c8 += 8) {
         int32_t d[S][8];
 #pragma unroll
         for (int l = 0; l < S; ++l) tmem_ld8(tlane + (uint32_t)(l * TN + c8), d[l]);
@@ -429,7 +479,8 @@ gp_trisumsq_ozaki_kernel(const int8_t* __restrict__ a_img, const int8_t* __restr
       }
       tc_fence_before();
       mbar_arrive(tmem_empty);
-      partial[((int64_t)it.o * od.nb + it.ib) * rows_pad + (int64_t)it.rt * TM + row] = sum;
+      // the two column halves are separate partial blocks (gp_var_kernel sums 2 nb of them in a fixed order)
+      partial[((int64_t)it.o * (2 * od.nb) + 2 * it.ib + half) * rows_pad + (int64_t)it.rt * TM + row] = sum;
       tphase ^= 1u;
     }
   }
@@ -442,7 +493,7 @@ gp_trisumsq_ozaki_kernel(const int8_t* __restrict__ a_img, const int8_t* __restr
 // Probe (tests): one CTA, nk K steps of a single 128 x 64 tile; dumps every level accumulator.  out[S][128][64] int32.
 // lbo / sbo are parameters so the descriptor convention is pinned by a test and not by a comment.
 // ---------------------------------------------------------------------------------------------------------------------
-template <int S>
+template <int S, bool REUSE>
 __global__ void __launch_bounds__(128, 1)
 oz_probe_kernel(const int8_t* __restrict__ a_img, const int8_t* __restrict__ b_img, int nk, uint32_t lbo, uint32_t sbo,
                 int32_t* __restrict__ out) {
@@ -471,10 +522,7 @@ oz_probe_kernel(const int8_t* __restrict__ a_img, const int8_t* __restrict__ b_i
       bulk_g2s(base + S * A_BLK, b_img + (int64_t)kb * S * B_BLK, S * B_BLK, full);
       mbar_wait(full, kb & 1);
       tc_fence_after();
-      for (int t = 0; t < S; ++t)
-        for (int uu = 0; uu + t < S; ++uu)
-          mma_i8(tmem_base + (uint32_t)((t + uu) * TN), make_desc(base + t * A_BLK, lbo, sbo),
-                 make_desc(base + S * A_BLK + uu * B_BLK, lbo, sbo), idesc, (kb > 0 || t > 0) ? 1u : 0u);
+      issue_kstep<S, REUSE>(tmem_base, desc_lo(base, lbo), desc_lo(base + S * A_BLK, lbo), desc_hi(sbo), idesc, kb > 0 ? 1u : 0u);
       tc_commit(done);
       mbar_wait(done, kb & 1);  // single stage: the next K step overwrites the operands
     }

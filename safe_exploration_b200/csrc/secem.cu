@@ -168,7 +168,7 @@ extern "C" int se_gp_set_gemm_impl(se_gp_t g, se_gemm_impl impl) {
 }
 extern "C" int se_gp_set_tc_digits(se_gp_t g, int digits) {
   SE_REQUIRE(g, "NULL handle");
-  SE_REQUIRE(digits >= 5 && digits <= 7, "se_gp_set_tc_digits: %d outside [5, 7]", digits);
+  SE_REQUIRE(digits >= 5 && digits <= 8, "se_gp_set_tc_digits: %d outside [5, 8]", digits);
   g->tc_digits = digits;
   return 0;
 }
@@ -241,7 +241,7 @@ static int64_t chunk_rows(const se_gp_s* g, int64_t N) {
 static int gp_reserve(se_gp_s* g, int64_t N) {
   const int64_t rows = chunk_rows(g, N);
   SE_TRY(grow(&g->kst, &g->kst_bytes, (size_t)g->ns * rows * g->n_pad * g->esz));
-  SE_TRY(grow(&g->partial, &g->partial_bytes, (size_t)g->ns * (g->n_pad / 64) * rows * g->esz));
+  SE_TRY(grow(&g->partial, &g->partial_bytes, (size_t)g->ns * (g->n_pad / 32) * rows * g->esz));
   return 0;
 }
 static int gp_reserve_posterior(se_gp_s* g, int64_t N) {

@@ -18,7 +18,7 @@ def run(w, N, seed=0):
     ssm.set_gemm_impl(_lib.SE_GEMM_MMA)
     m0, v0, j0 = ssm.predict_with_jacobians(z[:, :w.n_s], z[:, w.n_s:])
     torch.cuda.synchronize()
-    for S in (7, 6, 5):
+    for S in (8, 7, 6, 5):
         ssm.set_gemm_impl(_lib.SE_GEMM_TC)
         _lib.check(lib.se_gp_set_tc_digits(ssm.handle, S))
         m1, v1, j1 = ssm.predict_with_jacobians(z[:, :w.n_s], z[:, w.n_s:])

@@ -15,7 +15,7 @@ def main():
     lib = _lib.load()
     rng = np.random.default_rng(0)
     ok_all = True
-    for S in (7, 6, 5):
+    for S in (8, 7, 6, 5):
         for nk in (1, 3):
             a = rng.integers(-64, 65, size=(nk, S, 128, 32), dtype=np.int8)
             b = rng.integers(-64, 65, size=(nk, S, 64, 32), dtype=np.int8)
