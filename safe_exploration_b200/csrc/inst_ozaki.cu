@@ -18,7 +18,7 @@ int launch_oz_pack_model(const double* w, int n_pad, int ns, const double* host_
   int ea[SE_MAX_NS] = {};
   for (int o = 0; o < ns; ++o) {
     SE_REQUIRE(host_outputscale[o] > 0.0, "outputscale[%d] must be > 0", o);
-    frexp(host_outputscale[o], &ea[o]);
+    ea[o] = oz::digit_exponent(host_outputscale[o]);
   }
   SE_CUDA(cudaMemcpyAsync(exp_a, ea, ns * sizeof(int), cudaMemcpyHostToDevice, stream));
   const int64_t rows = (int64_t)ns * n_pad;
@@ -59,8 +59,9 @@ static int launch_oz_gemm_s(const int8_t* a_img, const int8_t* b_img, const doub
                                  C::SMEM_BYTES));
     attr_set = true;
   }
+  static const int dbg = getenv("SE_OZ_DBG") ? atoi(getenv("SE_OZ_DBG")) : 0;  // measurement knobs, see the kernel
   SE_LAUNCH((oz::gp_trisumsq_ozaki_kernel<S, REUSE>), grid, oz::THREADS, C::SMEM_BYTES, stream, a_img, b_img, scale_b, n_pad,
-            rows_pad, od, partial);
+            rows_pad, od, partial, dbg);
   return 0;
 }
 

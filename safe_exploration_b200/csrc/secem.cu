@@ -43,7 +43,7 @@ struct se_gp_s {
   se_gemm_impl impl = SE_GEMM_AUTO;
   int sm_count = 148;
   // tcgen05 digit-sliced variance GEMM: digit image of L^-1, per-row scales (built on first use)
-  int tc_digits = 7;
+  int tc_digits = 6;
   int tc_ready_digits = 0;
   int8_t* b_img = nullptr;
   int* exp_ab = nullptr;  // [ns] exponents of the output scales, then [ns][n_pad] row exponents of L^-1
@@ -177,7 +177,8 @@ extern "C" int se_gp_set_tc_digits(se_gp_t g, int digits) {
 static int tc_prepare(se_gp_s* g, cudaStream_t st) {
   if (g->tc_ready_digits == g->tc_digits) return 0;
   SE_REQUIRE(g->dtype == SE_F64, "the tcgen05 variance GEMM evaluates float64 models");
-  SE_REQUIRE(g->n_pad <= 32768, "the tcgen05 variance GEMM holds int32 level sums: n_train must be <= 32768");
+  SE_REQUIRE(g->n_pad <= (g->tc_digits == 8 ? 8192 : 16384),
+             "the tcgen05 variance GEMM holds int32 level sums: n_train must be <= 16384 (8192 with 8 digit planes)");
   SE_CUDA(cudaStreamSynchronize(st));  // a previous image may still be in use
   if (g->b_img) SE_CUDA(cudaFree(g->b_img));
   g->b_img = nullptr;

@@ -17,8 +17,8 @@ def main():
     ok_all = True
     for S in (8, 7, 6, 5):
         for nk in (1, 3):
-            a = rng.integers(-64, 65, size=(nk, S, 128, 32), dtype=np.int8)
-            b = rng.integers(-64, 65, size=(nk, S, 64, 32), dtype=np.int8)
+            a = rng.integers(-128, 128, size=(nk, S, 128, 32), dtype=np.int8)
+            b = rng.integers(-128, 128, size=(nk, S, 64, 32), dtype=np.int8)
             want = np.zeros((S, 128, 64), dtype=np.int64)
             for t in range(S):
                 for u in range(S - t):
