@@ -39,7 +39,8 @@ def parse_args():
     ap.add_argument('--dtype', default='f64', choices=['f64', 'f32'])
     ap.add_argument('--config', default='C2', choices=['C1', 'C2', 'C3'])
     ap.add_argument('--gemm', default='auto', choices=['auto', 'simt', 'mma', 'tc'])
-    ap.add_argument('--tc-digits', type=int, default=7, choices=[5, 6, 7, 8])
+    ap.add_argument('--tc-digits', type=int, default=0, choices=[0, 5, 6, 7, 8],
+                    help='digit planes of the tcgen05 variance GEMM (0 = chosen from outputscale / noise)')
     ap.add_argument('--cpu-sample', type=int, default=2048, help='candidates in the CPU-baseline sample')
     ap.add_argument('--no-cpu-baseline', action='store_true')
     return ap.parse_args()
@@ -181,8 +182,8 @@ def run_b200(args):
 
     w = make_workload(args.config, world)
     ssm, mpc = workloads.build_solver(w, dtype=dtype, device=dev, record='none', seed=1234, gemm_impl=gemm)
-    if args.gemm == 'tc':
-        _lib.check(lib.se_gp_set_tc_digits(ssm.handle, args.tc_digits))
+    if args.tc_digits:
+        ssm.set_tc_digits(args.tc_digits)
     comm = sedist.attach_population_sharding(mpc) if world > 1 else 0
     p0 = torch.as_tensor(w.p0, device=dev, dtype=dtype).unsqueeze(0)
     cand_steps = w.num_rollouts * w.time_horizon * w.num_iterations  # whole job, all ranks
@@ -257,33 +258,67 @@ def run_b200(args):
 
     # ---- roofline of the dominant kernel (variance GEMM) ----
     peaks, peak_src = measured_peaks()
-    pipe_peak = None
-    if rank == 0:
-        f = C.c_double(0)
-        kinds = [0] if args.dtype == 'f32' else [1, 2]
-        best = 0.0
+    impl_name, digits = ssm.gemm_info()
+    rows_local = w.num_rollouts // world
+    fp64_flop_per_launch = w.n_s * float(rows_local) * float(w.n_train) ** 2  # n^2/2 FMA per (candidate, output)
+    gemm_avg_ms = gemm_ms.value / max(1, gemm_n.value)
+
+    def pipe_peak(kinds):
+        best, f = 0.0, C.c_double(0)
         for k in kinds:
             _lib.check(lib.se_measure_peak(k, C.byref(f)))
             best = max(best, f.value)
-        pipe_peak = best / 1e12
-    rows_local = w.num_rollouts // world
-    flop_per_launch = w.n_s * float(rows_local) * float(w.n_train) ** 2  # n^2/2 FMA per (candidate, output) = n^2 flop
-    gemm_avg_ms = gemm_ms.value / max(1, gemm_n.value)
-    achieved = flop_per_launch / (gemm_avg_ms * 1e-3) / 1e12 if gemm_avg_ms > 0 else None
+        return best / 1e12
+
+    fp64_peak = pipe_peak([1, 2]) if (rank == 0 and args.dtype == 'f64') else None
+    if impl_name == 'tcgen05-i8':
+        # every float64 FMA of the contraction is evaluated as S (S + 1) / 2 exact int8 digit-plane MACs
+        pairs = digits * (digits + 1) // 2
+        work_per_launch = pairs * fp64_flop_per_launch  # int8 OP (2 x MAC)
+        peak_burst = pipe_peak([3]) if rank == 0 else None
+        peak = pipe_peak([4]) if rank == 0 else None  # the GEMM runs inside a long step: sustained figure
+        pipe = f'int8 tensor (tcgen05.mma kind::i8, {digits} radix-256 digit planes, {pairs} MMAs per K step)'
+        unit = 'TOP/s'
+        peak_src_txt = ('int8 tcgen05 peak measured in this run with se_measure_peak(4): back-to-back 128x256x32 MMAs, '
+                        f'operands resident, sustained for 1.5 s under the power cap (burst: {peak_burst} TOP/s); '
+                        f'for scale: 2 x MEASURED_PEAKS.json ({peak_src}) bf16 burst = '
+                        f'{2 * peaks.get("bf16_tflops", 0):.0f}, sustained = {2 * peaks.get("bf16_tflops_sustained", 0):.0f}')
+    else:
+        work_per_launch = fp64_flop_per_launch
+        peak = (fp64_peak if args.dtype == 'f64' else pipe_peak([0])) if rank == 0 else None
+        pipe = 'FP64 (DMMA / DFMA)' if args.dtype == 'f64' else 'FP32 FFMA'
+        unit = 'TFLOP/s'
+        peak_src_txt = ('measured in this run with se_measure_peak (register-resident FMA / DMMA loop on every SM); '
+                        f'MEASURED_PEAKS.json ({peak_src}) holds only HBM and bf16 numbers')
+    achieved = work_per_launch / (gemm_avg_ms * 1e-3) / 1e12 if gemm_avg_ms > 0 else None
+    fp64_equiv = fp64_flop_per_launch / (gemm_avg_ms * 1e-3) / 1e12 if gemm_avg_ms > 0 else None
+    op_bytes = digits if impl_name == 'tcgen05-i8' else esz
     roofline = {
-        'bound': 'tensor', 'kernel': 'gp_trisumsq (variance GEMM: || L^-1 k* ||^2)',
-        'pipe': 'FP64 (DMMA / DFMA)' if args.dtype == 'f64' else 'FP32 FFMA',
-        'achieved': achieved, 'peak': pipe_peak, 'unit': 'TFLOP/s',
-        'frac': (achieved / pipe_peak) if (achieved and pipe_peak) else None,
-        'peak_source': 'measured in this run with se_measure_peak (register-resident FMA / DMMA loop on every SM); '
-                       f'MEASURED_PEAKS.json ({peak_src}) holds only HBM and bf16 numbers',
-        'flop_per_launch': flop_per_launch, 'avg_launch_ms': gemm_avg_ms, 'launches': int(gemm_n.value),
+        'bound': 'tensor', 'kernel': 'gp_trisumsq (variance GEMM: || L^-1 k* ||^2)', 'impl': impl_name, 'pipe': pipe,
+        'achieved': achieved, 'peak': peak, 'unit': unit,
+        'frac': (achieved / peak) if (achieved and peak) else None, 'peak_source': peak_src_txt,
+        'work_per_launch': work_per_launch, 'avg_launch_ms': gemm_avg_ms, 'launches': int(gemm_n.value),
+        'fp64_equivalent_tflops': fp64_equiv, 'fp64_pipe_peak_tflops': fp64_peak,
         'share_of_step': gemm_ms.value / ms_total if ms_total > 0 else None,
         'kstar_share_of_step': kstar_ms.value / ms_total if ms_total > 0 else None,
         'traffic': None,
-        'hbm': {'algorithmic_bytes_per_launch': (w.n_s * rows_local * w.n_train + w.n_s * w.n_train ** 2 / 2) * esz,
+        'hbm': {'algorithmic_bytes_per_launch': (w.n_s * rows_local * w.n_train + w.n_s * w.n_train ** 2 / 2) * op_bytes,
                 'peak_gbs': peaks.get('hbm_gbs')},
     }
+
+    # ---- accuracy of the variance path actually timed, against the float64 DMMA kernel, on 2048 visited inputs ----
+    variance_check = None
+    if rank == 0 and args.dtype == 'f64' and impl_name != 'dmma':
+        gen = torch.Generator(device='cpu').manual_seed(7)
+        zs = torch.randn(2048, w.n_s + w.n_u, generator=gen, dtype=torch.float64) * 0.15
+        zs = zs.to(dev)
+        _, v_run = ssm.predict_without_jacobians(zs[:, :w.n_s], zs[:, w.n_s:])
+        ssm.set_gemm_impl(_lib.SE_GEMM_MMA)
+        _, v_ref = ssm.predict_without_jacobians(zs[:, :w.n_s], zs[:, w.n_s:])
+        ssm.set_gemm_impl(gemm)
+        rel = ((v_run - v_ref).abs() / v_ref.abs())
+        variance_check = {'against': 'float64 DMMA kernel', 'inputs': 2048, 'max_rel_err': float(rel.max()),
+                          'median_rel_err': float(rel.median())}
 
     cpu_baseline = None
     if rank == 0 and not args.no_cpu_baseline:
@@ -299,7 +334,7 @@ def run_b200(args):
             'warmup': max(3, args.warmup), 'ms_per_step': ms_per_step, 'mpc_solve_ms': ms_per_step,
             'higher_is_better': True, 'scaling': 'weak', 'vs_baseline': None, 'dtype': args.dtype, 'data': 'synthetic',
             'config': workload_desc(w, world, args.dtype), 'e2e': e2e, 'gpu_launches': launches, 'roofline': roofline,
-            'cpu_baseline': cpu_baseline, 'clocks': clocks.summary(), 'numeric_flags': flags,
+            'variance_check': variance_check, 'cpu_baseline': cpu_baseline, 'clocks': clocks.summary(), 'numeric_flags': flags,
             'found_solution': bool(int(res['found'][0])), 'last_result': result.name,
         }
         print(json.dumps(line), flush=True)

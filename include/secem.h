@@ -45,8 +45,9 @@ typedef enum {
   SE_GEMM_AUTO = 0,
   SE_GEMM_SIMT = 1, /* FP32 FFMA / FP64 DFMA register-tiled */
   SE_GEMM_MMA = 2,  /* FP64: DMMA m8n8k4 (mma.sync) */
-  SE_GEMM_TC = 3    /* FP64 models on the 5th-gen tensor cores: tcgen05.mma kind::i8 over 7-bit digit planes of both
-                       operands with exact int32 accumulation in TMEM (Ozaki scheme), recombined in int64 / double */
+  SE_GEMM_TC = 3    /* FP64 models on the 5th-gen tensor cores: tcgen05.mma kind::i8 over balanced radix-256 digit
+                       planes of both operands with exact int32 accumulation in TMEM (Ozaki scheme), recombined in
+                       int64 / double.  SE_GEMM_AUTO picks it for float64 models of 256 .. 16384 training points */
 } se_gemm_impl;
 
 typedef struct se_gp_s* se_gp_t;
@@ -75,9 +76,12 @@ int se_gp_destroy(se_gp_t gp);
 /* workspace cap (bytes) for the materialised kernel rows K*[n_s, N_chunk, n]; default 6 GiB */
 int se_gp_set_workspace_limit(se_gp_t gp, uint64_t bytes);
 int se_gp_set_gemm_impl(se_gp_t gp, se_gemm_impl impl);
-/* digit planes per operand of SE_GEMM_TC: 7 (default; variance within ~1e-9 relative of the float64 evaluation on the
- * bench workload), 8 (~1e-11: float64-equivalent, 29 % more MMAs), 6 (~1e-7, 25 % fewer MMAs) or 5 (~1e-5) */
+/* digit planes per operand of SE_GEMM_TC.  0 (default) = chosen from max_o outputscale_o / noise_o for a relative
+ * variance error <= 1e-8; measured against the float64 DMMA path at outputscale / noise = 10^3: 6 planes 1.7e-9
+ * (21 int8 MMAs per K step), 7 planes 1.5e-11 (28), 8 planes 7e-12 (36, float64 rounding level), 5 planes 3e-7 (15) */
 int se_gp_set_tc_digits(se_gp_t gp, int digits);
+/* which variance-GEMM implementation the handle resolved to, and the digit planes in use (0 until the first call) */
+int se_gp_get_gemm_info(se_gp_t gp, int* impl_out, int* tc_digits_out);
 
 /* mean [N, n_s], variance [N, n_s] (likelihood noise INCLUDED, gp_ssm_cem.py:93) and, if dev_jac != NULL, the
  * Jacobian of the mean w.r.t. z, [N, n_s, d].  Replaces GpCemSSM.predict_without_jacobians / predict_with_jacobians
@@ -214,7 +218,8 @@ int se_cem_select_refit(se_dtype dtype, const void* dev_objective, const void* d
 uint64_t se_launch_count(void);      /* kernels launched by this library since load / last reset */
 void se_launch_count_reset(void);
 /* Runs a register-resident FMA loop on every SM and returns the measured FLOP/s (synchronises the device).
- * kind: 0 = FP32 FFMA, 1 = FP64 DFMA, 2 = FP64 DMMA m8n8k4 */
+ * kind: 0 = FP32 FFMA, 1 = FP64 DFMA, 2 = FP64 DMMA m8n8k4, 3 = int8 tcgen05.mma (OP/s = 2 x MAC/s, operands resident; burst),
+ *       4 = the same sustained for ~1.5 s (what the pipe delivers under the 1 kW power cap) */
 int se_measure_peak(int kind, double* flops_out);
 /* Device time (ms, CUDA events recorded by the library on the launch stream) spent in the variance GEMM kernel and
  * in the kernel-row kernel since the last reset, and their launch counts; timing must be enabled first

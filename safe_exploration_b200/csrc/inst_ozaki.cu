@@ -120,4 +120,47 @@ int launch_oz_probe(const int8_t* a_img, const int8_t* b_img, int nk, int S, int
   return fail("probe: S = %d not compiled", S);
 }
 
+// measured int8 tensor-pipe peak in OP/s (2 x MAC).  sustained = 0: best of a few short launches (burst clocks);
+// sustained = 1: launches back to back for ~1.5 s and reports the last third (the 1 kW power cap has settled by then).
+int measure_peak_i8(int sustained, double* ops_out) {
+  int dev = 0, sms = 0;
+  SE_CUDA(cudaGetDevice(&dev));
+  SE_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+  const int smem = 14 * 1024, iters = 40000;
+  SE_CUDA(cudaFuncSetAttribute(oz::oz_peak_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+  cudaEvent_t e0, e1;
+  SE_CUDA(cudaEventCreate(&e0));
+  SE_CUDA(cudaEventCreate(&e1));
+  const double ops = (double)sms * iters * (2.0 * 128 * 256 * 32);
+  double result = 0.0;
+  if (!sustained) {
+    double best_ms = 1e30;
+    for (int rep = 0; rep < 4; ++rep) {
+      SE_CUDA(cudaEventRecord(e0, 0));
+      SE_LAUNCH(oz::oz_peak_kernel, sms, 128, smem, 0, iters, nullptr);
+      SE_CUDA(cudaEventRecord(e1, 0));
+      SE_CUDA(cudaEventSynchronize(e1));
+      float ms = 0.f;
+      SE_CUDA(cudaEventElapsedTime(&ms, e0, e1));
+      if (rep > 0 && ms < best_ms) best_ms = ms;
+    }
+    result = ops / (best_ms * 1e-3);
+  } else {
+    const int reps = 450;  // ~3 ms each
+    for (int rep = 0; rep < reps; ++rep) {
+      if (rep == reps * 2 / 3) SE_CUDA(cudaEventRecord(e0, 0));
+      SE_LAUNCH(oz::oz_peak_kernel, sms, 128, smem, 0, iters, nullptr);
+    }
+    SE_CUDA(cudaEventRecord(e1, 0));
+    SE_CUDA(cudaEventSynchronize(e1));
+    float ms = 0.f;
+    SE_CUDA(cudaEventElapsedTime(&ms, e0, e1));
+    result = ops * (reps - reps * 2 / 3) / (ms * 1e-3);
+  }
+  cudaEventDestroy(e0);
+  cudaEventDestroy(e1);
+  *ops_out = result;
+  return 0;
+}
+
 }  // namespace se

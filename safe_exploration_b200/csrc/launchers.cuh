@@ -57,6 +57,7 @@ int launch_cem_pack_costs(const T* objective, const T* constraint, int64_t count
 int launch_cem_init_dist(double* mean, double* stdv, int count, cudaStream_t stream);
 
 int measure_peak(int kind, double* flops_out);
+int measure_peak_i8(int sustained, double* ops_out);
 
 // tcgen05 (kind::i8) digit-sliced variance GEMM (ozaki_kernels.cuh)
 int launch_oz_pack_model(const double* w, int n_pad, int ns, const double* host_outputscale, int S, int* exp_a,

@@ -179,16 +179,31 @@ __host__ __device__ __forceinline__ int digit_exponent(double x) {
   if (x > 0.0 && frexp(x, &e) > 0.99) ++e;
   return e;
 }
-// balanced digits of a fixed-point integer q = sum_t d_t 2^(8 (S-1-t)), d_t in [-128, 127]; word[t] byte `e` <- d_t
-template <int S>
-__device__ __forceinline__ void push_digits(long long q, int e, uint32_t (&word)[S]) {
+// Balanced radix-256 digits of four 63-bit fixed-point integers at once.  q = sum_t d_t 256^(7-t) with d_t in
+// [-128, 127]  <=>  q + B = sum_t (d_t + 128) 256^(7-t) with B = 0x8080...80, i.e. the digits are the plain bytes of
+// q + B with the top bit of every byte flipped: one 64-bit add and one xor instead of a carry chain.  A 4 x 4 byte
+// transpose (PRMT) then gathers digit t of the four values into word[t] (byte e = value e), the unit the images store.
+__device__ __forceinline__ void transpose4x4(uint32_t x0, uint32_t x1, uint32_t x2, uint32_t x3, uint32_t& b0,
+                                             uint32_t& b1, uint32_t& b2, uint32_t& b3) {
+  const uint32_t a = __byte_perm(x0, x1, 0x5140), b = __byte_perm(x2, x3, 0x5140);
+  const uint32_t c = __byte_perm(x0, x1, 0x7362), d = __byte_perm(x2, x3, 0x7362);
+  b0 = __byte_perm(a, b, 0x5410);
+  b1 = __byte_perm(a, b, 0x7632);
+  b2 = __byte_perm(c, d, 0x5410);
+  b3 = __byte_perm(c, d, 0x7632);
+}
+__device__ __forceinline__ void digits4(const long long (&q)[4], uint32_t (&word)[MAX_S]) {
+  static_assert(MAX_S == 8, "digits4 splits a 64-bit value into 8 byte digits");
+  uint32_t lo[4], hi[4];
 #pragma unroll
-  for (int t = S - 1; t >= 1; --t) {
-    const int d = (int)((q + 128) & 255) - 128;
-    q = (q - d) >> RB;
-    word[t] |= (uint32_t)(d & 0xFF) << (8 * e);
+  for (int e = 0; e < 4; ++e) {
+    const unsigned long long u = ((unsigned long long)q[e] + 0x8080808080808080ull) ^ 0x8080808080808080ull;
+    lo[e] = (uint32_t)u;
+    hi[e] = (uint32_t)(u >> 32);
   }
-  word[0] |= (uint32_t)((int)q & 0xFF) << (8 * e);
+  // digit t = byte 7 - t of the 64-bit value: hi holds digits 3, 2, 1, 0 in its bytes 0 .. 3; lo holds 7, 6, 5, 4
+  transpose4x4(hi[0], hi[1], hi[2], hi[3], word[3], word[2], word[1], word[0]);
+  transpose4x4(lo[0], lo[1], lo[2], lo[3], word[7], word[6], word[5], word[4]);
 }
 
 // ---------------------------------------------------------------------------------------------------------------------
@@ -223,10 +238,10 @@ __global__ void oz_pack_b_kernel(const double* __restrict__ w, int n_pad, const 
   const double* row = w + ((int64_t)o * n_pad + i) * n_pad;
   const double sc = ldexp(1.0, RB * MAX_S - 1 - exp_b[o * n_pad + i]);
   uint32_t word[MAX_S];
+  long long q[4];
 #pragma unroll
-  for (int t = 0; t < MAX_S; ++t) word[t] = 0;
-#pragma unroll
-  for (int e = 0; e < 4; ++e) push_digits<MAX_S>(__double2ll_rn(row[j0 + e] * sc), e, word);
+  for (int e = 0; e < 4; ++e) q[e] = __double2ll_rn(row[j0 + e] * sc);
+  digits4(q, word);
   const int nb = n_pad / TN, nkb = n_pad / KB;
   const int ib = i / TN, il = i % TN, kb = j0 / KB, c = j0 % KB;
   int8_t* dst = b_img + (((int64_t)o * nb + ib) * nkb + kb) * (int64_t)(S * B_BLK) + blk_off(il, c);
@@ -304,8 +319,7 @@ gp_kstar_slices_kernel(GpDev<double> gp, const double* __restrict__ p, int64_t p
 #pragma unroll
       for (int o = 0; o < NS; ++o) {
         uint32_t word[MAX_S];
-#pragma unroll
-        for (int t = 0; t < MAX_S; ++t) word[t] = 0;
+        long long q[4];
 #pragma unroll
         for (int e = 0; e < 4; ++e) {
           double diff[D];
@@ -316,7 +330,7 @@ gp_kstar_slices_kernel(GpDev<double> gp, const double* __restrict__ p, int64_t p
             ee += diff[dd] * diff[dd] * gp.inv_l2[o][dd];
           }
           const double k = (rvalid[r] && (j0 + e) < gp.n) ? gp.outputscale[o] * exp(-0.5 * ee) : 0.0;
-          push_digits<MAX_S>(__double2ll_rn(k * qscale[o]), e, word);
+          q[e] = __double2ll_rn(k * qscale[o]);
           const double wk = al[o][e] * k;
           m_acc[r][o] += wk;
           if (JAC) {
@@ -324,6 +338,7 @@ gp_kstar_slices_kernel(GpDev<double> gp, const double* __restrict__ p, int64_t p
             for (int dd = 0; dd < D; ++dd) j_acc[r][o][dd] -= wk * diff[dd] * gp.inv_l2[o][dd];
           }
         }
+        digits4(q, word);
         int8_t* dst = a_img + (((int64_t)o * rt_count + ct) * nkb + kb) * (int64_t)(S * A_BLK) + blk_off(rl, c);
 #pragma unroll
         for (int t = 0; t < MAX_S; ++t)
@@ -549,6 +564,56 @@ oz_probe_kernel(const int8_t* __restrict__ a_img, const int8_t* __restrict__ b_i
 #pragma unroll
       for (int j = 0; j < 8; ++j) out[((int64_t)l * TM + row) * TN + c8 + j] = v[j];
     }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 0) tmem_dealloc(tmem_base, TMEM_COLS);
+}
+
+// ---------------------------------------------------------------------------------------------------------------------
+// Pipe peak (se_measure_peak kind 3): back-to-back 128 x 256 x 32 s8 MMAs on every SM, operands resident in shared
+// memory, no loads and no epilogue -- the denominator bench.py quotes for the tcgen05 variance GEMM.
+// ---------------------------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(128, 1) oz_peak_kernel(int iters, int32_t* __restrict__ sink) {
+  extern __shared__ unsigned char smem_raw[];
+  const uint32_t raw = smem_u32(smem_raw);
+  const uint32_t base = (raw + 1023u) & ~1023u;
+  const uint32_t bar = base + 12 * 1024, tmem_slot = bar + 8;
+  const int warp = threadIdx.x >> 5;
+  for (int i = threadIdx.x; i < 12 * 1024 / 4; i += blockDim.x)
+    reinterpret_cast<uint32_t*>(smem_raw + (base - raw))[i] = 0x01010101u * (uint32_t)(i & 3);
+  if (threadIdx.x == 0) {
+    mbar_init(bar, 1);
+    mbar_fence_init();
+  }
+  if (warp == 0) tmem_alloc(tmem_slot, TMEM_COLS);
+  asm volatile("fence.proxy.async.shared::cta;\n" ::: "memory");  // generic-proxy smem writes -> async proxy (UMMA)
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  uint32_t tmem_base;
+  asm volatile("ld.shared.u32 %0, [%1];\n" : "=r"(tmem_base) : "r"(tmem_slot));
+  if (warp == 0) {
+    const uint32_t tb = __shfl_sync(0xffffffffu, tmem_base, 0);
+    const uint32_t alo = desc_lo(__shfl_sync(0xffffffffu, base, 0), LBO), dhi = desc_hi(SBO);
+    constexpr uint32_t idesc = make_idesc(128, 256);
+    if (elect_one()) {
+      const uint64_t ad = pack_desc(alo, dhi), bd = pack_desc(alo + (4096 >> 4), dhi);
+      for (int i = 0; i < iters; i += 2) {
+        mma_i8<0>(tb, ad, bd, idesc, 1u);
+        mma_i8<0>(tb + 256, ad, bd, idesc, 1u);
+      }
+      tc_commit(bar);
+    }
+    __syncwarp();
+  }
+  mbar_wait(bar, 0);
+  tc_fence_after();
+  if (sink == reinterpret_cast<int32_t*>(1)) {  // never true: keeps the accumulators observable
+    int32_t v[8];
+    tmem_ld8(tmem_base, v);
+    tmem_ld_wait();
+    sink[0] = v[0];
+  }
   tc_fence_before();
   __syncthreads();
   if (warp == 0) tmem_dealloc(tmem_base, TMEM_COLS);

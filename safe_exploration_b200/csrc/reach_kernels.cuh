@@ -159,14 +159,15 @@ struct StepIO {
   T* q_all;        // [N, T, NS, NS]
   T* sigma_all;    // [N, T, NS]
   int32_t* flags;
+  int64_t first;   // first candidate of this launch (all arrays are indexed by the absolute candidate id)
 };
 
 template <typename T, int NS, int NU>
 __global__ void __launch_bounds__(128)
 reach_step_kernel(ProbDev<T> pr, StepIO<T> io, int64_t N) {
   constexpr int D = NS + NU;
-  const int64_t c = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
-  if (c >= N) return;
+  const int64_t c = io.first + blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (c >= io.first + N) return;
 
   T p[NS], u[NU], mu[NS], sg[NS];
 #pragma unroll

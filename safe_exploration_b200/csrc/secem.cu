@@ -2,6 +2,7 @@
 #include <dlfcn.h>
 
 #include <cmath>
+#include <cstdlib>
 #include <vector>
 
 #include "cem_kernels.cuh"
@@ -43,11 +44,15 @@ struct se_gp_s {
   se_gemm_impl impl = SE_GEMM_AUTO;
   int sm_count = 148;
   // tcgen05 digit-sliced variance GEMM: digit image of L^-1, per-row scales (built on first use)
-  int tc_digits = 6;
+  int tc_digits_req = 0;  // 0 = chosen from the prior / noise ratio (tc_auto_digits)
+  int tc_digits = 0;      // resolved value (tc_prepare)
   int tc_ready_digits = 0;
   int8_t* b_img = nullptr;
   int* exp_ab = nullptr;  // [ns] exponents of the output scales, then [ns][n_pad] row exponents of L^-1
   double* scale_b = nullptr;
+  // second stream + events of the two-part pipeline in se_cem_solve (created on first use)
+  cudaStream_t side = nullptr;
+  cudaEvent_t ev_fork = nullptr, ev_join = nullptr, ev_k[2] = {nullptr, nullptr}, ev_g[2] = {nullptr, nullptr};
   // timing
   bool timing = false;
   std::vector<cudaEvent_t> ev_gemm, ev_kstar;  // (start, stop) pairs
@@ -83,8 +88,23 @@ extern "C" int se_version(void) { return 100; }
 extern "C" uint64_t se_launch_count(void) { return g_launches.load(); }
 extern "C" void se_launch_count_reset(void) { g_launches.store(0); }
 extern "C" int se_measure_peak(int kind, double* flops_out) {
-  SE_REQUIRE(kind >= 0 && kind <= 2 && flops_out, "se_measure_peak: bad arguments");
+  SE_REQUIRE(kind >= 0 && kind <= 4 && flops_out, "se_measure_peak: bad arguments");
+  if (kind >= 3) return measure_peak_i8(kind == 4, flops_out);
   return measure_peak(kind, flops_out);
+}
+
+// SE_GEMM_AUTO: float64 models of 256 .. 16384 training points run the variance GEMM on the tcgen05 tensor cores
+// (2.9x the FP64 DMMA path at n = 2000); smaller ones are launch-bound and stay on the exact DMMA kernel; float32
+// models run FFMA.  SE_GEMM_AUTO_IMPL=mma|simt|tc overrides (benchmarks).
+static se_gemm_impl resolve_impl(const se_gp_s* g, se_gemm_impl impl) {
+  if (impl != SE_GEMM_AUTO) return impl;
+  if (const char* e = getenv("SE_GEMM_AUTO_IMPL")) {
+    if (!strcmp(e, "mma")) return SE_GEMM_MMA;
+    if (!strcmp(e, "simt")) return SE_GEMM_SIMT;
+    if (!strcmp(e, "tc") && g->dtype == SE_F64) return SE_GEMM_TC;
+  }
+  if (g->dtype == SE_F64 && g->n_pad >= 256 && g->n_pad <= 16384) return SE_GEMM_TC;
+  return g->dtype == SE_F64 ? SE_GEMM_MMA : SE_GEMM_SIMT;
 }
 
 extern "C" int se_gp_create(se_gp_t* out, int n_s, int n_u, int n, se_dtype dtype, const void* dev_x,
@@ -140,6 +160,7 @@ extern "C" int se_gp_create(se_gp_t* out, int n_s, int n_u, int n, se_dtype dtyp
     rc = launch_pack_model<float>((const float*)dev_x, (const float*)dev_alpha, (const float*)dev_linv, n, g->d, n_s,
                                   g->n_pad, (float*)g->xt, (float*)g->alpha, (float*)g->w, st);
   if (rc != 0) return cleanup_fail();
+  g->impl = resolve_impl(g, SE_GEMM_AUTO);
   *out = g;
   return 0;
 }
@@ -151,6 +172,9 @@ extern "C" int se_gp_destroy(se_gp_t g) {
     if (p) cudaFree(p);
   for (auto e : g->ev_gemm) cudaEventDestroy(e);
   for (auto e : g->ev_kstar) cudaEventDestroy(e);
+  for (cudaEvent_t e : {g->ev_fork, g->ev_join, g->ev_k[0], g->ev_k[1], g->ev_g[0], g->ev_g[1]})
+    if (e) cudaEventDestroy(e);
+  if (g->side) cudaStreamDestroy(g->side);
   delete g;
   return 0;
 }
@@ -163,19 +187,42 @@ extern "C" int se_gp_set_workspace_limit(se_gp_t g, uint64_t bytes) {
 extern "C" int se_gp_set_gemm_impl(se_gp_t g, se_gemm_impl impl) {
   SE_REQUIRE(g, "NULL handle");
   SE_REQUIRE(impl != SE_GEMM_TC || g->dtype == SE_F64, "SE_GEMM_TC evaluates float64 models");
-  g->impl = impl;
+  g->impl = resolve_impl(g, impl);
   return 0;
 }
 extern "C" int se_gp_set_tc_digits(se_gp_t g, int digits) {
   SE_REQUIRE(g, "NULL handle");
-  SE_REQUIRE(digits >= 5 && digits <= 8, "se_gp_set_tc_digits: %d outside [5, 8]", digits);
-  g->tc_digits = digits;
+  SE_REQUIRE(digits == 0 || (digits >= 5 && digits <= 8), "se_gp_set_tc_digits: %d is neither 0 (auto) nor in [5, 8]",
+             digits);
+  g->tc_digits_req = digits;
   return 0;
+}
+extern "C" int se_gp_get_gemm_info(se_gp_t g, int* impl_out, int* tc_digits_out) {
+  SE_REQUIRE(g, "NULL handle");
+  if (impl_out) *impl_out = (int)g->impl;
+  if (tc_digits_out) *tc_digits_out = g->tc_digits;
+  return 0;
+}
+
+// Digit planes for a target relative variance error of 1e-8.  The variance s + noise - ||L^-1 k||^2 cancels down to
+// ~noise, so an error eps relative to the prior scale s shows up as eps * s / noise; measured on the bench workloads
+// (tools/tc_check.py) the truncation after S planes is eps ~ 480 * 2^(-8 S) ... i.e. 1.7e-9 relative at S = 6 and
+// s / noise = 10^3.
+static int tc_auto_digits(const se_gp_s* g) {
+  double ratio = 1.0;
+  for (int o = 0; o < g->ns; ++o)
+    if (g->noise[o] > 0.0) ratio = std::fmax(ratio, g->outputscale[o] / g->noise[o]);
+  for (int S = 6; S < 8; ++S)
+    if (480.0 * ratio * std::ldexp(1.0, -8 * S) <= 1e-8) return S;
+  return 8;
 }
 
 // digit image of L^-1 for the tcgen05 path; rebuilt when the number of digit planes changes
 static int tc_prepare(se_gp_s* g, cudaStream_t st) {
-  if (g->tc_ready_digits == g->tc_digits) return 0;
+  int want = g->tc_digits_req ? g->tc_digits_req : tc_auto_digits(g);
+  if (want == 8 && g->n_pad > 8192 && !g->tc_digits_req) want = 7;
+  if (g->tc_ready_digits == want) return 0;
+  g->tc_digits = want;
   SE_REQUIRE(g->dtype == SE_F64, "the tcgen05 variance GEMM evaluates float64 models");
   SE_REQUIRE(g->n_pad <= (g->tc_digits == 8 ? 8192 : 16384),
              "the tcgen05 variance GEMM holds int32 level sums: n_train must be <= 16384 (8192 with 8 digit planes)");
@@ -268,39 +315,78 @@ static int record_event(std::vector<cudaEvent_t>& ev, cudaStream_t st) {
   return 0;
 }
 
+// ---- GP posterior in three stages, for rows [row0, row0 + nrows) of a candidate batch -------------------------------
+// The stages of one part use the workspace slice `slot` (kernel rows / digit image and partial sums), so two parts can
+// be in flight on two streams (cem_solve_t pipelines the population in halves).
+struct PostPart {
+  int64_t row0;
+  int nrows, rows_pad, nb;
+  void* kst;      // this part's kernel rows (plain) or digit image (tcgen05 path)
+  void* partial;  // this part's partial sums
+};
+
+template <typename T>
+static PostPart post_part(se_gp_s* g, int64_t row0, int nrows, int64_t slot_row0) {
+  PostPart pp;
+  pp.row0 = row0, pp.nrows = nrows, pp.rows_pad = (int)round_up(nrows, kTile), pp.nb = 0;
+  // slot_row0: first (padded) row of this part inside the workspace
+  pp.kst = (char*)g->kst + (size_t)g->ns * slot_row0 * g->n_pad * g->esz;
+  pp.partial = (char*)g->partial + (size_t)g->ns * (g->n_pad / 32) * slot_row0 * g->esz;
+  return pp;
+}
+
+template <typename T>
+static int post_kstar(se_gp_s* g, const GpDev<T>& gd, const PostPart& pp, const T* p, int64_t p_stride, const T* u,
+                      int64_t u_stride, T* mean, T* jac, cudaStream_t st) {
+  const bool tc = g->impl == SE_GEMM_TC;
+  if (g->timing) SE_TRY(record_event(g->ev_kstar, st));
+  if constexpr (sizeof(T) == 8) {
+    if (tc)  // kernel rows as int8 digit planes (<= 8 bytes per element, like the float64 rows they replace)
+      SE_TRY(launch_kstar_slices(gd, p, p_stride, u, u_stride, pp.row0, pp.nrows, pp.rows_pad, g->exp_ab,
+                                 g->tc_digits, (int8_t*)pp.kst, mean, jac, st));
+  }
+  if (!tc)
+    SE_TRY(launch_kstar<T>(gd, p, p_stride, u, u_stride, pp.row0, pp.nrows, pp.rows_pad, (T*)pp.kst, mean, jac, st));
+  if (g->timing) SE_TRY(record_event(g->ev_kstar, st));
+  return 0;
+}
+
+template <typename T>
+static int post_gemm(se_gp_s* g, const GpDev<T>& gd, PostPart& pp, cudaStream_t st) {
+  const bool tc = g->impl == SE_GEMM_TC;
+  if (g->timing) SE_TRY(record_event(g->ev_gemm, st));
+  if constexpr (sizeof(T) == 8) {
+    if (tc)
+      SE_TRY(launch_trisumsq_ozaki((const int8_t*)pp.kst, g->b_img, g->scale_b, g->n_pad, pp.rows_pad, g->ns,
+                                   g->tc_digits, (double*)pp.partial, g->sm_count, &pp.nb, st));
+  }
+  if (!tc)
+    SE_TRY(launch_trisumsq<T>(g->impl, (const T*)pp.kst, gd.w, g->n_pad, pp.rows_pad, g->ns, (T*)pp.partial,
+                              g->counter, g->sm_count, &pp.nb, st));
+  if (g->timing) SE_TRY(record_event(g->ev_gemm, st));
+  return 0;
+}
+
+template <typename T>
+static int post_var(se_gp_s* g, const GpDev<T>& gd, const PostPart& pp, T* var, cudaStream_t st) {
+  return launch_var<T>(gd, (const T*)pp.partial, pp.nb, pp.rows_pad, pp.row0, pp.nrows, var, st);
+}
+
 // GP posterior for N candidates whose inputs are z_c = [p[c*p_stride : +ns] | u[c*u_stride : +nu]]
 template <typename T>
 static int gp_posterior(se_gp_s* g, const T* p, int64_t p_stride, const T* u, int64_t u_stride, int64_t N, T* mean,
                         T* var, T* jac, cudaStream_t st) {
   if (N <= 0) return 0;
   SE_TRY(gp_reserve(g, N));
+  if (g->impl == SE_GEMM_TC) SE_TRY(tc_prepare(g, st));
   const GpDev<T> gd = gp_dev<T>(g);
   const int64_t rows_chunk = chunk_rows(g, N);
-  const bool tc = g->impl == SE_GEMM_TC;
-  if (tc) SE_TRY(tc_prepare(g, st));
   for (int64_t row0 = 0; row0 < N; row0 += rows_chunk) {
     const int nrows = (int)((N - row0) < rows_chunk ? (N - row0) : rows_chunk);
-    const int rows_pad = (int)round_up(nrows, kTile);
-    if (g->timing) SE_TRY(record_event(g->ev_kstar, st));
-    if constexpr (sizeof(T) == 8) {
-      if (tc)  // kernel rows as int8 digit planes (the workspace holds <= 7 bytes per element instead of 8)
-        SE_TRY(launch_kstar_slices(gd, p, p_stride, u, u_stride, row0, nrows, rows_pad, g->exp_ab, g->tc_digits,
-                                   (int8_t*)g->kst, mean, jac, st));
-    }
-    if (!tc) SE_TRY(launch_kstar<T>(gd, p, p_stride, u, u_stride, row0, nrows, rows_pad, (T*)g->kst, mean, jac, st));
-    if (g->timing) SE_TRY(record_event(g->ev_kstar, st));
-    int nb = 0;
-    if (g->timing) SE_TRY(record_event(g->ev_gemm, st));
-    if constexpr (sizeof(T) == 8) {
-      if (tc)
-        SE_TRY(launch_trisumsq_ozaki((const int8_t*)g->kst, g->b_img, g->scale_b, g->n_pad, rows_pad, g->ns,
-                                     g->tc_digits, (double*)g->partial, g->sm_count, &nb, st));
-    }
-    if (!tc)
-      SE_TRY(launch_trisumsq<T>(g->impl, (const T*)g->kst, gd.w, g->n_pad, rows_pad, g->ns, (T*)g->partial,
-                                g->counter, g->sm_count, &nb, st));
-    if (g->timing) SE_TRY(record_event(g->ev_gemm, st));
-    SE_TRY(launch_var<T>(gd, (const T*)g->partial, nb, rows_pad, row0, nrows, var, st));
+    PostPart pp = post_part<T>(g, row0, nrows, 0);
+    SE_TRY(post_kstar<T>(g, gd, pp, p, p_stride, u, u_stride, mean, jac, st));
+    SE_TRY(post_gemm<T>(g, gd, pp, st));
+    SE_TRY(post_var<T>(g, gd, pp, var, st));
   }
   return 0;
 }
@@ -681,6 +767,21 @@ static int cem_solve_t(se_cem_s* c, const ProbDev<T>& pr, const T* p0, const T* 
   if (out->flags) SE_CUDA(cudaMemsetAsync(out->flags, 0, 4 * sizeof(int32_t), st));
   SE_TRY(launch_cem_init_dist(c->mean, c->stdv, (int)dist, st));
 
+  // pipeline the population in two halves when it is large enough and fits the workspace in one piece
+  // (off by default: on the 1 kW B200 both the int8 GEMM and the FP64 kernel-row kernel run into the power cap, so
+  // overlapping them does not shorten the solve -- measured 132 ms pipelined vs 124 ms sequential at C2)
+  const int pipe_env = getenv("SE_PIPELINE") ? atoi(getenv("SE_PIPELINE")) : 0;
+  const int64_t half0_rows = round_up((cand + 1) / 2, kTile);
+  const int64_t two_part_rows = half0_rows + round_up(cand - half0_rows > 0 ? cand - half0_rows : 1, kTile);
+  const bool pipelined = pipe_env != 0 && cand >= 4 * kTile && chunk_rows(g, two_part_rows) >= two_part_rows;
+  SE_TRY(gp_reserve(g, pipelined ? two_part_rows : cand));
+  if (g->impl == SE_GEMM_TC) SE_TRY(tc_prepare(g, st));
+  if (pipelined && !g->side) {
+    SE_CUDA(cudaStreamCreateWithFlags(&g->side, cudaStreamNonBlocking));
+    for (cudaEvent_t* e : {&g->ev_fork, &g->ev_join, &g->ev_k[0], &g->ev_k[1], &g->ev_g[0], &g->ev_g[1]})
+      SE_CUDA(cudaEventCreateWithFlags(e, cudaEventDisableTiming));
+  }
+
   ActionSrc<T> src;
   memset(&src, 0, sizeof(src));
   src.seed = seed, src.n_global = Ng, src.tnu = tnu;
@@ -697,21 +798,50 @@ static int cem_solve_t(se_cem_s* c, const ProbDev<T>& pr, const T* p0, const T* 
     SE_TRY(launch_cem_sample<T>(src, M, cf.first_rollout, Nl, ns, p0, actions, p, rec_act, st));
 
     // RolloutFunction._sample_trajectory (constrained_cem_mpc.py:175-183): T sequential ellipsoid steps
-    for (int t = 0; t < T_len; ++t) {
-      const bool point = t == 0;  // get_action starts from a point state: q = None (safempc_cem.py:234-235, quirk Q9)
-      SE_TRY(gp_posterior<T>(g, p, ns, actions + (int64_t)t * nu, tnu, cand, mean, var, point ? nullptr : jac, st));
+    auto make_io = [&](int t, int64_t first) {
       StepIO<T> io;
       memset(&io, 0, sizeof(io));
       io.p_in = p, io.q_in = q, io.p_out = p, io.q_out = q;
       io.u = actions + (int64_t)t * nu, io.u_stride = tnu;
       io.mean = mean, io.var = var, io.jac = jac;
-      io.point = point ? 1 : 0;
+      io.point = t == 0 ? 1 : 0;  // get_action starts from a point state: q = None (safempc_cem.py:234-235, quirk Q9)
       io.objective = objective, io.constraint = constraint;
       io.first_step = t == 0, io.last_step = t == T_len - 1;
       io.act_all = actions, io.T_len = T_len, io.t_index = t;
       io.traj = rec_traj;
       io.flags = out->flags;
-      SE_TRY(launch_reach_step<T>(pr, io, cand, st));
+      io.first = first;
+      return io;
+    };
+    if (!pipelined) {
+      for (int t = 0; t < T_len; ++t) {
+        SE_TRY(gp_posterior<T>(g, p, ns, actions + (int64_t)t * nu, tnu, cand, mean, var, t == 0 ? nullptr : jac, st));
+        SE_TRY(launch_reach_step<T>(pr, make_io(t, 0), cand, st));
+      }
+    } else {
+      // Two-part software pipeline: the population is cut in halves; the main stream runs nothing but the variance
+      // GEMMs (tensor pipe) while the side stream prepares the other half (kernel rows: FP64 pipe) and advances the
+      // ellipsoids of the half whose GEMM just finished.  A half's own chain stays sequential:
+      //   kstar(h, t) -> gemm(h, t) -> var, reach(h, t) -> kstar(h, t + 1)
+      SE_CUDA(cudaEventRecord(g->ev_fork, st));
+      SE_CUDA(cudaStreamWaitEvent(g->side, g->ev_fork, 0));
+      const GpDev<T> gd = gp_dev<T>(g);
+      const int64_t half0 = half0_rows;
+      PostPart part[2] = {post_part<T>(g, 0, (int)half0, 0), post_part<T>(g, half0, (int)(cand - half0), half0)};
+      for (int t = 0; t < T_len; ++t)
+        for (int h = 0; h < 2; ++h) {
+          PostPart& pp = part[h];
+          SE_TRY(post_kstar<T>(g, gd, pp, p, ns, actions + (int64_t)t * nu, tnu, mean, t == 0 ? nullptr : jac, g->side));
+          SE_CUDA(cudaEventRecord(g->ev_k[h], g->side));
+          SE_CUDA(cudaStreamWaitEvent(st, g->ev_k[h], 0));
+          SE_TRY(post_gemm<T>(g, gd, pp, st));
+          SE_CUDA(cudaEventRecord(g->ev_g[h], st));
+          SE_CUDA(cudaStreamWaitEvent(g->side, g->ev_g[h], 0));
+          SE_TRY(post_var<T>(g, gd, pp, var, g->side));
+          SE_TRY(launch_reach_step<T>(pr, make_io(t, pp.row0), pp.nrows, g->side));
+        }
+      SE_CUDA(cudaEventRecord(g->ev_join, g->side));
+      SE_CUDA(cudaStreamWaitEvent(st, g->ev_join, 0));
     }
 
     T* rec_obj = out->objective ? (T*)out->objective + (size_t)it * cand : nullptr;

@@ -120,7 +120,7 @@ class B200GpCemSSM(CemSSM):
 
     def __init__(self, conf, state_dimen: int, action_dimen: int, lengthscale=None, outputscale=None, noise=None,
                  dtype: torch.dtype = torch.float64, device: Optional[str] = None, gemm_impl: int = _lib.SE_GEMM_AUTO,
-                 workspace_bytes: Optional[int] = None):
+                 workspace_bytes: Optional[int] = None, tc_digits: int = 0):
         super().__init__(state_dimen, action_dimen)
         kernel = getattr(conf, 'exact_gp_kernel', 'rbf') if conf is not None else 'rbf'
         if kernel != 'rbf':
@@ -140,6 +140,7 @@ class B200GpCemSSM(CemSSM):
         self.noise = torch.full((state_dimen,), ln2, **f64) if noise is None else \
             torch.as_tensor(noise, **f64).reshape(state_dimen).clone()
         self._gemm_impl = gemm_impl
+        self._tc_digits = tc_digits
         self._workspace_bytes = workspace_bytes
         self._handle = C.c_void_p(None)
         self._last_training_losses = []
@@ -166,6 +167,18 @@ class B200GpCemSSM(CemSSM):
         self._gemm_impl = impl
         if self._handle:
             _lib.check(self._lib.se_gp_set_gemm_impl(self._handle, impl))
+
+    def set_tc_digits(self, digits: int) -> None:
+        """Digit planes of the tcgen05 variance GEMM: 0 = chosen from outputscale / noise (default), or 5 .. 8."""
+        self._tc_digits = digits
+        if self._handle:
+            _lib.check(self._lib.se_gp_set_tc_digits(self._handle, digits))
+
+    def gemm_info(self) -> Tuple[str, int]:
+        """(implementation the variance GEMM resolved to, digit planes in use -- 0 before the first evaluation)."""
+        impl, digits = C.c_int(0), C.c_int(0)
+        _lib.check(self._lib.se_gp_get_gemm_info(self.handle, C.byref(impl), C.byref(digits)))
+        return {_lib.SE_GEMM_SIMT: 'simt', _lib.SE_GEMM_MMA: 'dmma', _lib.SE_GEMM_TC: 'tcgen05-i8'}[impl.value], digits.value
 
     # ---- CemSSM ------------------------------------------------------------------------------------------------
     def _update_model(self, x_train: Tensor, y_train: Tensor) -> None:
@@ -198,6 +211,8 @@ class B200GpCemSSM(CemSSM):
         self._handle = handle
         if self._gemm_impl != _lib.SE_GEMM_AUTO:
             _lib.check(self._lib.se_gp_set_gemm_impl(handle, self._gemm_impl))
+        if self._tc_digits:
+            _lib.check(self._lib.se_gp_set_tc_digits(handle, self._tc_digits))
         if self._workspace_bytes is not None:
             _lib.check(self._lib.se_gp_set_workspace_limit(handle, int(self._workspace_bytes)))
 

@@ -1,0 +1,178 @@
+"""GPU parity tests of the tcgen05 (kind::i8) variance GEMM -- SE_GEMM_TC, what SE_GEMM_AUTO resolves to for float64
+models of 256 .. 16384 training points.
+
+The contraction || L^-1 k* ||^2 is evaluated from balanced radix-256 digit planes with exact int32 accumulation, so
+the only error is the truncation after S planes.  Tolerances written here (relative to the variance itself, which on
+these workloads is ~10^3 below the prior scale): S = 7, 8 -> 1e-9 (the float64 bar of test_gpu_parity.py); S = 6 and the
+automatic choice -> 1e-8; S = 5 -> 1e-5.  The tile primitive itself is integer work and must be bit-exact.
+"""
+import numpy as np
+import pytest
+import torch
+
+import safe_exploration_b200 as se
+from oracle import oracle
+from safe_exploration_b200 import _lib, workloads
+
+pytestmark = pytest.mark.gpu
+DEV = 'cuda:0'
+T = lambda x: torch.as_tensor(np.asarray(x, dtype=np.float64))
+G = lambda x: torch.as_tensor(np.asarray(x, dtype=np.float64)).to(device=DEV)
+TOL = {0: 1e-8, 5: 1e-5, 6: 1e-8, 7: 1e-9, 8: 1e-9}
+
+
+def rel_err(a, b, scale=None):
+    a, b = np.asarray(a, dtype=np.float64), np.asarray(b, dtype=np.float64)
+    den = np.maximum(np.abs(b), 0 if scale is None else scale)
+    den = np.where(den == 0, 1.0, den)
+    return float(np.max(np.abs(a - b) / den)) if a.size else 0.0
+
+
+def image(planes):
+    """[nk][S][rows][32] int8 digit planes -> bytes in shared-memory operand order [row/8][k/16][row%8][k%16]."""
+    nk, S, R, K = planes.shape
+    return np.ascontiguousarray(planes.reshape(nk, S, R // 8, 8, 2, 16).transpose(0, 1, 2, 4, 3, 5)).reshape(-1)
+
+
+@pytest.mark.parametrize('S', [5, 6, 7, 8])
+@pytest.mark.parametrize('nk', [1, 2, 5])
+def test_tile_primitive_is_bit_exact(S, nk):
+    """One 128 x 64 tile: level sums D_l = sum_{t+u=l} A_t B_u^T over nk K steps, full signed-byte range."""
+    lib = _lib.load()
+    rng = np.random.default_rng(100 * S + nk)
+    a = rng.integers(-128, 128, size=(nk, S, 128, 32), dtype=np.int8)
+    b = rng.integers(-128, 128, size=(nk, S, 64, 32), dtype=np.int8)
+    want = np.zeros((S, 128, 64), dtype=np.int64)
+    for t in range(S):
+        for u in range(S - t):
+            for k in range(nk):
+                want[t + u] += a[k, t].astype(np.int64) @ b[k, u].astype(np.int64).T
+    da, db = torch.from_numpy(image(a)).to(DEV), torch.from_numpy(image(b)).to(DEV)
+    out = torch.full((S, 128, 64), -1, dtype=torch.int32, device=DEV)
+    _lib.check(lib.se_debug_tc_probe(_lib.ptr(da), _lib.ptr(db), nk, S, 128, 256, _lib.ptr(out), _lib.stream_ptr(DEV)))
+    torch.cuda.synchronize()
+    assert np.array_equal(out.cpu().numpy().astype(np.int64), want)
+
+
+def _random_model(n_s, n_u, n, seed, ratio=1e3):
+    rng = np.random.default_rng(seed)
+    d = n_s + n_u
+    x = rng.uniform(-1, 1, (n, d))
+    y = 0.1 * np.sin(x @ rng.standard_normal((d, n_s)))
+    ls = rng.uniform(0.6, 1.4, (n_s, d))
+    os_ = rng.uniform(0.02, 0.08, n_s)
+    nz = os_ / ratio * rng.uniform(0.8, 1.2, n_s)
+    return x, y, ls, os_, nz
+
+
+@pytest.mark.parametrize('digits', [0, 5, 6, 7, 8])
+@pytest.mark.parametrize('n_s,n_u,n,N', [(2, 1, 300, 1000), (4, 1, 700, 513), (6, 2, 257, 129), (1, 3, 1500, 77),
+                                         (3, 2, 129, 128)])
+def test_tc_predict_matches_oracle(digits, n_s, n_u, n, N):
+    """Ragged n and N, every state dimension; mean and Jacobian are float64 FMA work and keep the 1e-9 bar."""
+    x, y, ls, os_, nz = _random_model(n_s, n_u, n, n + N)
+    z = np.random.default_rng(1).uniform(-1.1, 1.1, (N, n_s + n_u))
+    z[: N // 2] = x[np.random.default_rng(2).integers(0, n, N // 2)] + 1e-3  # next to training points: var ~ noise
+    gp = se.B200GpCemSSM(None, n_s, n_u, ls, os_, nz, device=DEV, gemm_impl=_lib.SE_GEMM_TC, tc_digits=digits)
+    gp.update_model(G(x), G(y), replace_old=True)
+    ref = oracle.OracleGpCemSSM(n_s, n_u, ls, os_, nz)
+    ref.update_model(T(x), T(y), replace_old=True)
+    mean, var, jac = gp.predict_with_jacobians(G(z[:, :n_s]), G(z[:, n_s:]))
+    m0, v0, j0 = ref.predict_with_jacobians(T(z[:, :n_s]), T(z[:, n_s:]))
+    impl, used = gp.gemm_info()
+    assert impl == 'tcgen05-i8' and (used == digits if digits else used in (6, 7, 8))
+    assert rel_err(mean.cpu(), m0, np.abs(m0.numpy()).max()) < 1e-9
+    assert rel_err(jac.cpu(), j0, np.abs(j0.numpy()).max()) < 1e-9
+    assert rel_err(var.cpu(), v0) < TOL[digits], (digits, used)
+    m1, v1 = gp.predict_without_jacobians(G(z[:, :n_s]), G(z[:, n_s:]))
+    assert torch.equal(v1, var) and torch.allclose(m1, mean, rtol=1e-12, atol=1e-14)
+
+
+def test_auto_digits_follow_the_prior_to_noise_ratio():
+    """outputscale / noise = 10^3 -> 6 planes, 10^5 -> 7, 10^8 -> 8; the 1e-8 target holds for each."""
+    for ratio, want in ((1e3, 6), (1e5, 7), (1e8, 8)):
+        x, y, ls, os_, nz = _random_model(2, 1, 400, 5, ratio)
+        nz = os_ / ratio
+        gp = se.B200GpCemSSM(None, 2, 1, ls, os_, nz, device=DEV)
+        gp.update_model(G(x), G(y), replace_old=True)
+        z = np.random.default_rng(3).uniform(-1, 1, (256, 3))
+        _, var = gp.predict_without_jacobians(G(z[:, :2]), G(z[:, 2:]))
+        assert gp.gemm_info() == ('tcgen05-i8', want)
+        gp.set_gemm_impl(_lib.SE_GEMM_MMA)
+        _, v64 = gp.predict_without_jacobians(G(z[:, :2]), G(z[:, 2:]))
+        assert gp.gemm_info()[0] == 'dmma'
+        # against the float64 kernel on the same factors; at 10^8 the float64 kernel's own rounding, amplified by the
+        # cancellation, is ~1e-7, so only the looser bound can be asked there
+        assert rel_err(var.cpu(), v64.cpu()) < (1e-8 if ratio < 1e6 else 1e-5)
+
+
+def test_auto_impl_selection():
+    """n <= 128 stays on the exact DMMA kernel, larger float64 models use the tensor cores, float32 models FFMA."""
+    x, y, ls, os_, nz = _random_model(2, 1, 100, 1)
+    gp = se.B200GpCemSSM(None, 2, 1, ls, os_, nz, device=DEV)
+    gp.update_model(G(x), G(y), replace_old=True)
+    assert gp.gemm_info()[0] == 'dmma'
+    x, y, ls, os_, nz = _random_model(2, 1, 200, 1)
+    gp = se.B200GpCemSSM(None, 2, 1, ls, os_, nz, device=DEV)
+    gp.update_model(G(x), G(y), replace_old=True)
+    assert gp.gemm_info()[0] == 'tcgen05-i8'
+    gp32 = se.B200GpCemSSM(None, 2, 1, ls, os_, nz, device=DEV, dtype=torch.float32)
+    gp32.update_model(G(x), G(y), replace_old=True)
+    assert gp32.gemm_info()[0] == 'simt'
+    with pytest.raises(_lib.SecemError):
+        gp32.set_gemm_impl(_lib.SE_GEMM_TC)
+
+
+def test_tc_chunked_workspace_and_reruns_are_bit_identical():
+    """Integer accumulation and a fixed partial-sum order: chunking the batch or repeating the call changes nothing."""
+    x, y, ls, os_, nz = _random_model(2, 1, 500, 9)
+    z = G(np.random.default_rng(4).uniform(-1, 1, (1000, 3)))
+    mk = lambda ws: se.B200GpCemSSM(None, 2, 1, ls, os_, nz, device=DEV, gemm_impl=_lib.SE_GEMM_TC, workspace_bytes=ws)
+    big, small = mk(None), mk(2 * 256 * 512 * 8)  # 256 rows per chunk
+    for gp in (big, small):
+        gp.update_model(G(x), G(y), replace_old=True)
+    a = big.predict_with_jacobians(z[:, :2].contiguous(), z[:, 2:].contiguous())
+    b = small.predict_with_jacobians(z[:, :2].contiguous(), z[:, 2:].contiguous())
+    c = big.predict_with_jacobians(z[:, :2].contiguous(), z[:, 2:].contiguous())
+    for s, t, r in zip(a, b, c):
+        assert torch.equal(s, t) and torch.equal(s, r)
+
+
+def test_tc_model_update_rebuilds_the_digit_image():
+    """update_model appends data (ssm_cem.py:72-99): the digit image of the new factor must be used afterwards."""
+    x, y, ls, os_, nz = _random_model(2, 1, 600, 11)
+    gp = se.B200GpCemSSM(None, 2, 1, ls, os_, nz, device=DEV, gemm_impl=_lib.SE_GEMM_TC)
+    gp.update_model(G(x[:300]), G(y[:300]), replace_old=True)
+    z = np.random.default_rng(5).uniform(-1, 1, (200, 3))
+    gp.predict_without_jacobians(G(z[:, :2]), G(z[:, 2:]))
+    gp.update_model(G(x[300:]), G(y[300:]))
+    _, var = gp.predict_without_jacobians(G(z[:, :2]), G(z[:, 2:]))
+    ref = oracle.OracleGpCemSSM(2, 1, ls, os_, nz)
+    ref.update_model(T(x), T(y), replace_old=True)
+    _, v0 = ref.predict_without_jacobians(T(z[:, :2]), T(z[:, 2:]))
+    assert rel_err(var.cpu(), v0) < 1e-8
+
+
+@pytest.mark.parametrize('pipeline', ['0', '1'])
+def test_tc_cem_solve_matches_oracle(pipeline, monkeypatch):
+    """Full safe CEM-MPC solve on the tensor-core path (pendulum, n = 400): same elites, same constraint decisions,
+    costs to 1e-8 -- with and without the two-stream population pipeline."""
+    monkeypatch.setenv('SE_PIPELINE', pipeline)
+    w = workloads.pendulum_workload(n_train=400, num_rollouts=1024, time_horizon=6, num_elites=32, num_iterations=3,
+                                    name='tc')
+    ssm, mpc = workloads.build_solver(w, record='full', seed=11)
+    assert ssm.gemm_info()[0] == 'tcgen05-i8'
+    res = mpc.solve(G(w.p0).unsqueeze(0), seed=11)
+    noise = np.stack([oracle.philox_normal_noise(11, i, 0, w.num_rollouts, w.time_horizon, 1)
+                      for i in range(w.num_iterations)])
+    gp = oracle.OracleGpCemSSM(2, 1, w.lengthscale, w.outputscale, w.noise)
+    gp.update_model(T(w.x_train), T(w.y_train), replace_old=True)
+    prob = oracle.SafeCemProblem(gp, w.l_mu, w.l_sigma, w.k_fb, w.a, w.b, w.beta_safety, w.h_mat, w.h_vec, w.act_a,
+                                 w.act_b)
+    ref = oracle.cem_solve(prob, T(w.p0), T(noise), w.num_elites)
+    assert np.array_equal(res['elite_ids'][:, 0].cpu().numpy(), ref['elite_ids'].numpy())
+    for i, r in enumerate(ref['rollouts']):
+        assert np.array_equal(res['constraint'][i, 0].cpu().numpy(), r.constraint_costs.numpy())
+        assert rel_err(res['objective'][i, 0].cpu().numpy(), r.objective_costs.numpy()) < 1e-8
+        assert rel_err(res['trajectories'][i, 0].cpu().numpy(), r.trajectories.numpy(), 1e-6) < 1e-7
+    assert int(res['best_id'][0]) == ref['best_id']

@@ -20,7 +20,7 @@ def run(w, N, seed=0):
     torch.cuda.synchronize()
     for S in (8, 7, 6, 5):
         ssm.set_gemm_impl(_lib.SE_GEMM_TC)
-        _lib.check(lib.se_gp_set_tc_digits(ssm.handle, S))
+        ssm.set_tc_digits(S)
         m1, v1, j1 = ssm.predict_with_jacobians(z[:, :w.n_s], z[:, w.n_s:])
         torch.cuda.synchronize()
         rel = ((v1 - v0).abs() / v0.abs())
