@@ -219,7 +219,8 @@ uint64_t se_launch_count(void);      /* kernels launched by this library since l
 void se_launch_count_reset(void);
 /* Runs a register-resident FMA loop on every SM and returns the measured FLOP/s (synchronises the device).
  * kind: 0 = FP32 FFMA, 1 = FP64 DFMA, 2 = FP64 DMMA m8n8k4, 3 = int8 tcgen05.mma (OP/s = 2 x MAC/s, operands resident; burst),
- *       4 = the same sustained for ~1.5 s (what the pipe delivers under the 1 kW power cap) */
+ *       4 = the same sustained for ~1.5 s (what the pipe delivers under the 1 kW power cap),
+ *       5 / 6 = burst / sustained with the variance GEMM's own instruction shape (128 x 64 x 32, A tile reused) */
 int se_measure_peak(int kind, double* flops_out);
 /* Device time (ms, CUDA events recorded by the library on the launch stream) spent in the variance GEMM kernel and
  * in the kernel-row kernel since the last reset, and their launch counts; timing must be enabled first

@@ -50,8 +50,8 @@ int launch_kstar_slices(const GpDev<double>& gp, const double* p, int64_t p_stri
 }
 
 template <int S, bool REUSE>
-static int launch_oz_gemm_s(const int8_t* a_img, const int8_t* b_img, const double* scale_b, int n_pad, int rows_pad,
-                            const TriOrder& od, int grid, double* partial, cudaStream_t stream) {
+static int launch_oz_gemm_s(const int8_t* a_img, const int8_t* b_img, const double* scale_b, int n, int n_pad,
+                            int rows_pad, const TriOrder& od, int grid, double* partial, cudaStream_t stream) {
   using C = oz::Cfg<S>;
   static bool attr_set = false;
   if (!attr_set) {
@@ -60,16 +60,16 @@ static int launch_oz_gemm_s(const int8_t* a_img, const int8_t* b_img, const doub
     attr_set = true;
   }
   static const int dbg = getenv("SE_OZ_DBG") ? atoi(getenv("SE_OZ_DBG")) : 0;  // measurement knobs, see the kernel
-  SE_LAUNCH((oz::gp_trisumsq_ozaki_kernel<S, REUSE>), grid, oz::THREADS, C::SMEM_BYTES, stream, a_img, b_img, scale_b, n_pad,
-            rows_pad, od, partial, dbg);
+  SE_LAUNCH((oz::gp_trisumsq_ozaki_kernel<S, REUSE>), grid, oz::THREADS, C::SMEM_BYTES, stream, a_img, b_img, scale_b, n,
+            n_pad, rows_pad, od, partial, dbg);
   return 0;
 }
 
-int launch_trisumsq_ozaki(const int8_t* a_img, const int8_t* b_img, const double* scale_b, int n_pad, int rows_pad,
-                          int ns, int S, double* partial, int sm_count, int* nb_out, cudaStream_t stream) {
+int launch_trisumsq_ozaki(const int8_t* a_img, const int8_t* b_img, const double* scale_b, int n, int n_pad,
+                          int rows_pad, int ns, int S, double* partial, int sm_count, int* nb_out, cudaStream_t stream) {
   static const int64_t l2_budget = getenv("SE_OZ_L2MB") ? atoll(getenv("SE_OZ_L2MB")) << 20 : (64ll << 20);
   TriOrder od;
-  od.nb = n_pad / oz::TN;
+  od.nb = (n + oz::TN - 1) / oz::TN;  // row tiles that hold at least one training point
   od.rt_count = rows_pad / oz::TM;
   od.ns = ns;
   int64_t rc = l2_budget / ((int64_t)oz::TM * n_pad * S * ns);
@@ -82,8 +82,8 @@ int launch_trisumsq_ozaki(const int8_t* a_img, const int8_t* b_img, const double
   static const int reuse = getenv("SE_OZ_REUSE") ? atoi(getenv("SE_OZ_REUSE")) : 1;
 #define SE_OZ_CASE(S_)                                                                                               \
   case S_:                                                                                                           \
-    return reuse ? launch_oz_gemm_s<S_, true>(a_img, b_img, scale_b, n_pad, rows_pad, od, grid, partial, stream)     \
-                 : launch_oz_gemm_s<S_, false>(a_img, b_img, scale_b, n_pad, rows_pad, od, grid, partial, stream);
+    return reuse ? launch_oz_gemm_s<S_, true>(a_img, b_img, scale_b, n, n_pad, rows_pad, od, grid, partial, stream)     \
+                 : launch_oz_gemm_s<S_, false>(a_img, b_img, scale_b, n, n_pad, rows_pad, od, grid, partial, stream);
   switch (S) {
     SE_OZ_CASE(5)
     SE_OZ_CASE(6)
@@ -122,22 +122,22 @@ int launch_oz_probe(const int8_t* a_img, const int8_t* b_img, int nk, int S, int
 
 // measured int8 tensor-pipe peak in OP/s (2 x MAC).  sustained = 0: best of a few short launches (burst clocks);
 // sustained = 1: launches back to back for ~1.5 s and reports the last third (the 1 kW power cap has settled by then).
-int measure_peak_i8(int sustained, double* ops_out) {
+int measure_peak_i8(int sustained, int n_mma, double* ops_out) {
   int dev = 0, sms = 0;
   SE_CUDA(cudaGetDevice(&dev));
   SE_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
-  const int smem = 14 * 1024, iters = 40000;
+  const int smem = 14 * 1024, iters = 40000 * (256 / n_mma);
   SE_CUDA(cudaFuncSetAttribute(oz::oz_peak_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
   cudaEvent_t e0, e1;
   SE_CUDA(cudaEventCreate(&e0));
   SE_CUDA(cudaEventCreate(&e1));
-  const double ops = (double)sms * iters * (2.0 * 128 * 256 * 32);
+  const double ops = (double)sms * iters * (2.0 * 128 * n_mma * 32);
   double result = 0.0;
   if (!sustained) {
     double best_ms = 1e30;
     for (int rep = 0; rep < 4; ++rep) {
       SE_CUDA(cudaEventRecord(e0, 0));
-      SE_LAUNCH(oz::oz_peak_kernel, sms, 128, smem, 0, iters, nullptr);
+      SE_LAUNCH(oz::oz_peak_kernel, sms, 128, smem, 0, iters, n_mma, nullptr);
       SE_CUDA(cudaEventRecord(e1, 0));
       SE_CUDA(cudaEventSynchronize(e1));
       float ms = 0.f;
@@ -149,7 +149,7 @@ int measure_peak_i8(int sustained, double* ops_out) {
     const int reps = 450;  // ~3 ms each
     for (int rep = 0; rep < reps; ++rep) {
       if (rep == reps * 2 / 3) SE_CUDA(cudaEventRecord(e0, 0));
-      SE_LAUNCH(oz::oz_peak_kernel, sms, 128, smem, 0, iters, nullptr);
+      SE_LAUNCH(oz::oz_peak_kernel, sms, 128, smem, 0, iters, n_mma, nullptr);
     }
     SE_CUDA(cudaEventRecord(e1, 0));
     SE_CUDA(cudaEventSynchronize(e1));

@@ -88,8 +88,8 @@ extern "C" int se_version(void) { return 100; }
 extern "C" uint64_t se_launch_count(void) { return g_launches.load(); }
 extern "C" void se_launch_count_reset(void) { g_launches.store(0); }
 extern "C" int se_measure_peak(int kind, double* flops_out) {
-  SE_REQUIRE(kind >= 0 && kind <= 4 && flops_out, "se_measure_peak: bad arguments");
-  if (kind >= 3) return measure_peak_i8(kind == 4, flops_out);
+  SE_REQUIRE(kind >= 0 && kind <= 6 && flops_out, "se_measure_peak: bad arguments");
+  if (kind >= 3) return measure_peak_i8(kind == 4 || kind == 6, kind >= 5 ? 64 : 256, flops_out);
   return measure_peak(kind, flops_out);
 }
 
@@ -357,7 +357,7 @@ static int post_gemm(se_gp_s* g, const GpDev<T>& gd, PostPart& pp, cudaStream_t 
   if (g->timing) SE_TRY(record_event(g->ev_gemm, st));
   if constexpr (sizeof(T) == 8) {
     if (tc)
-      SE_TRY(launch_trisumsq_ozaki((const int8_t*)pp.kst, g->b_img, g->scale_b, g->n_pad, pp.rows_pad, g->ns,
+      SE_TRY(launch_trisumsq_ozaki((const int8_t*)pp.kst, g->b_img, g->scale_b, g->n, g->n_pad, pp.rows_pad, g->ns,
                                    g->tc_digits, (double*)pp.partial, g->sm_count, &pp.nb, st));
   }
   if (!tc)
