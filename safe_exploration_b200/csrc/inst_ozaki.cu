@@ -31,17 +31,27 @@ int launch_oz_pack_model(const double* w, int n_pad, int ns, const double* host_
 int launch_kstar_slices(const GpDev<double>& gp, const double* p, int64_t p_stride, const double* u, int64_t u_stride,
                         int64_t row0, int nrows, int rows_pad, const int* exp_a, int S, int8_t* a_img, double* mean,
                         double* jac, cudaStream_t stream) {
-  const int warps = rows_pad / 2;
+  // rows per warp: 1 caps the kernel at 128 registers = 2 CTAs / SM, which hides the dependent DFMA chains of exp()
+  // better than the wider 2-row variant (C2: 0.224 vs 0.251 ms, C3: 1.08 vs 1.24 ms per launch)
+  static const int r_env = getenv("SE_KSTAR_R") ? atoi(getenv("SE_KSTAR_R")) : 0;
+  const int R = r_env == 2 ? 2 : 1;
+  const int warps = rows_pad / R;
   const int grid = (int)ceil_div(warps, 8);
   const bool want_jac = jac != nullptr;
 #define SE_CASE(NS_, NU_)                                                                                        \
   if (gp.ns == NS_ && gp.nu == NU_) {                                                                            \
-    if (want_jac)                                                                                                \
-      SE_LAUNCH((oz::gp_kstar_slices_kernel<NS_, NS_ + NU_, true>), grid, 256, 0, stream, gp, p, p_stride, u,    \
+    if (want_jac && R == 1)                                                                                      \
+      SE_LAUNCH((oz::gp_kstar_slices_kernel<NS_, NS_ + NU_, true, 1>), grid, 256, 0, stream, gp, p, p_stride, u, \
                 u_stride, row0, nrows, rows_pad, exp_a, S, a_img, mean, jac);                                    \
+    else if (want_jac)                                                                                           \
+      SE_LAUNCH((oz::gp_kstar_slices_kernel<NS_, NS_ + NU_, true, 2>), grid, 256, 0, stream, gp, p, p_stride, u, \
+                u_stride, row0, nrows, rows_pad, exp_a, S, a_img, mean, jac);                                    \
+    else if (R == 1)                                                                                             \
+      SE_LAUNCH((oz::gp_kstar_slices_kernel<NS_, NS_ + NU_, false, 1>), grid, 256, 0, stream, gp, p, p_stride,   \
+                u, u_stride, row0, nrows, rows_pad, exp_a, S, a_img, mean, jac);                                 \
     else                                                                                                         \
-      SE_LAUNCH((oz::gp_kstar_slices_kernel<NS_, NS_ + NU_, false>), grid, 256, 0, stream, gp, p, p_stride, u,   \
-                u_stride, row0, nrows, rows_pad, exp_a, S, a_img, mean, jac);                                    \
+      SE_LAUNCH((oz::gp_kstar_slices_kernel<NS_, NS_ + NU_, false, 2>), grid, 256, 0, stream, gp, p, p_stride,   \
+                u, u_stride, row0, nrows, rows_pad, exp_a, S, a_img, mean, jac);                                 \
     return 0;                                                                                                    \
   }
   SE_FOR_NS_NU(SE_CASE)

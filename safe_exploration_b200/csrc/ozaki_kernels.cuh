@@ -42,7 +42,9 @@ __host__ __device__ __forceinline__ int blk_off(int r, int c) {
 
 template <int S>
 struct Cfg {
-  static constexpr int STAGE_BYTES = S * (A_BLK + B_BLK);
+  static constexpr int KS = 2;  // K steps per pipeline stage (one barrier round trip per KS * S (S + 1) / 2 MMAs)
+  static constexpr int STEP_BYTES = S * (A_BLK + B_BLK);
+  static constexpr int STAGE_BYTES = KS * STEP_BYTES;
   static constexpr int STAGES = (220 * 1024) / STAGE_BYTES;
   static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*alignment slack*/ + 256 /*barriers*/;
   static constexpr int PAIRS = S * (S + 1) / 2;
@@ -255,12 +257,11 @@ __global__ void oz_pack_b_kernel(const double* __restrict__ w, int n_pad, const 
 // One warp owns R = 2 candidate rows (an even/odd pair shares every 32-byte sector of the image); a lane owns 4
 // consecutive training points per 128-point block, so each digit plane is written with one 32-bit store per lane.
 // ---------------------------------------------------------------------------------------------------------------------
-template <int NS, int D, bool JAC>
-__global__ void __launch_bounds__(256)
+template <int NS, int D, bool JAC, int R>
+__global__ void __launch_bounds__(256, R == 1 ? 2 : 1)
 gp_kstar_slices_kernel(GpDev<double> gp, const double* __restrict__ p, int64_t p_stride, const double* __restrict__ u,
                        int64_t u_stride, int64_t row0, int nrows, int rows_pad, const int* __restrict__ exp_a, int S,
                        int8_t* __restrict__ a_img, double* __restrict__ mean, double* __restrict__ jac) {
-  constexpr int R = 2;
   const int lane = threadIdx.x & 31;
   const int64_t warp = blockIdx.x * (int64_t)(blockDim.x >> 5) + (threadIdx.x >> 5);
   const int64_t r0 = warp * R;
@@ -444,15 +445,16 @@ gp_trisumsq_ozaki_kernel(const int8_t* __restrict__ a_img, const int8_t* __restr
         const int8_t* a_src = a_img + ((int64_t)it.o * od.rt_count + it.rt) * nkb * (int64_t)(S * A_BLK);
         const int8_t* b_src = b_img + ((int64_t)it.o * nb_img + it.ib) * nkb * (int64_t)(S * B_BLK);
         const int nk = item_ksteps(it.ib, n);
-        for (int kb = 0; kb < nk; ++kb) {
+        for (int kb = 0; kb < nk; kb += C::KS) {
+          const int ks = min(C::KS, nk - kb);  // K steps in this stage: stage = [A digits of ks steps | B digits]
           mbar_wait(empty_bar(stage), phase ^ 1u);
           if (dbg & 1) {  // measurement only: no operand traffic
             mbar_arrive(full_bar(stage));
           } else {
-            mbar_expect_tx(full_bar(stage), C::STAGE_BYTES);
+            mbar_expect_tx(full_bar(stage), ks * C::STEP_BYTES);
             const uint32_t dst = base + stage * C::STAGE_BYTES;
-            bulk_g2s(dst, a_src + (int64_t)kb * (S * A_BLK), S * A_BLK, full_bar(stage));
-            bulk_g2s(dst + S * A_BLK, b_src + (int64_t)kb * (S * B_BLK), S * B_BLK, full_bar(stage));
+            bulk_g2s(dst, a_src + (int64_t)kb * (S * A_BLK), ks * S * A_BLK, full_bar(stage));
+            bulk_g2s(dst + C::KS * S * A_BLK, b_src + (int64_t)kb * (S * B_BLK), ks * S * B_BLK, full_bar(stage));
           }
           if (++stage == C::STAGES) stage = 0, phase ^= 1u;
         }
@@ -474,14 +476,20 @@ gp_trisumsq_ozaki_kernel(const int8_t* __restrict__ a_img, const int8_t* __restr
       const uint32_t idesc = make_idesc(TM, item_cols(it.ib, n));
       mbar_wait(tmem_empty, tphase ^ 1u);  // the epilogue has drained the previous item's accumulators
       tc_fence_after();
-      for (int kb = 0; kb < nk; ++kb) {
+      for (int kb = 0; kb < nk; kb += C::KS) {
+        const int ks = min(C::KS, nk - kb);
         mbar_wait(full_bar(stage), phase);
         tc_fence_after();
         const uint32_t a_lo = a_lo0 + stage * (C::STAGE_BYTES >> 4);
+        const uint32_t b_lo = a_lo + (C::KS * S * A_BLK >> 4);
         if (elect_one()) {
-          issue_kstep<S, REUSE>(tb, a_lo, a_lo + (S * A_BLK >> 4), dhi, idesc, kb > 0 ? 1u : 0u);
+#pragma unroll
+          for (int k = 0; k < C::KS; ++k)
+            if (k < ks)
+              issue_kstep<S, REUSE>(tb, a_lo + k * (S * A_BLK >> 4), b_lo + k * (S * B_BLK >> 4), dhi, idesc,
+                                    kb + k > 0 ? 1u : 0u);
           tc_commit(empty_bar(stage));  // frees the stage once these MMAs have read it
-          if (kb == nk - 1) tc_commit(tmem_full);
+          if (kb + ks == nk) tc_commit(tmem_full);
         }
         __syncwarp();
         if (++stage == C::STAGES) stage = 0, phase ^= 1u;
