@@ -191,7 +191,9 @@ class B200GpCemSSM(CemSSM):
         k.diagonal(dim1=1, dim2=2).add_(self.noise.to(self.device).view(-1, 1))
         chol = torch.linalg.cholesky(k)
         del k
-        alpha = torch.cholesky_solve(y.t().unsqueeze(-1), chol).squeeze(-1)
+        # alpha = (L L^T)^-1 y by two triangular solves (cholesky_solve's batched cuSOLVER path rejects n = 16384)
+        alpha = torch.linalg.solve_triangular(chol, y.t().unsqueeze(-1), upper=False)
+        alpha = torch.linalg.solve_triangular(chol.transpose(1, 2), alpha, upper=True).squeeze(-1)
         eye = torch.eye(n, dtype=torch.float64, device=self.device).expand(self.num_states, -1, -1)
         linv = torch.linalg.solve_triangular(chol, eye, upper=False).tril_()
         del chol
