@@ -116,11 +116,13 @@ class B200GpCemSSM(CemSSM):
     :param conf: optional config object; `exact_gp_training_iterations` and `exact_gp_kernel` are read if present
                  (only 'rbf' is accelerated; the reference's 'linear' / 'nn' kernels stay on GPyTorch).
     :param dtype: torch.float64 (reference precision, default) or torch.float32
+    :param incremental: keep the float64 inverse Cholesky factor on the device (n_s n^2 doubles) so that
+                        `update_model(..., replace_old=False)` only computes the rows of the appended samples
     """
 
     def __init__(self, conf, state_dimen: int, action_dimen: int, lengthscale=None, outputscale=None, noise=None,
                  dtype: torch.dtype = torch.float64, device: Optional[str] = None, gemm_impl: int = _lib.SE_GEMM_AUTO,
-                 workspace_bytes: Optional[int] = None, tc_digits: int = 0):
+                 workspace_bytes: Optional[int] = None, tc_digits: int = 0, incremental: bool = True):
         super().__init__(state_dimen, action_dimen)
         kernel = getattr(conf, 'exact_gp_kernel', 'rbf') if conf is not None else 'rbf'
         if kernel != 'rbf':
@@ -140,6 +142,8 @@ class B200GpCemSSM(CemSSM):
         self.noise = torch.full((state_dimen,), ln2, **f64) if noise is None else \
             torch.as_tensor(noise, **f64).reshape(state_dimen).clone()
         self._gemm_impl = gemm_impl
+        self._incremental = incremental  # keep the float64 inverse factor so appended samples cost O(m n^2)
+        self._factor = None              # (x [n, d], L^-1 [n_s, n, n], hyper-parameters) of the current handle
         self._tc_digits = tc_digits
         self._workspace_bytes = workspace_bytes
         self._handle = C.c_void_p(None)
@@ -186,17 +190,25 @@ class B200GpCemSSM(CemSSM):
         x = x_train.detach().to(device=self.device, dtype=torch.float64)
         y = y_train.detach().to(device=self.device, dtype=torch.float64)
         n = x.size(0)
-        ls = self.lengthscale.to(self.device)
-        k = _rbf_ard(x, x, ls, self.outputscale.to(self.device))
-        k.diagonal(dim1=1, dim2=2).add_(self.noise.to(self.device).view(-1, 1))
-        chol = torch.linalg.cholesky(k)
-        del k
-        # alpha = (L L^T)^-1 y by two triangular solves (cholesky_solve's batched cuSOLVER path rejects n = 16384)
-        alpha = torch.linalg.solve_triangular(chol, y.t().unsqueeze(-1), upper=False)
-        alpha = torch.linalg.solve_triangular(chol.transpose(1, 2), alpha, upper=True).squeeze(-1)
-        eye = torch.eye(n, dtype=torch.float64, device=self.device).expand(self.num_states, -1, -1)
-        linv = torch.linalg.solve_triangular(chol, eye, upper=False).tril_()
-        del chol
+        hyp = torch.cat((self.lengthscale.reshape(-1), self.outputscale, self.noise))
+        linv = self._append_rows(x, hyp) if self._incremental else None
+        self.last_update = 'full' if linv is None else 'incremental'
+        if linv is None:
+            ls = self.lengthscale.to(self.device)
+            k = _rbf_ard(x, x, ls, self.outputscale.to(self.device))
+            k.diagonal(dim1=1, dim2=2).add_(self.noise.to(self.device).view(-1, 1))
+            chol = torch.linalg.cholesky(k)
+            del k
+            eye = torch.eye(n, dtype=torch.float64, device=self.device).expand(self.num_states, -1, -1)
+            linv = torch.linalg.solve_triangular(chol, eye, upper=False).tril_()
+            # alpha = (L L^T)^-1 y by two triangular solves (cholesky_solve's batched cuSOLVER path rejects n = 16384)
+            alpha = torch.linalg.solve_triangular(chol, y.t().unsqueeze(-1), upper=False)
+            alpha = torch.linalg.solve_triangular(chol.transpose(1, 2), alpha, upper=True).squeeze(-1)
+            del chol
+        else:
+            alpha = torch.matmul(linv.transpose(1, 2), torch.matmul(linv, y.t().unsqueeze(-1))).squeeze(-1)
+        if self._incremental:
+            self._factor = (x, linv, hyp)
         xs = x.to(self.dtype).contiguous()
         al = alpha.to(self.dtype).contiguous()
         li = linv.to(self.dtype).contiguous()
@@ -217,6 +229,39 @@ class B200GpCemSSM(CemSSM):
             _lib.check(self._lib.se_gp_set_tc_digits(handle, self._tc_digits))
         if self._workspace_bytes is not None:
             _lib.check(self._lib.se_gp_set_workspace_limit(handle, int(self._workspace_bytes)))
+
+    def _append_rows(self, x: Tensor, hyp: Tensor) -> Optional[Tensor]:
+        """Incremental factor update (the idea of ssm_pytorch/utilities.py:122-165 `update_cholesky`):
+        when `update_model` appended m samples to the n the factor was built on, with unchanged hyper-parameters,
+
+            L' = [[L, 0], [B, C]],  B = K(new, old) L^-T,  C C^T = K(new, new) + noise I - B B^T
+            L'^-1 = [[L^-1, 0], [-C^-1 B L^-1, C^-1]]
+
+        so the first n rows of L^-1 are kept and only m new rows are computed: O(m n^2) instead of O(n^3).
+        Returns the new [n_s, n + m, n + m] inverse factor, or None when a full factorisation is needed."""
+        if self._factor is None:
+            return None
+        x_old, linv_old, hyp_old = self._factor
+        n_old, n = x_old.size(0), x.size(0)
+        if not (n_old < n and hyp_old.shape == hyp.shape and torch.equal(hyp_old, hyp) and
+                torch.equal(x[:n_old], x_old)):
+            return None
+        ls, os_, nz = (t.to(self.device) for t in (self.lengthscale, self.outputscale, self.noise))
+        x_add = x[n_old:]
+        m = n - n_old
+        k_cross = _rbf_ard(x_add, x_old, ls, os_)                       # [n_s, m, n]
+        b = torch.matmul(k_cross, linv_old.transpose(1, 2))             # B = K(new, old) L^-T
+        s = _rbf_ard(x_add, x_add, ls, os_) - torch.matmul(b, b.transpose(1, 2))
+        s.diagonal(dim1=1, dim2=2).add_(nz.view(-1, 1))
+        c = torch.linalg.cholesky(s)
+        c_inv = torch.linalg.solve_triangular(c, torch.eye(m, dtype=torch.float64, device=self.device)
+                                              .expand(self.num_states, -1, -1), upper=False).tril_()
+        low = -torch.matmul(c_inv, torch.matmul(b, linv_old))           # -C^-1 B L^-1
+        linv = torch.zeros((self.num_states, n, n), dtype=torch.float64, device=self.device)
+        linv[:, :n_old, :n_old] = linv_old
+        linv[:, n_old:, :n_old] = low
+        linv[:, n_old:, n_old:] = c_inv
+        return linv
 
     def _train_model(self, x_train: Tensor, y_train: Tensor) -> None:
         """gp_ssm_cem.py:103-129: Adam(lr=0.01) on the exact marginal log likelihood, softplus-parametrised like

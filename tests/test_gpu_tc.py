@@ -155,6 +155,32 @@ def test_tc_model_update_rebuilds_the_digit_image():
     assert rel_err(var.cpu(), v0) < 1e-8
 
 
+def test_incremental_model_update_equals_full_refactorisation():
+    """appending samples (update_model(replace_old=False), ssm_cem.py:72-99) only computes the new rows
+    of L^-1; predictions must equal those of a model factorised from scratch, and the path taken is reported."""
+    x, y, ls, os_, nz = _random_model(2, 1, 700, 21)
+    z = np.random.default_rng(6).uniform(-1, 1, (300, 3))
+    inc = se.B200GpCemSSM(None, 2, 1, ls, os_, nz, device=DEV)
+    inc.update_model(G(x[:400]), G(y[:400]), replace_old=True)
+    assert inc.last_update == 'full'
+    for lo, hi in ((400, 401), (401, 530), (530, 700)):
+        inc.update_model(G(x[lo:hi]), G(y[lo:hi]))
+        assert inc.last_update == 'incremental' and inc.x_train.shape[0] == hi
+    full = se.B200GpCemSSM(None, 2, 1, ls, os_, nz, device=DEV, incremental=False)
+    full.update_model(G(x), G(y), replace_old=True)
+    assert full.last_update == 'full'
+    a = inc.predict_with_jacobians(G(z[:, :2]), G(z[:, 2:]))
+    b = full.predict_with_jacobians(G(z[:, :2]), G(z[:, 2:]))
+    for s_, t_ in zip(a, b):
+        assert rel_err(s_.cpu(), t_.cpu(), 1e-3 * float(t_.abs().max())) < 1e-8
+    # changed hyper-parameters or replaced data force a full factorisation
+    inc.noise = inc.noise * 2
+    inc.update_model(G(x[:5]), G(y[:5]))
+    assert inc.last_update == 'full'
+    inc.update_model(G(x[:300]), G(y[:300]), replace_old=True)
+    assert inc.last_update == 'full'
+
+
 @pytest.mark.parametrize('pipeline', ['0', '1'])
 def test_tc_cem_solve_matches_oracle(pipeline, monkeypatch):
     """Full safe CEM-MPC solve on the tensor-core path (pendulum, n = 400): same elites, same constraint decisions,
