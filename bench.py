@@ -151,6 +151,23 @@ class ClockSampler:
                 'reasons': sorted(self.reasons), 'samples': len(self.samples)}
 
 
+def profiled_traffic(kernel_substr: str):
+    """DRAM bytes (read + write) per launch of the dominant kernel from the committed `ncu --set full` capture of this
+    workload (profiles/r01_ncu_full_tc_c2.csv), or None.  The capture is of the default C2 / tcgen05 configuration."""
+    import csv
+    path = os.path.join(ROOT, 'profiles', 'r01_ncu_full_tc_c2.csv')
+    try:
+        rows = list(csv.reader(open(path)))
+        head, units = rows[0], rows[1]
+        name, rd, wr = head.index('Kernel Name'), head.index('dram__bytes_read.sum'), head.index('dram__bytes_write.sum')
+        scale = {'byte': 1.0, 'Kbyte': 1e3, 'Mbyte': 1e6, 'Gbyte': 1e9}
+        vals = [float(r[rd]) * scale[units[rd]] + float(r[wr]) * scale[units[wr]]
+                for r in rows[2:] if kernel_substr in r[name]]
+        return sum(vals) / len(vals) if vals else None
+    except Exception:
+        return None
+
+
 def measured_peaks():
     path = os.path.join(ROOT, 'MEASURED_PEAKS.json')
     if os.path.exists(path):
@@ -301,7 +318,9 @@ def run_b200(args):
         'fp64_equivalent_tflops': fp64_equiv, 'fp64_pipe_peak_tflops': fp64_peak,
         'share_of_step': gemm_ms.value / ms_total if ms_total > 0 else None,
         'kstar_share_of_step': kstar_ms.value / ms_total if ms_total > 0 else None,
-        'traffic': None,
+        'traffic': profiled_traffic('gp_trisumsq_ozaki') if (impl_name == 'tcgen05-i8' and args.config == 'C2' and
+                                                             world == 1) else None,
+        'traffic_source': 'profiles/r01_ncu_full_tc_c2.csv (ncu --set full, dram__bytes_read.sum + dram__bytes_write.sum)',
         'hbm': {'algorithmic_bytes_per_launch': (w.n_s * rows_local * w.n_train + w.n_s * w.n_train ** 2 / 2) * op_bytes,
                 'peak_gbs': peaks.get('hbm_gbs')},
     }
