@@ -55,6 +55,7 @@ SIGNATURES = {
     "se_gp_set_tc_digits": (_i, [_vp, _i]),
     "se_gp_get_gemm_info": (_i, [_vp, C.POINTER(_i), C.POINTER(_i)]),
     "se_debug_tc_probe": (_i, [_vp, _vp, _i, _i, _i, _i, _vp, _vp]),
+    "se_debug_exp": (_i, [_vp, _i64, _vp, _vp]),
     "se_gp_predict": (_i, [_vp, _vp, _i64, _vp, _vp, _vp, _vp]),
     "se_reach_onestep": (_i, [_vp, C.POINTER(SeProblem), _vp, _vp, _vp, _i64, _vp, _vp, _vp, _vp, _vp]),
     "se_reach_multistep": (_i, [_vp, C.POINTER(SeProblem), _vp, _vp, _vp, _i64, _i, _dbl_p, _vp, _vp, _vp, _vp, _vp,

@@ -92,6 +92,37 @@ struct ProbDev {
   T act_penalty, state_penalty, objective_theta;
 };
 
+// exp(x) in double for finite x <= 700, without the special-case branch of the library routine (which keeps every exp()
+// of the kernel-row loop a serial 15-DFMA chain; without it the independent evaluations of a lane interleave).
+// x below -700 is clamped (2^k stays a normal number, so the scaling is one integer add; the kernel rows are quantised
+// to 2^-47 of the prior scale afterwards, so values below e^-700 are zero either way).  The clamp is an integer compare
+// on the high word.  NaN / +Inf are the CALLER's business (the kernel-row kernels poison the row's mean instead).
+// Polynomial: degree 11 through the Chebyshev nodes of |r| <= ln2/2, derived and checked by tools/exp_poly.py
+// (evaluation error 1.4 x 2^-53).
+__device__ __forceinline__ double exp_nb(double x) {
+  const bool tiny = (unsigned)__double2hiint(x) >= 0xC085E000u;  // x <= -700 (or -Inf)
+  const double xc = tiny ? -700.0 : x;
+  const double t = fma(xc, 1.4426950408889634, 6755399441055744.0);  // 1.5 * 2^52: k = rint(x log2 e) in the low word
+  const int k = __double2loint(t);
+  const double kf = t - 6755399441055744.0;
+  double r = fma(kf, -0.6931471805599453, xc);  // ln 2 = hi + lo
+  r = fma(kf, -2.3190468138462996e-17, r);
+  double p = 2.5110046444457486e-08;
+  p = fma(p, r, 2.76326511328741e-07);
+  p = fma(p, r, 2.7557240894691074e-06);
+  p = fma(p, r, 2.4801485451264055e-05);
+  p = fma(p, r, 0.00019841269890069431);
+  p = fma(p, r, 0.0013888888952343797);
+  p = fma(p, r, 0.008333333333319592);
+  p = fma(p, r, 0.04166666666648799);
+  p = fma(p, r, 0.1666666666666668);
+  p = fma(p, r, 0.5000000000000019);
+  p = fma(p, r, 1.0);
+  p = fma(p, r, 1.0);
+  return __hiloint2double(__double2hiint(p) + (k << 20), __double2loint(p));
+}
+__device__ __forceinline__ bool finite_f64(double x) { return (__double2hiint(x) & 0x7ff00000) != 0x7ff00000; }
+
 template <typename T>
 struct Num;
 template <>

@@ -31,13 +31,30 @@ int launch_oz_pack_model(const double* w, int n_pad, int ns, const double* host_
 int launch_kstar_slices(const GpDev<double>& gp, const double* p, int64_t p_stride, const double* u, int64_t u_stride,
                         int64_t row0, int nrows, int rows_pad, const int* exp_a, int S, int8_t* a_img, double* mean,
                         double* jac, cudaStream_t stream) {
-  // rows per warp: 1 caps the kernel at 128 registers = 2 CTAs / SM, which hides the dependent DFMA chains of exp()
-  // better than the wider 2-row variant (C2: 0.224 vs 0.251 ms, C3: 1.08 vs 1.24 ms per launch)
-  static const int r_env = getenv("SE_KSTAR_R") ? atoi(getenv("SE_KSTAR_R")) : 0;
+  // SE_KSTAR_R = 1 / 2: the one-warp-per-row(-pair) kernels, kept for comparison; default: the row-group kernel
+  static const int r_env = getenv("SE_KSTAR_R") ? atoi(getenv("SE_KSTAR_R")) : 8;
+  const bool want_jac = jac != nullptr;
+  if (r_env != 1 && r_env != 2) {
+    static const int nostore = getenv("SE_KSTAR_NOSTORE") ? atoi(getenv("SE_KSTAR_NOSTORE")) : 0;  // measurement only
+    if (nostore) S = 0;
+    const int grid8 = (int)ceil_div(rows_pad / 8, 2);
+#define SE_CASE8(NS_, NU_)                                                                                          \
+  if (gp.ns == NS_ && gp.nu == NU_) {                                                                               \
+    if (want_jac)                                                                                                   \
+      SE_LAUNCH((oz::gp_kstar_slices8_kernel<NS_, NS_ + NU_, true>), grid8, 64, 0, stream, gp, p, p_stride, u,      \
+                u_stride, row0, nrows, rows_pad, exp_a, S, a_img, mean, jac);                                       \
+    else                                                                                                            \
+      SE_LAUNCH((oz::gp_kstar_slices8_kernel<NS_, NS_ + NU_, false>), grid8, 64, 0, stream, gp, p, p_stride, u,     \
+                u_stride, row0, nrows, rows_pad, exp_a, S, a_img, mean, jac);                                       \
+    return 0;                                                                                                       \
+  }
+    SE_FOR_NS_NU(SE_CASE8)
+#undef SE_CASE8
+    return fail("unsupported (n_s, n_u) = (%d, %d)", gp.ns, gp.nu);
+  }
   const int R = r_env == 2 ? 2 : 1;
   const int warps = rows_pad / R;
   const int grid = (int)ceil_div(warps, 8);
-  const bool want_jac = jac != nullptr;
 #define SE_CASE(NS_, NU_)                                                                                        \
   if (gp.ns == NS_ && gp.nu == NU_) {                                                                            \
     if (want_jac && R == 1)                                                                                      \
@@ -59,18 +76,18 @@ int launch_kstar_slices(const GpDev<double>& gp, const double* p, int64_t p_stri
   return fail("unsupported (n_s, n_u) = (%d, %d)", gp.ns, gp.nu);
 }
 
-template <int S, bool REUSE>
+template <int S, int MODE>
 static int launch_oz_gemm_s(const int8_t* a_img, const int8_t* b_img, const double* scale_b, int n, int n_pad,
                             int rows_pad, const TriOrder& od, int grid, double* partial, cudaStream_t stream) {
   using C = oz::Cfg<S>;
   static bool attr_set = false;
   if (!attr_set) {
-    SE_CUDA(cudaFuncSetAttribute((oz::gp_trisumsq_ozaki_kernel<S, REUSE>), cudaFuncAttributeMaxDynamicSharedMemorySize,
+    SE_CUDA(cudaFuncSetAttribute((oz::gp_trisumsq_ozaki_kernel<S, MODE>), cudaFuncAttributeMaxDynamicSharedMemorySize,
                                  C::SMEM_BYTES));
     attr_set = true;
   }
   static const int dbg = getenv("SE_OZ_DBG") ? atoi(getenv("SE_OZ_DBG")) : 0;  // measurement knobs, see the kernel
-  SE_LAUNCH((oz::gp_trisumsq_ozaki_kernel<S, REUSE>), grid, oz::THREADS, C::SMEM_BYTES, stream, a_img, b_img, scale_b, n,
+  SE_LAUNCH((oz::gp_trisumsq_ozaki_kernel<S, MODE>), grid, oz::THREADS, C::SMEM_BYTES, stream, a_img, b_img, scale_b, n,
             n_pad, rows_pad, od, partial, dbg);
   return 0;
 }
@@ -89,11 +106,12 @@ int launch_trisumsq_ozaki(const int8_t* a_img, const int8_t* b_img, const double
   const int64_t items = (int64_t)od.nb * od.rt_count * ns;
   const int grid = (int)(items < sm_count ? items : sm_count);
   *nb_out = 2 * od.nb;  // the epilogue writes one partial block per 32 columns
-  static const int reuse = getenv("SE_OZ_REUSE") ? atoi(getenv("SE_OZ_REUSE")) : 1;
+  static const int reuse = getenv("SE_OZ_REUSE") ? atoi(getenv("SE_OZ_REUSE")) : 2;
 #define SE_OZ_CASE(S_)                                                                                               \
   case S_:                                                                                                           \
-    return reuse ? launch_oz_gemm_s<S_, true>(a_img, b_img, scale_b, n, n_pad, rows_pad, od, grid, partial, stream)     \
-                 : launch_oz_gemm_s<S_, false>(a_img, b_img, scale_b, n, n_pad, rows_pad, od, grid, partial, stream);
+    return reuse == 2 ? launch_oz_gemm_s<S_, 2>(a_img, b_img, scale_b, n, n_pad, rows_pad, od, grid, partial, stream)  \
+           : reuse ? launch_oz_gemm_s<S_, 1>(a_img, b_img, scale_b, n, n_pad, rows_pad, od, grid, partial, stream)     \
+                   : launch_oz_gemm_s<S_, 0>(a_img, b_img, scale_b, n, n_pad, rows_pad, od, grid, partial, stream);
   switch (S) {
     SE_OZ_CASE(5)
     SE_OZ_CASE(6)
@@ -108,13 +126,16 @@ template <int S>
 static int launch_probe_s(const int8_t* a_img, const int8_t* b_img, int nk, uint32_t lbo, uint32_t sbo, int32_t* out,
                           cudaStream_t stream) {
   const int smem = S * (oz::A_BLK + oz::B_BLK) + 1024 + 64;
-  static const int reuse = getenv("SE_OZ_REUSE") ? atoi(getenv("SE_OZ_REUSE")) : 1;
-  if (reuse) {
-    SE_CUDA(cudaFuncSetAttribute((oz::oz_probe_kernel<S, true>), cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-    SE_LAUNCH((oz::oz_probe_kernel<S, true>), 1, 128, smem, stream, a_img, b_img, nk, lbo, sbo, out);
+  static const int reuse = getenv("SE_OZ_REUSE") ? atoi(getenv("SE_OZ_REUSE")) : 2;
+  if (reuse == 2) {
+    SE_CUDA(cudaFuncSetAttribute((oz::oz_probe_kernel<S, 2>), cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    SE_LAUNCH((oz::oz_probe_kernel<S, 2>), 1, 128, smem, stream, a_img, b_img, nk, lbo, sbo, out);
+  } else if (reuse) {
+    SE_CUDA(cudaFuncSetAttribute((oz::oz_probe_kernel<S, 1>), cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    SE_LAUNCH((oz::oz_probe_kernel<S, 1>), 1, 128, smem, stream, a_img, b_img, nk, lbo, sbo, out);
   } else {
-    SE_CUDA(cudaFuncSetAttribute((oz::oz_probe_kernel<S, false>), cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-    SE_LAUNCH((oz::oz_probe_kernel<S, false>), 1, 128, smem, stream, a_img, b_img, nk, lbo, sbo, out);
+    SE_CUDA(cudaFuncSetAttribute((oz::oz_probe_kernel<S, 0>), cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    SE_LAUNCH((oz::oz_probe_kernel<S, 0>), 1, 128, smem, stream, a_img, b_img, nk, lbo, sbo, out);
   }
   return 0;
 }
@@ -128,6 +149,16 @@ int launch_oz_probe(const int8_t* a_img, const int8_t* b_img, int nk, int S, int
     case 8: return launch_probe_s<8>(a_img, b_img, nk, lbo, sbo, out, stream);
   }
   return fail("probe: S = %d not compiled", S);
+}
+
+static __global__ void debug_exp_kernel(const double* __restrict__ x, int64_t n, double* __restrict__ out) {
+  const int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (i < n) out[i] = exp_nb(x[i]);
+}
+int launch_debug_exp(const double* x, int64_t n, double* out, cudaStream_t stream) {
+  if (n <= 0) return 0;
+  SE_LAUNCH(debug_exp_kernel, (int)ceil_div(n, (int64_t)256), 256, 0, stream, x, n, out);
+  return 0;
 }
 
 // measured int8 tensor-pipe peak in OP/s (2 x MAC).  sustained = 0: best of a few short launches (burst clocks);

@@ -129,27 +129,56 @@ __device__ __forceinline__ uint64_t pack_desc(uint32_t lo, uint32_t hi) {
   return d;
 }
 
+// instruction descriptor: c = s32 (2 << 4), a = b = signed 8 bit (1 << 7, 1 << 10), both K-major, N >> 3, M >> 4
+__host__ __device__ constexpr uint32_t make_idesc(int m, int n) {
+  return (2u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(n >> 3) << 17) | ((uint32_t)(m >> 4) << 24);
+}
+
 // All digit pairs (t, u), t + u <= S - 1, of one K step: level t + u accumulates A_t B_u^T.
 // a_lo / b_lo: low descriptor words of digit plane 0 (start address >> 4 | LBO); the other planes are a constant
-// number of 16-byte units further on, so a descriptor costs one add.  The issue rate matters: an N = 64 MMA occupies the
-// tensor core for only 32 cycles.
-template <int S, bool REUSE>
+// number of 16-byte units further on, so a descriptor costs one add.
+// MODE 0 / 1: one N = 64 MMA per pair (1: the A digit tile stays in the collector across its pairs).  The issue rate
+//   matters there: an N = 64 MMA occupies the tensor core for only 32 cycles.
+// MODE 2: the digit planes of L^-1 lie back to back in the stage (64 rows = 8 row groups each, SBO apart) and the level
+//   accumulators lie back to back in TMEM, so A_t times planes 0 .. S-1-t is ONE MMA of N = 64 (S - t) columns that
+//   lands on levels t .. S-1 -- split only where N would exceed 256.  S = 6: 9 MMAs per K step instead of 21.
+template <int S, int MODE>
 __device__ __forceinline__ void issue_kstep(uint32_t tmem_base, uint32_t a_lo, uint32_t b_lo, uint32_t desc_hi,
                                             uint32_t idesc, uint32_t not_first) {
+  if constexpr (MODE == 2) {
 #pragma unroll
-  for (int t = 0; t < S; ++t) {
-    const uint64_t ad = pack_desc(a_lo + t * (A_BLK >> 4), desc_hi);
+    for (int t = 0; t < S; ++t) {
+      const uint64_t ad = pack_desc(a_lo + t * (A_BLK >> 4), desc_hi);
+      const int planes = S - t, chunks = (planes + 3) / 4;
 #pragma unroll
-    for (int uu = 0; uu + t < S; ++uu) {
-      const uint64_t bd = pack_desc(b_lo + uu * (B_BLK >> 4), desc_hi);
-      // level t + uu is first written by the pair (0, t + uu) of K step 0
-      const uint32_t acc = t > 0 ? 1u : not_first;
-      const uint32_t dcol = tmem_base + (uint32_t)((t + uu) * TN);
-      const int uses = S - t;
-      if (!REUSE || uses == 1) mma_i8<0>(dcol, ad, bd, idesc, acc);
-      else if (uu == 0) mma_i8<1>(dcol, ad, bd, idesc, acc);
-      else if (uu == uses - 1) mma_i8<3>(dcol, ad, bd, idesc, acc);
-      else mma_i8<2>(dcol, ad, bd, idesc, acc);
+      for (int c = 0; c < chunks; ++c) {
+        const int cnt = planes - 4 * c < 4 ? planes - 4 * c : 4;
+        const uint64_t bd = pack_desc(b_lo + 4 * c * (B_BLK >> 4), desc_hi);
+        const uint32_t acc = t > 0 ? 1u : not_first;  // level l is first written by digit 0 of K step 0
+        const uint32_t dcol = tmem_base + (uint32_t)((t + 4 * c) * TN);
+        const uint32_t id = make_idesc(TM, cnt * TN);
+        if (chunks == 1) mma_i8<0>(dcol, ad, bd, id, acc);
+        else if (c == 0) mma_i8<1>(dcol, ad, bd, id, acc);
+        else if (c == chunks - 1) mma_i8<3>(dcol, ad, bd, id, acc);
+        else mma_i8<2>(dcol, ad, bd, id, acc);
+      }
+    }
+  } else {
+#pragma unroll
+    for (int t = 0; t < S; ++t) {
+      const uint64_t ad = pack_desc(a_lo + t * (A_BLK >> 4), desc_hi);
+#pragma unroll
+      for (int uu = 0; uu + t < S; ++uu) {
+        const uint64_t bd = pack_desc(b_lo + uu * (B_BLK >> 4), desc_hi);
+        // level t + uu is first written by the pair (0, t + uu) of K step 0
+        const uint32_t acc = t > 0 ? 1u : not_first;
+        const uint32_t dcol = tmem_base + (uint32_t)((t + uu) * TN);
+        const int uses = S - t;
+        if (MODE == 0 || uses == 1) mma_i8<0>(dcol, ad, bd, idesc, acc);
+        else if (uu == 0) mma_i8<1>(dcol, ad, bd, idesc, acc);
+        else if (uu == uses - 1) mma_i8<3>(dcol, ad, bd, idesc, acc);
+        else mma_i8<2>(dcol, ad, bd, idesc, acc);
+      }
     }
   }
 }
@@ -168,10 +197,6 @@ __device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.
 __device__ __forceinline__ uint64_t make_desc(uint32_t smem_addr, uint32_t lbo, uint32_t sbo) {
   return (uint64_t)((smem_addr >> 4) & 0x3FFFu) | ((uint64_t)((lbo >> 4) & 0x3FFFu) << 16) |
          ((uint64_t)((sbo >> 4) & 0x3FFFu) << 32) | (1ull << 46);
-}
-// instruction descriptor: c = s32 (2 << 4), a = b = signed 8 bit (1 << 7, 1 << 10), both K-major, N >> 3, M >> 4
-__host__ __device__ constexpr uint32_t make_idesc(int m, int n) {
-  return (2u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(n >> 3) << 17) | ((uint32_t)(m >> 4) << 24);
 }
 
 constexpr int RB = 8;  // radix bits
@@ -382,6 +407,170 @@ gp_kstar_slices_kernel(GpDev<double> gp, const double* __restrict__ p, int64_t p
 }
 
 // ---------------------------------------------------------------------------------------------------------------------
+// K1, row-group mapping (the default): one warp owns the 8 candidate rows of one core-matrix row group; lane = (row
+// lane & 7, quad lane >> 3) owns 4 consecutive training points of every 16-point K half.  A digit-plane store of the
+// warp is then one full 128-byte line (8 rows x 16 bytes, contiguous in the image), and a training point / alpha value
+// is fetched once per 8 candidates instead of once per candidate (the one-row-per-warp kernel above pulls 80 KB through
+// L1 per candidate at n = 2048 and sits at 84 % L1 throughput with the FP64 pipe at 41 %).
+// ---------------------------------------------------------------------------------------------------------------------
+template <int NS, int D, bool JAC>
+__global__ void __launch_bounds__(64, 8)
+gp_kstar_slices8_kernel(GpDev<double> gp, const double* __restrict__ p, int64_t p_stride, const double* __restrict__ u,
+                        int64_t u_stride, int64_t row0, int nrows, int rows_pad, const int* __restrict__ exp_a, int S,
+                        int8_t* __restrict__ a_img, double* __restrict__ mean, double* __restrict__ jac) {
+  const int lane = threadIdx.x & 31;
+  const int64_t warp = blockIdx.x * (int64_t)(blockDim.x >> 5) + (threadIdx.x >> 5);
+  const int64_t r0 = warp * 8;  // rows_pad is a multiple of 128 and the grid is rows_pad / 16 CTAs: every warp has rows
+  const int r8 = lane & 7, quad = lane >> 3;
+  const int64_t row = r0 + r8;
+  const bool valid = row < nrows;
+  const int n_pad = gp.n_pad;
+  const int nkb = n_pad / KB, rt_count = rows_pad / TM;
+
+  double z[D];
+#pragma unroll
+  for (int dd = 0; dd < D; ++dd) {
+    double v = 0.0;
+    if (valid) v = dd < NS ? p[(row0 + row) * p_stride + dd] : u[(row0 + row) * u_stride + (dd - NS)];
+    z[dd] = v;
+  }
+  double qscale[NS], log_s[NS], nh_inv_l2[NS][D];
+#pragma unroll
+  for (int o = 0; o < NS; ++o) {
+    log_s[o] = log(gp.outputscale[o]);
+    qscale[o] = ldexp(1.0, RB * MAX_S - 1 - exp_a[o]);
+#pragma unroll
+    for (int dd = 0; dd < D; ++dd) nh_inv_l2[o][dd] = -0.5 * gp.inv_l2[o][dd];
+  }
+  // exp_nb() wants finite arguments: a non-finite input or hyper-parameter poisons the row's mean (and Jacobian)
+  // instead, which is what the NaN check of the ellipsoid step looks at (gp_reachability_pytorch.py:234-243)
+  bool poison = false;
+#pragma unroll
+  for (int dd = 0; dd < D; ++dd) poison |= !finite_f64(z[dd]);
+#pragma unroll
+  for (int o = 0; o < NS; ++o) {
+    poison |= !finite_f64(log_s[o]) && log_s[o] > 0.0;
+    poison |= log_s[o] != log_s[o];
+#pragma unroll
+    for (int dd = 0; dd < D; ++dd) poison |= !finite_f64(nh_inv_l2[o][dd]);
+  }
+  double m_acc[NS], j_acc[NS][JAC ? D : 1];
+#pragma unroll
+  for (int o = 0; o < NS; ++o) {
+    m_acc[o] = 0.0;
+#pragma unroll
+    for (int dd = 0; dd < (JAC ? D : 1); ++dd) j_acc[o][dd] = 0.0;
+  }
+  // byte offset of (this lane's row, K index 4 quad) inside a digit-plane block; the K half adds 128
+  const int ct = (int)(r0 / TM), rl = (int)(r0 % TM) + r8;
+  int8_t* const img_row = a_img + (int64_t)ct * nkb * (int64_t)(S * A_BLK) + blk_off(rl, 4 * quad);
+  const int64_t img_o = (int64_t)rt_count * nkb * (int64_t)(S * A_BLK);
+
+  // Training inputs and alpha go through shared memory: the CTA copies them in chunks of 128 points with cp.async
+  // (no registers, double buffered, one chunk ahead), so a step reads its operands with short, fixed latency.  Straight
+  // global loads leave ~40 % of the issue slots waiting on L2 (ncu: long scoreboard at the first use of x) because
+  // ptxas sinks any register prefetch to the end of the loop body.
+  constexpr int CH = 128;  // points per chunk: 1 KB per array
+  __shared__ __align__(16) double stage[2][D + NS][CH];
+  auto fill = [&](int chunk, int buf) {
+#pragma unroll
+    for (int a = 0; a < D + NS; ++a) {
+      const double* src = (a < D ? gp.xt + (int64_t)a * n_pad : gp.alpha + (int64_t)(a - D) * n_pad) + chunk * CH +
+                          2 * threadIdx.x;  // 64 threads x 16 bytes = one array row of the chunk
+      const uint32_t dst = smem_u32(&stage[buf][a][2 * threadIdx.x]);
+      asm volatile("cp.async.cg.shared.global [%0], [%1], 16;\n" ::"r"(dst), "l"(src) : "memory");
+    }
+    asm volatile("cp.async.commit_group;\n" ::: "memory");
+  };
+  const int chunks = n_pad / CH;
+  fill(0, 0);
+#pragma unroll 1
+  for (int ch = 0; ch < chunks; ++ch) {
+    const int buf = ch & 1;
+    if (ch + 1 < chunks) {
+      fill(ch + 1, buf ^ 1);
+      asm volatile("cp.async.wait_group 1;\n" ::: "memory");
+    } else {
+      asm volatile("cp.async.wait_group 0;\n" ::: "memory");
+    }
+    __syncthreads();
+#pragma unroll 1
+  for (int jl = 0; jl < CH; jl += 16) {
+    const int j16 = ch * CH + jl;
+    double x[D][4], al[NS][4];
+#pragma unroll
+    for (int dd = 0; dd < D; ++dd) {
+      const double2 t0 = *reinterpret_cast<const double2*>(&stage[buf][dd][jl + 4 * quad]);
+      const double2 t1 = *reinterpret_cast<const double2*>(&stage[buf][dd][jl + 4 * quad + 2]);
+      x[dd][0] = t0.x, x[dd][1] = t0.y, x[dd][2] = t1.x, x[dd][3] = t1.y;
+    }
+#pragma unroll
+    for (int o = 0; o < NS; ++o) {
+      const double2 t0 = *reinterpret_cast<const double2*>(&stage[buf][D + o][jl + 4 * quad]);
+      const double2 t1 = *reinterpret_cast<const double2*>(&stage[buf][D + o][jl + 4 * quad + 2]);
+      al[o][0] = t0.x, al[o][1] = t0.y, al[o][2] = t1.x, al[o][3] = t1.y;
+    }
+    // zero-padded training points: finite garbage kernel values that meet alpha = 0 and zero columns of L^-1
+    long long q[NS][4];
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+      double diff[D], sq[D];
+#pragma unroll
+      for (int dd = 0; dd < D; ++dd) {
+        diff[dd] = z[dd] - x[dd][e];
+        sq[dd] = diff[dd] * diff[dd];
+      }
+#pragma unroll
+      for (int o = 0; o < NS; ++o) {
+        double arg = log_s[o];
+#pragma unroll
+        for (int dd = 0; dd < D; ++dd) arg = fma(sq[dd], nh_inv_l2[o][dd], arg);
+        const double k = exp_nb(arg);
+        q[o][e] = __double2ll_rn(k * qscale[o]);
+        const double wk = al[o][e] * k;
+        m_acc[o] += wk;
+        if (JAC) {
+#pragma unroll
+          for (int dd = 0; dd < D; ++dd) j_acc[o][dd] = fma(wk, diff[dd], j_acc[o][dd]);
+        }
+      }
+    }
+    int8_t* const dst0 = img_row + (int64_t)(j16 >> 5) * (S * A_BLK) + ((j16 & 16) ? 128 : 0);
+#pragma unroll
+    for (int o = 0; o < NS; ++o) {
+      uint32_t word[MAX_S];
+      digits4(q[o], word);
+      int8_t* dst = dst0 + o * img_o;
+#pragma unroll
+      for (int t = 0; t < MAX_S; ++t)
+        if (t < S) *reinterpret_cast<uint32_t*>(dst + t * A_BLK) = word[t];
+    }
+  }
+    __syncthreads();  // everyone is done with this buffer before the chunk after next lands in it
+  }
+
+  // the four quads of a row hold disjoint training points: fold them (lanes r8, r8 + 8, r8 + 16, r8 + 24)
+#pragma unroll
+  for (int o = 0; o < NS; ++o) {
+    double v = m_acc[o];
+    v += __shfl_xor_sync(0xffffffffu, v, 8);
+    v += __shfl_xor_sync(0xffffffffu, v, 16);
+    if (poison) v = __longlong_as_double(0x7ff8000000000000ll);
+    if (quad == 0 && valid) mean[(row0 + row) * NS + o] = v;
+    if (JAC) {
+#pragma unroll
+      for (int dd = 0; dd < D; ++dd) {
+        double g = j_acc[o][dd];  // sum_i alpha_i k_i (z_d - x_id); d mean / d z_d = -that / l_d^2
+        g += __shfl_xor_sync(0xffffffffu, g, 8);
+        g += __shfl_xor_sync(0xffffffffu, g, 16);
+        if (poison) g = __longlong_as_double(0x7ff8000000000000ll);
+        if (quad == 0 && valid) jac[((row0 + row) * NS + o) * D + dd] = -g * gp.inv_l2[o][dd];
+      }
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------------------------------------------------
 // K2 (Ozaki flavour): partial[o][ib][c] = sum_{i in 64-row block ib} ( sum_{j <= i} W_o[i][j] K*_o[c][j] )^2
 // Persistent, warp-specialised: bulk-copy producer / single-thread tcgen05.mma issuer / 4 epilogue warps.
 // ---------------------------------------------------------------------------------------------------------------------
@@ -398,7 +587,7 @@ __device__ __forceinline__ bool next_item(int round, const TriOrder& od, int tot
   return true;
 }
 
-template <int S, bool REUSE>
+template <int S, int MODE>
 __global__ void __launch_bounds__(THREADS, 1)
 gp_trisumsq_ozaki_kernel(const int8_t* __restrict__ a_img, const int8_t* __restrict__ b_img,
                          const double* __restrict__ scale_b, int n, int n_pad, int rows_pad, TriOrder od,
@@ -474,6 +663,7 @@ gp_trisumsq_ozaki_kernel(const int8_t* __restrict__ a_img, const int8_t* __restr
       const int nk = item_ksteps(it.ib, n);
       // the last row tile may hold fewer than 64 training points: a narrower MMA (N is a multiple of 16) skips the padding
       const uint32_t idesc = make_idesc(TM, item_cols(it.ib, n));
+      const bool full_width = item_cols(it.ib, n) == TN;
       mbar_wait(tmem_empty, tphase ^ 1u);  // the epilogue has drained the previous item's accumulators
       tc_fence_after();
       for (int kb = 0; kb < nk; kb += C::KS) {
@@ -483,11 +673,19 @@ gp_trisumsq_ozaki_kernel(const int8_t* __restrict__ a_img, const int8_t* __restr
         const uint32_t a_lo = a_lo0 + stage * (C::STAGE_BYTES >> 4);
         const uint32_t b_lo = a_lo + (C::KS * S * A_BLK >> 4);
         if (elect_one()) {
+          if (MODE == 2 && !full_width) {  // ragged last row tile: per-pair MMAs of the narrower width
 #pragma unroll
-          for (int k = 0; k < C::KS; ++k)
-            if (k < ks)
-              issue_kstep<S, REUSE>(tb, a_lo + k * (S * A_BLK >> 4), b_lo + k * (S * B_BLK >> 4), dhi, idesc,
-                                    kb + k > 0 ? 1u : 0u);
+            for (int k = 0; k < C::KS; ++k)
+              if (k < ks)
+                issue_kstep<S, 1>(tb, a_lo + k * (S * A_BLK >> 4), b_lo + k * (S * B_BLK >> 4), dhi, idesc,
+                                  kb + k > 0 ? 1u : 0u);
+          } else {
+#pragma unroll
+            for (int k = 0; k < C::KS; ++k)
+              if (k < ks)
+                issue_kstep<S, MODE>(tb, a_lo + k * (S * A_BLK >> 4), b_lo + k * (S * B_BLK >> 4), dhi, idesc,
+                                     kb + k > 0 ? 1u : 0u);
+          }
           tc_commit(empty_bar(stage));  // frees the stage once these MMAs have read it
           if (kb + ks == nk) tc_commit(tmem_full);
         }
@@ -510,27 +708,41 @@ gp_trisumsq_ozaki_kernel(const int8_t* __restrict__ a_img, const int8_t* __restr
       tc_fence_after();
       const double* sbp = scale_b + (int64_t)it.o * n_pad + (int64_t)it.ib * TN;
       const uint32_t tlane = tmem_base + ((uint32_t)(quad * 32) << 16);
-      double sum = 0.0;
       const int c_end = (dbg & 2) ? 0 : min((half + 1) * (TN / 2), item_cols(it.ib, n));
-#pragma unroll 1
-      for (int c8 = half * (TN / 2); c8 < c_end; c8 += 8) {
-        int32_t d[S][8];
+      // Phase 1 (the tensor core waits for it): drain this warp's 32 columns of every level and fold the levels into
+      // two exact 64-bit integers per element (integer pipe only), then hand the accumulators back to the MMA warp.
+      long long hi[TN / 2], lo[TN / 2];
 #pragma unroll
-        for (int l = 0; l < S; ++l) tmem_ld8(tlane + (uint32_t)(l * TN + c8), d[l]);
-        tmem_ld_wait();
+      for (int b = 0; b < TN / 16; ++b) {
+        const int c8 = half * (TN / 2) + b * 8;
+        if (c8 < c_end) {  // warp-uniform: c_end is a multiple of 16
+          int32_t d[S][8];
 #pragma unroll
-        for (int j = 0; j < 8; ++j) {
-          long long hi = 0, lo = 0;
+          for (int l = 0; l < S; ++l) tmem_ld8(tlane + (uint32_t)(l * TN + c8), d[l]);
+          tmem_ld_wait();
 #pragma unroll
-          for (int l = 0; l < S && l < 4; ++l) hi += (long long)d[l][j] << (RB * (3 - l));
+          for (int j = 0; j < 8; ++j) {
+            long long h = 0, w = 0;
 #pragma unroll
-          for (int l = 4; l < S; ++l) lo += (long long)d[l][j] << (RB * (S - 1 - l));
-          const double v = ((double)hi + (double)lo * lo_scale) * __ldg(sbp + c8 + j);
-          sum += v * v;
+            for (int l = 0; l < S && l < 4; ++l) h += (long long)d[l][j] << (RB * (3 - l));
+#pragma unroll
+            for (int l = 4; l < S; ++l) w += (long long)d[l][j] << (RB * (S - 1 - l));
+            hi[b * 8 + j] = h, lo[b * 8 + j] = w;
+          }
+        } else {
+#pragma unroll
+          for (int j = 0; j < 8; ++j) hi[b * 8 + j] = 0, lo[b * 8 + j] = 0;
         }
       }
       tc_fence_before();
       mbar_arrive(tmem_empty);
+      // Phase 2 (overlaps the next item's MMAs): one conversion to double per half, row scale, square, row sum.
+      double sum = 0.0;
+#pragma unroll
+      for (int e = 0; e < TN / 2; ++e) {
+        const double v = ((double)hi[e] + (double)lo[e] * lo_scale) * __ldg(sbp + half * (TN / 2) + e);
+        sum += v * v;
+      }
       // the two column halves are separate partial blocks (gp_var_kernel sums 2 nb of them in a fixed order)
       partial[((int64_t)it.o * (2 * od.nb) + 2 * it.ib + half) * rows_pad + (int64_t)it.rt * TM + row] = sum;
       tphase ^= 1u;
@@ -545,7 +757,7 @@ gp_trisumsq_ozaki_kernel(const int8_t* __restrict__ a_img, const int8_t* __restr
 // Probe (tests): one CTA, nk K steps of a single 128 x 64 tile; dumps every level accumulator.  out[S][128][64] int32.
 // lbo / sbo are parameters so the descriptor convention is pinned by a test and not by a comment.
 // ---------------------------------------------------------------------------------------------------------------------
-template <int S, bool REUSE>
+template <int S, int MODE>
 __global__ void __launch_bounds__(128, 1)
 oz_probe_kernel(const int8_t* __restrict__ a_img, const int8_t* __restrict__ b_img, int nk, uint32_t lbo, uint32_t sbo,
                 int32_t* __restrict__ out) {
@@ -574,7 +786,7 @@ oz_probe_kernel(const int8_t* __restrict__ a_img, const int8_t* __restrict__ b_i
       bulk_g2s(base + S * A_BLK, b_img + (int64_t)kb * S * B_BLK, S * B_BLK, full);
       mbar_wait(full, kb & 1);
       tc_fence_after();
-      issue_kstep<S, REUSE>(tmem_base, desc_lo(base, lbo), desc_lo(base + S * A_BLK, lbo), desc_hi(sbo), idesc, kb > 0 ? 1u : 0u);
+      issue_kstep<S, MODE>(tmem_base, desc_lo(base, lbo), desc_lo(base + S * A_BLK, lbo), desc_hi(sbo), idesc, kb > 0 ? 1u : 0u);
       tc_commit(done);
       mbar_wait(done, kb & 1);  // single stage: the next K step overwrites the operands
     }

@@ -245,6 +245,11 @@ extern "C" int se_debug_tc_probe(const int8_t* dev_a_img, const int8_t* dev_b_im
   return launch_oz_probe(dev_a_img, dev_b_img, nk, digits, lbo, sbo, dev_out, static_cast<cudaStream_t>(stream));
 }
 
+extern "C" int se_debug_exp(const double* dev_x, int64_t n, double* dev_out, void* stream) {
+  SE_REQUIRE(n >= 0 && (n == 0 || (dev_x && dev_out)), "se_debug_exp: bad arguments");
+  return launch_debug_exp(dev_x, n, dev_out, static_cast<cudaStream_t>(stream));
+}
+
 extern "C" int se_gp_timing_enable(se_gp_t g, int enable) {
   SE_REQUIRE(g, "NULL handle");
   g->timing = enable != 0;

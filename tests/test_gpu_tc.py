@@ -204,3 +204,43 @@ def test_tc_cem_solve_matches_oracle(pipeline, monkeypatch):
         assert rel_err(res['objective'][i, 0].cpu().numpy(), r.objective_costs.numpy()) < 1e-8
         assert rel_err(res['trajectories'][i, 0].cpu().numpy(), r.trajectories.numpy(), 1e-6) < 1e-7
     assert int(res['best_id'][0]) == ref['best_id']
+
+
+def test_branch_free_exp_is_within_two_ulp_of_libm():
+    """csrc/common.cuh exp_nb (the exp of the kernel-row kernels): <= 2 ulp against numpy's exp over the range the
+    kernel rows use, exact powers at the reduction boundaries, and the clamp below -700 stays tiny and positive."""
+    lib = _lib.load()
+    rng = np.random.default_rng(7)
+    x = np.concatenate([rng.uniform(-60.0, 2.0, 400000), rng.uniform(-700.0, 700.0, 100000),
+                        np.array([0.0, -0.0, 1e-300, -1e-300, np.log(2.0) / 2, -np.log(2.0) / 2, -699.999, 699.999]),
+                        np.arange(-1000, 1001) * np.log(2.0) / 2])
+    x = x[(x > -700.0) & (x < 700.0)]
+    dx = torch.from_numpy(x).to(DEV)
+    out = torch.empty_like(dx)
+    _lib.check(lib.se_debug_exp(_lib.ptr(dx), x.size, _lib.ptr(out), _lib.stream_ptr(DEV)))
+    got, want = out.cpu().numpy(), np.exp(x)
+    ulp = np.abs(got - want) / np.spacing(want)
+    assert ulp.max() <= 2.0, (ulp.max(), x[ulp.argmax()])
+    tiny = torch.tensor([-700.0, -750.0, -1e5, -1e300, -np.inf], dtype=torch.float64, device=DEV)
+    out = torch.empty_like(tiny)
+    _lib.check(lib.se_debug_exp(_lib.ptr(tiny), tiny.numel(), _lib.ptr(out), _lib.stream_ptr(DEV)))
+    o = out.cpu().numpy()
+    assert np.all(o > 0) and np.all(o < 1e-300)
+
+
+def test_non_finite_inputs_poison_the_mean():
+    """A NaN / Inf state must surface as NaN in the posterior mean (the ellipsoid step's NaN check looks there,
+    gp_reachability_pytorch.py:234-243); the other rows of the batch are unaffected."""
+    x, y, ls, os_, nz = _random_model(2, 1, 300, 21)
+    gp = se.B200GpCemSSM(None, 2, 1, ls, os_, nz, device=DEV, gemm_impl=_lib.SE_GEMM_TC)
+    gp.update_model(G(x), G(y), replace_old=True)
+    z = np.random.default_rng(5).uniform(-1, 1, (64, 3))
+    clean = gp.predict_with_jacobians(G(z[:, :2]), G(z[:, 2:]))
+    z2 = z.copy()
+    z2[3, 0], z2[17, 2], z2[40, 1] = np.nan, np.inf, -np.inf
+    mean, var, jac = gp.predict_with_jacobians(G(z2[:, :2]), G(z2[:, 2:]))
+    bad = np.zeros(64, dtype=bool)
+    bad[[3, 17, 40]] = True
+    assert torch.isnan(mean[bad]).all() and torch.isnan(jac[bad]).all()
+    assert torch.equal(mean[~bad], clean[0][~bad]) and torch.equal(var[~bad], clean[1][~bad])
+    assert torch.equal(jac[~bad], clean[2][~bad])

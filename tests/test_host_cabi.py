@@ -155,3 +155,19 @@ def test_update_model_shape_errors():
         ssm.update_model(torch.zeros(5, 4), torch.zeros(5, 2))
     with pytest.raises(ValueError):
         ssm.update_model(torch.zeros(5, 3), torch.zeros(5, 3))
+
+
+def test_exp_polynomial_in_the_kernel_source_is_the_derived_one():
+    """csrc/common.cuh exp_nb: its Horner constants are exactly what tools/exp_poly.py derives (no hand-edited digits)."""
+    import importlib.util
+    import re
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    spec = importlib.util.spec_from_file_location('exp_poly', os.path.join(root, 'tools', 'exp_poly.py'))
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+    coef = mod.coefficients()
+    src = open(os.path.join(root, 'safe_exploration_b200', 'csrc', 'common.cuh')).read()
+    body = src[src.index('double exp_nb(double x)'):src.index('finite_f64')]
+    got = [float(body[body.index('double p = ') + 11:].split(';')[0])]
+    got += [float(v) for v in re.findall(r'p = fma\(p, r, ([0-9.e+-]+)\);', body)]
+    assert got == coef[::-1]
