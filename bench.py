@@ -68,10 +68,11 @@ def workload_desc(w, world, dtype):
 
 
 # ---- CPU baseline: the reference's path, float64, eager torch, all host threads ------------------------------------------
-def cpu_reference_run(w, sample: int, repeats: int, warmup: int):
+def cpu_reference_run(w, sample: int, repeats: int, warmup: int, loops: bool = True):
     """One CEM iteration (sample -> T reachability steps -> constraint loop -> elite selection -> refit) of the oracle
     port with the reference's per-item Python loops, on `sample` candidates of the same workload (full n_train, full
-    horizon).  Returns (candidate-steps/s, seconds per iteration, threads)."""
+    horizon).  loops=False runs the same math with the three per-item loops (eig, trace, constraints) batched: the
+    "reference math, de-looped" line of SURVEY 8(d).  Returns (candidate-steps/s, seconds per iteration, threads)."""
     from oracle import oracle
     threads = os.cpu_count() or 1
     torch.set_num_threads(threads)
@@ -85,7 +86,7 @@ def cpu_reference_run(w, sample: int, repeats: int, warmup: int):
     for rep in range(warmup + repeats):
         noise = T(oracle.philox_normal_noise(rep, 0, 0, sample, w.time_horizon, w.n_u)).unsqueeze(0)
         t0 = time.perf_counter()
-        oracle.cem_solve(prob, T(w.p0), noise, elites, loops=True)
+        oracle.cem_solve(prob, T(w.p0), noise, elites, loops=loops)
         dt = time.perf_counter() - t0
         if rep >= warmup:
             times.append(dt)
@@ -347,6 +348,10 @@ def run_b200(args):
                         'sample': f'{args.cpu_sample} candidates x horizon {w1.time_horizon} x 1 CEM iteration at full '
                                   f'n_train={w1.n_train}, float64 eager torch, reference per-item loops kept '
                                   f'({sec:.2f} s per sample)'}
+        # the same math with the reference's per-item Python loops batched, so the ratio is not credited to loop removal
+        v2, sec2, _ = cpu_reference_run(w1, args.cpu_sample, 2, 1, loops=False)
+        cpu_baseline['delooped'] = {'value': v2, 'unit': UNIT, 'cores': threads, 'kind': 'port',
+                                    'sample': f'same sample, eig / trace / constraint loops batched ({sec2:.2f} s)'}
     if rank == 0:
         line = {
             'metric': METRIC, 'value': value, 'unit': UNIT, 'n_gpus': world, 'steps': args.steps,
