@@ -29,6 +29,7 @@ extern "C" {
 #define SE_MAX_NU 3   /* action dimension */
 #define SE_MAX_FACES 16 /* faces of the safety polytope (pendulum 4, cart-pole 9) */
 #define SE_MAX_ACT_FACES 8
+#define SE_MAX_OBS_FACES 8
 #define SE_MAX_T 64   /* horizon */
 
 typedef enum { SE_F32 = 0, SE_F64 = 1 } se_dtype;
@@ -114,6 +115,13 @@ typedef struct {
   double objective_theta;
   int all_states_constraint; /* 0 = reference behaviour (terminal ellipsoid only, quirk Q1); 1 = check every
                                 ellipsoid of the trajectory (intended semantics)                           */
+  /* Obstacle polytope for the INTERMEDIATE ellipsoids (steps 1 .. T-1), the constraint the reference's CasADi solver
+   * poses (safempc_simple.py:373-383: lin_ellipsoid_safety_distance(p_i, q_i, h_mat_obs, h_obs) <= 0 for i < H-1) and
+   * that construct_constraints drops on the CEM path (safempc_cem.py:137 reads h_mat_obs, h_obs and never uses them).
+   * Every intermediate ellipsoid that is not strictly inside costs state_penalty.  m_obs = 0: reference behaviour. */
+  int m_obs;               /* faces of h_mat_obs x <= h_vec_obs, at most SE_MAX_OBS_FACES                  */
+  const double* h_mat_obs; /* [m_obs, n_s]                                                                 */
+  const double* h_vec_obs; /* [m_obs]                                                                      */
 } se_problem;
 
 /* ---------------------------------------------------------------------------------------------------------------

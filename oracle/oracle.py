@@ -332,7 +332,8 @@ class SafeCemProblem:
     (safempc_cem.py:135-146, 162-200, 288-312), as plain tensors."""
 
     def __init__(self, ssm, l_mu, l_sigma, k_fb, a, b, beta_safety, h_mat, h_vec, act_a, act_b,
-                 objective: str = "neg_variance", objective_theta: float = 0.0, use_prior_model: bool = True):
+                 objective: str = "neg_variance", objective_theta: float = 0.0, use_prior_model: bool = True,
+                 h_mat_obs=None, h_vec_obs=None):
         t = lambda x: torch.as_tensor(x, dtype=F64)
         self.ssm = ssm
         self.n_s, self.n_u = ssm.num_states, ssm.num_actions
@@ -348,6 +349,11 @@ class SafeCemProblem:
         self.act_a, self.act_b = t(act_a), t(act_b).reshape(-1)
         self.objective = objective
         self.objective_theta = float(objective_theta)
+        # Opt-in obstacle polytope for the intermediate ellipsoids.  The reference's CEM path never applies it
+        # (safempc_cem.py:137 reads h_mat_obs, h_obs and drops them); the constraint itself is the one its CasADi
+        # solver poses (safempc_simple.py:373-383), charged 10 per violating state like safempc_cem.py:132.
+        self.h_mat_obs = None if h_mat_obs is None else t(h_mat_obs)
+        self.h_vec_obs = None if h_vec_obs is None else t(h_vec_obs).reshape(-1)
 
     def objective_cost(self, p_next: Tensor, sigma: Tensor) -> Tensor:
         """safempc_cem.py:304-312; environments.py:505-510 (pendulum objective |theta* - p[:,1]|);
@@ -373,11 +379,14 @@ def perform_rollouts(prob: SafeCemProblem, p0: Tensor, actions: Tensor, loops: b
     traj = torch.empty((n, t_len + 1, n_s + n_s * n_s), dtype=F64)
     traj[:, 0] = flatten_pq(p, None)
     objective = torch.zeros((n,), dtype=F64)
+    obstacle = torch.zeros((n,), dtype=F64)
     for t in range(t_len):
         p, q, sigma = onestep_reachability(p, prob.ssm, actions[:, t], prob.l_mu, prob.l_sigma, q, prob.k_fb,
                                            prob.beta, prob.a, prob.b, loops)
         traj[:, t + 1] = flatten_pq(p, q)
         objective = objective + prob.objective_cost(p, sigma)
+        if prob.h_mat_obs is not None and t < t_len - 1:
+            obstacle = obstacle + terminal_constraint_costs(p, q, prob.h_mat_obs, prob.h_vec_obs)
         # unflatten's "all-zero q => None" rule (safempc_cem.py:70-71) cannot trigger here: q_1 > 0 on its diagonal.
     if loops:
         # constrained_cem_mpc.py:187-192: per-rollout Python loop over the constraint objects
@@ -388,7 +397,7 @@ def perform_rollouts(prob: SafeCemProblem, p0: Tensor, actions: Tensor, loops: b
     else:
         cc = (action_constraint_costs(actions, prob.act_a, prob.act_b)
               + terminal_constraint_costs(p, q, prob.h_mat, prob.h_vec))
-    return Rollouts(traj, actions, objective, cc)
+    return Rollouts(traj, actions, objective, cc + obstacle)
 
 
 def select_elites(objective_costs: Tensor, constraint_costs: Tensor, num_elites: int) -> Tensor:

@@ -16,7 +16,8 @@ from .cem import (ActionConstraint, B200ConstrainedCemMpc, Constraint, DynamicsF
                   box2torchpoly, sample_noise, select_elites_refit)
 from .reachability import (SafeProblem, is_ellipsoid_inside_polytope, lin_ellipsoid_safety_distance,
                            multistep_reachability, onestep_reachability)
-from .safempc import (B200CemSafeMPC, B200SafeDynamics, EllipsoidStateConstraint, EllipsoidTerminalConstraint,
+from .safempc import (B200CemSafeMPC, B200SafeDynamics, EllipsoidObstacleConstraint, EllipsoidStateConstraint,
+                      EllipsoidTerminalConstraint,
                       LqrFeedbackController, MpcResult, PQFlattener, SafeMPC, construct_constraints, dlqr)
 from .ssm import B200GpCemSSM, CemSSM, assert_shape
 

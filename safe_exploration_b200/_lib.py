@@ -15,6 +15,7 @@ SE_F32, SE_F64 = 0, 1
 SE_GEMM_AUTO, SE_GEMM_SIMT, SE_GEMM_MMA, SE_GEMM_TC = 0, 1, 2, 3
 SE_OBJ_NEG_VARIANCE, SE_OBJ_ABS_STATE1, SE_OBJ_NEG_LAST_STATE = 0, 1, 2
 SE_MAX_NS, SE_MAX_NU, SE_MAX_FACES, SE_MAX_ACT_FACES, SE_MAX_T = 6, 3, 16, 8, 64
+SE_MAX_OBS_FACES = 8
 MAX_ELITES = 4096
 
 _dbl_p = C.POINTER(C.c_double)
@@ -27,7 +28,8 @@ class SeProblem(C.Structure):
                 ("l_sigma", _dbl_p), ("c_safety", C.c_double), ("m_safe", C.c_int), ("h_mat", _dbl_p),
                 ("h_vec", _dbl_p), ("m_act", C.c_int), ("act_a", _dbl_p), ("act_b", _dbl_p),
                 ("act_penalty", C.c_double), ("state_penalty", C.c_double), ("objective", C.c_int),
-                ("objective_theta", C.c_double), ("all_states_constraint", C.c_int)]
+                ("objective_theta", C.c_double), ("all_states_constraint", C.c_int), ("m_obs", C.c_int),
+                ("h_mat_obs", _dbl_p), ("h_vec_obs", _dbl_p)]
 
 
 class SeCemConfig(C.Structure):

@@ -77,7 +77,7 @@ struct GpDev {
 // problem constants in kernel-parameter form (converted from se_problem on the host)
 template <typename T>
 struct ProbDev {
-  int ns, nu, m_safe, m_act, objective, all_states;
+  int ns, nu, m_safe, m_act, objective, all_states, m_obs;
   T k_fb[SE_MAX_NU][SE_MAX_NS];
   T a[SE_MAX_NS][SE_MAX_NS];
   T b[SE_MAX_NS][SE_MAX_NU];
@@ -90,6 +90,8 @@ struct ProbDev {
   T act_a[SE_MAX_ACT_FACES][SE_MAX_NU];
   T act_b[SE_MAX_ACT_FACES];
   T act_penalty, state_penalty, objective_theta;
+  T hobs_mat[SE_MAX_OBS_FACES][SE_MAX_NS];  // obstacle polytope of the intermediate ellipsoids (m_obs faces)
+  T hobs_vec[SE_MAX_OBS_FACES];
 };
 
 // exp(x) in double for finite x <= 700, without the special-case branch of the library routine (which keeps every exp()

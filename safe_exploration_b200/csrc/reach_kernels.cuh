@@ -111,25 +111,30 @@ __device__ __forceinline__ T fix_zero_nan(T x, int32_t* flags) {
 
 // support-function distance of the ellipsoid (p, q) to every face; returns true iff all d < 0
 // (gp_reachability_pytorch.py:184-231; c_safety = 1 on the CEM path, quirk Q2)
-template <typename T, int NS>
-__device__ __forceinline__ bool inside_polytope(const T (&p)[NS], const T (&q)[NS][NS], const ProbDev<T>& pr,
-                                                T c_safety, T* d_out) {
+template <typename T, int NS, int MAXF>
+__device__ __forceinline__ bool inside_faces(const T (&p)[NS], const T (&q)[NS][NS], const T (&h_mat)[MAXF][SE_MAX_NS],
+                                             const T (&h_vec)[MAXF], int m, T c_safety, T* d_out) {
   bool inside = true;
-  for (int f = 0; f < pr.m_safe; ++f) {
+  for (int f = 0; f < m; ++f) {
     T hp = T(0), hqh = T(0);
 #pragma unroll
     for (int i = 0; i < NS; ++i) {
-      hp += pr.h_mat[f][i] * p[i];
+      hp += h_mat[f][i] * p[i];
       T qh = T(0);
 #pragma unroll
-      for (int j = 0; j < NS; ++j) qh += q[i][j] * pr.h_mat[f][j];
-      hqh += pr.h_mat[f][i] * qh;
+      for (int j = 0; j < NS; ++j) qh += q[i][j] * h_mat[f][j];
+      hqh += h_mat[f][i] * qh;
     }
-    const T d = hp + c_safety * Num<T>::sqrt_(hqh) - pr.h_vec[f];
+    const T d = hp + c_safety * Num<T>::sqrt_(hqh) - h_vec[f];
     if (d_out) d_out[f] = d;
     if (d >= T(0)) inside = false;  // (d_safety >= 0).sum() == 0, gp_reachability_pytorch.py:230-231
   }
   return inside;
+}
+template <typename T, int NS>
+__device__ __forceinline__ bool inside_polytope(const T (&p)[NS], const T (&q)[NS][NS], const ProbDev<T>& pr,
+                                                T c_safety, T* d_out) {
+  return inside_faces<T, NS, SE_MAX_FACES>(p, q, pr.h_mat, pr.h_vec, pr.m_safe, c_safety, d_out);
 }
 
 template <typename T>
@@ -338,6 +343,11 @@ reach_step_kernel(ProbDev<T> pr, StepIO<T> io, int64_t N) {
     if (pr.m_safe > 0 && (io.last_step || pr.all_states)) {
       const bool inside = inside_polytope<T, NS>(p1, q1, pr, T(1), nullptr);
       if (!inside) cc += pr.state_penalty;  // 10 * (1 - inside), safempc_cem.py:132
+    }
+    if (pr.m_obs > 0 && !io.last_step) {
+      // intermediate ellipsoids against the obstacle polytope (safempc_simple.py:373-383, as a penalty)
+      if (!inside_faces<T, NS, SE_MAX_OBS_FACES>(p1, q1, pr.hobs_mat, pr.hobs_vec, pr.m_obs, T(1), nullptr))
+        cc += pr.state_penalty;
     }
     if (io.last_step && pr.m_act > 0) {
       // ActionConstraint: penalty * #{t : some face has A u_t - b > 0}  (constrained_cem_mpc.py:29-41, 100-110)

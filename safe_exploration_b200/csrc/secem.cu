@@ -425,6 +425,9 @@ static int make_prob(const se_problem* pr, const double* k_fb_override, ProbDev<
   SE_REQUIRE(pr->l_mu && pr->l_sigma, "se_problem: l_mu / l_sigma is NULL");
   SE_REQUIRE(pr->m_safe == 0 || (pr->h_mat && pr->h_vec), "se_problem: h_mat / h_vec is NULL");
   SE_REQUIRE(pr->m_act == 0 || (pr->act_a && pr->act_b), "se_problem: act_a / act_b is NULL");
+  SE_REQUIRE(pr->m_obs >= 0 && pr->m_obs <= SE_MAX_OBS_FACES, "se_problem: m_obs = %d outside [0, %d]", pr->m_obs,
+             SE_MAX_OBS_FACES);
+  SE_REQUIRE(pr->m_obs == 0 || (pr->h_mat_obs && pr->h_vec_obs), "se_problem: h_mat_obs / h_vec_obs is NULL");
   ProbDev<T>& o = *out;
   memset(&o, 0, sizeof(o));
   o.ns = ns, o.nu = nu, o.m_safe = pr->m_safe, o.m_act = pr->m_act;
@@ -469,6 +472,11 @@ static int make_prob(const se_problem* pr, const double* k_fb_override, ProbDev<
   for (int f = 0; f < pr->m_safe; ++f) {
     for (int j = 0; j < ns; ++j) o.h_mat[f][j] = (T)pr->h_mat[f * ns + j];
     o.h_vec[f] = (T)pr->h_vec[f];
+  }
+  o.m_obs = pr->m_obs;
+  for (int f = 0; f < pr->m_obs; ++f) {
+    for (int j = 0; j < ns; ++j) o.hobs_mat[f][j] = (T)pr->h_mat_obs[f * ns + j];
+    o.hobs_vec[f] = (T)pr->h_vec_obs[f];
   }
   for (int f = 0; f < pr->m_act; ++f) {
     for (int k = 0; k < nu; ++k) o.act_a[f][k] = (T)pr->act_a[f * nu + k];

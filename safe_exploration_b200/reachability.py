@@ -21,7 +21,8 @@ class SafeProblem:
     def __init__(self, n_s: int, n_u: int, l_mu, l_sigma, k_fb=None, a=None, b=None, c_safety: float = 1.0,
                  h_mat=None, h_vec=None, act_a=None, act_b=None, act_penalty: float = 3.0,
                  state_penalty: float = 10.0, objective: int = _lib.SE_OBJ_NEG_VARIANCE,
-                 objective_theta: float = 0.0, all_states_constraint: bool = False):
+                 objective_theta: float = 0.0, all_states_constraint: bool = False, h_mat_obs=None,
+                 h_vec_obs=None):
         def arr(x, shape):
             if x is None:
                 return None
@@ -49,13 +50,17 @@ class SafeProblem:
         self.act_penalty, self.state_penalty = float(act_penalty), float(state_penalty)
         self.objective, self.objective_theta = int(objective), float(objective_theta)
         self.all_states_constraint = bool(all_states_constraint)
+        # obstacle polytope of the intermediate ellipsoids (safempc_simple.py:373-383); None = reference CEM behaviour
+        self.h_mat_obs = arr(h_mat_obs, (-1, n_s))
+        self.h_vec_obs = None if h_vec_obs is None else arr(h_vec_obs, (self.h_mat_obs.shape[0],))
 
     def with_(self, **kw) -> 'SafeProblem':
         cur = dict(n_s=self.n_s, n_u=self.n_u, l_mu=self.l_mu, l_sigma=self.l_sigma, k_fb=self.k_fb, a=self.a,
                    b=self.b, c_safety=self.c_safety, h_mat=self.h_mat, h_vec=self.h_vec, act_a=self.act_a,
                    act_b=self.act_b, act_penalty=self.act_penalty, state_penalty=self.state_penalty,
                    objective=self.objective, objective_theta=self.objective_theta,
-                   all_states_constraint=self.all_states_constraint)
+                   all_states_constraint=self.all_states_constraint, h_mat_obs=self.h_mat_obs,
+                   h_vec_obs=self.h_vec_obs)
         cur.update(kw)
         return SafeProblem(**cur)
 
@@ -73,6 +78,8 @@ class SafeProblem:
         s.act_penalty, s.state_penalty = self.act_penalty, self.state_penalty
         s.objective, s.objective_theta = self.objective, self.objective_theta
         s.all_states_constraint = 1 if self.all_states_constraint else 0
+        s.m_obs = 0 if self.h_mat_obs is None else self.h_mat_obs.shape[0]
+        s.h_mat_obs, s.h_vec_obs = dp(self.h_mat_obs), dp(self.h_vec_obs)
         return s  # the numpy arrays it points into are owned by `self`
 
 

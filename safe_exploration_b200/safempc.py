@@ -109,16 +109,42 @@ class EllipsoidTerminalConstraint(Constraint):
         return self._constraint(trajectory[-1:, :], actions[-1:, :])
 
 
+class EllipsoidObstacleConstraint(Constraint):
+    """The intermediate-state constraint of the reference's CasADi solver (safempc_simple.py:373-383): every ellipsoid
+    BEFORE the terminal one must lie inside the obstacle polytope h_mat_obs x <= h_obs.  The reference's CEM path
+    reads that polytope and drops it (safempc_cem.py:137); here it is an opt-in constraint, 10 per violating state
+    like the other state constraints."""
+
+    def __init__(self, state_dimen: int, obstacle_polytope_a: np.ndarray, obstacle_polytope_b: np.ndarray,
+                 device: str = None):
+        self._pq_flattener = PQFlattener(state_dimen)
+        self._polytope_a = torch.as_tensor(np.asarray(obstacle_polytope_a, dtype=np.float64), device=device)
+        self._polytope_b = torch.as_tensor(np.asarray(obstacle_polytope_b, dtype=np.float64),
+                                           device=device).reshape(-1, 1)
+
+    def __call__(self, trajectory, actions) -> float:
+        states = trajectory[1:-1]  # slot 0 is the (point) initial state, the last slot the terminal ellipsoid
+        if states.shape[0] == 0:
+            return 0
+        p, q = self._pq_flattener.unflatten(states)
+        inside = is_ellipsoid_inside_polytope(p, q, self._polytope_a.to(p), self._polytope_b.to(p))
+        return (inside.size(0) - inside.sum()) * 10
+
+
 def construct_constraints(conf, env) -> List[Constraint]:
     """safempc_cem.py:135-146: [ActionConstraint(normalised action box), Ellipsoid{State|Terminal}Constraint]."""
-    h_mat_safe, h_safe, _, _ = env.get_safety_constraints(normalize=True)
+    h_mat_safe, h_safe, h_mat_obs, h_obs = env.get_safety_constraints(normalize=True)
     boxes = np.array([np.array(xs) for xs in zip(env.u_min_norm, env.u_max_norm)])
     action_constraint = ActionConstraint(box2torchpoly(boxes))
     if conf.use_state_constraint:
         constraint = EllipsoidStateConstraint(env.n_s, h_mat_safe, h_safe)
     else:
         constraint = EllipsoidTerminalConstraint(env.n_s, h_mat_safe, h_safe)
-    return [action_constraint, constraint]
+    constraints = [action_constraint, constraint]
+    # opt-in (no such key in the reference's configs): pose the obstacle constraint the CasADi solvers pose
+    if getattr(conf, 'use_obstacle_constraint', False) and h_mat_obs is not None:
+        constraints.append(EllipsoidObstacleConstraint(env.n_s, h_mat_obs, h_obs))
+    return constraints
 
 
 class B200SafeDynamics(DynamicsFunc):
@@ -161,9 +187,12 @@ def fold_constraints(problem: SafeProblem, constraints: Sequence[Constraint]) ->
         elif isinstance(c, EllipsoidStateConstraint):
             kw.update(h_mat=c._polytope_a.cpu().numpy(), h_vec=c._polytope_b.cpu().numpy().reshape(-1),
                       all_states_constraint=c.all_states)
+        elif isinstance(c, EllipsoidObstacleConstraint):
+            kw.update(h_mat_obs=c._polytope_a.cpu().numpy(), h_vec_obs=c._polytope_b.cpu().numpy().reshape(-1))
         else:
             raise TypeError(f'{type(c).__name__} cannot be evaluated inside the fused CEM kernels; supported: '
-                            f'ActionConstraint, EllipsoidTerminalConstraint, EllipsoidStateConstraint')
+                            f'ActionConstraint, EllipsoidTerminalConstraint, EllipsoidStateConstraint, '
+                            f'EllipsoidObstacleConstraint')
     return problem.with_(**kw)
 
 

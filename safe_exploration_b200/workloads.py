@@ -107,6 +107,16 @@ def cartpole_polytope():
     return np.array(rows) @ np.diag(norm_x), h_vec
 
 
+def cartpole_obstacle_polytope():
+    """The obstacle polytope of _init_safety_constraints (:1118-1139), normalised like the safety polytope: cart
+    position in [-10, 3], pole angle within +-90 degrees -- plus the row the reference stacks in between by accident
+    (`h_1_mat`, `h_1_vec` still hold the SAFETY face -7.25 theta - dtheta <= 1 at that point of the function)."""
+    rows = [[1., 0., 0., 0.], [-1., 0., 0., 0.], [0., 0., -7.25, -1.], [0., 0., 1., 0.], [0., 0., -1., 0.]]
+    h_vec = np.array([3.0, 10.0, 1.0, np.deg2rad(90), np.deg2rad(90)])
+    norm_x, _ = cartpole_norms()
+    return np.array(rows) @ np.diag(norm_x), h_vec
+
+
 # ---- synthetic GP data ------------------------------------------------------------------------------------------------
 def _synthetic_targets(x: np.ndarray, n_s: int, rng: np.random.Generator, scale: float) -> np.ndarray:
     """A fixed smooth residual-dynamics function + observation noise."""

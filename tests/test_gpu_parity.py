@@ -490,3 +490,41 @@ def test_full_size_c2_properties():
     assert np.array_equal(full['constraint'][-1, 0].cpu().numpy()[pick], ref.constraint_costs.numpy())
     assert rel_err(full['objective'][-1, 0].cpu().numpy()[pick], ref.objective_costs) < 1e-7
     assert rel_err(full['trajectories'][-1, 0].cpu().numpy()[pick], ref.trajectories, 1e-4) < 1e-7
+
+
+def test_cem_obstacle_polytope_matches_oracle():
+    """Opt-in intermediate-state constraint (se_problem.m_obs; the reference's CasADi solvers pose it,
+    safempc_simple.py:373-383, its CEM path drops it): whole solve against the oracle with the same polytope, and the
+    host-side EllipsoidObstacleConstraint object evaluates the recorded trajectories to the same costs."""
+    w = workloads.pendulum_workload(n_train=100, num_rollouts=500, time_horizon=5, num_elites=20, num_iterations=4,
+                                    name='C1')
+    h_obs, v_obs = workloads.box_polytope([-1.5, -0.6], [1.5, 0.6])  # cuts ~4 of 5 candidates of the first population
+    ssm = se.B200GpCemSSM(None, w.n_s, w.n_u, w.lengthscale, w.outputscale, w.noise, device=DEV)
+    ssm.update_model(G(w.x_train), G(w.y_train), replace_old=True)
+    prob = se.SafeProblem(w.n_s, w.n_u, w.l_mu, w.l_sigma, k_fb=w.k_fb, a=w.a, b=w.b, c_safety=w.beta_safety)
+    obstacle = se.EllipsoidObstacleConstraint(w.n_s, h_obs, v_obs)
+    cons = [se.ActionConstraint(se.TorchPolytope((w.act_a, w.act_b))),
+            se.EllipsoidTerminalConstraint(w.n_s, w.h_mat, w.h_vec), obstacle]
+    mpc = se.B200ConstrainedCemMpc(se.B200SafeDynamics(ssm, prob), cons, 6, 1, w.time_horizon, w.num_rollouts,
+                                   w.num_elites, w.num_iterations, seed=9, record='full')
+    res = mpc.solve(G(w.p0).unsqueeze(0), seed=9)
+    noise = np.stack([oracle.philox_normal_noise(9, i, 0, w.num_rollouts, w.time_horizon, 1)
+                      for i in range(w.num_iterations)])
+    ref_gp = make_oracle_gp(w.x_train, w.y_train, w.lengthscale, w.outputscale, w.noise)
+    rp = oracle.SafeCemProblem(ref_gp, w.l_mu, w.l_sigma, w.k_fb, w.a, w.b, w.beta_safety, w.h_mat, w.h_vec, w.act_a,
+                               w.act_b, h_mat_obs=h_obs, h_vec_obs=v_obs)
+    ref = oracle.cem_solve(rp, T(w.p0), T(noise), w.num_elites)
+    plain = oracle.SafeCemProblem(ref_gp, w.l_mu, w.l_sigma, w.k_fb, w.a, w.b, w.beta_safety, w.h_mat, w.h_vec,
+                                  w.act_a, w.act_b)
+    base = oracle.perform_rollouts(plain, T(w.p0), ref['rollouts'][0].actions)
+    extra = ref['rollouts'][0].constraint_costs - base.constraint_costs
+    assert (extra > 0).sum() > 10 and (extra == 0).sum() > 10  # the polytope is actually exercised, both ways
+    assert np.array_equal(res['elite_ids'][:, 0].cpu().numpy(), ref['elite_ids'].numpy())
+    for i, r in enumerate(ref['rollouts']):
+        assert np.array_equal(res['constraint'][i, 0].cpu().numpy(), r.constraint_costs.numpy())
+        assert rel_err(res['objective'][i, 0].cpu(), r.objective_costs) < 1e-8
+    assert int(res['best_id'][0]) == ref['best_id']
+    # the Constraint object on the recorded trajectories (what a non-fused ConstrainedCemMpc would call per rollout)
+    traj, act = res['trajectories'][0, 0], res['rollout_actions'][0, 0]
+    for i in (0, 7, 123, 499):
+        assert float(obstacle(traj[i], act[i])) == float(extra[i])

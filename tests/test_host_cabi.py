@@ -31,11 +31,28 @@ def test_library_exports_every_declared_symbol():
     assert lib.se_version() == 100
 
 
-def test_struct_layouts_match_header():
-    # se_problem: 2 ints, 5 pointers, double, int, 2 pointers, int, 2 pointers, 2 doubles, int, double, int
-    assert ctypes.sizeof(_lib.SeProblem) == 144
-    assert ctypes.sizeof(_lib.SeCemConfig) == 32
-    assert ctypes.sizeof(_lib.SeCemOutputs) == 11 * 8
+def test_struct_layouts_match_header(tmp_path):
+    """ctypes mirrors against the C compiler's view of include/secem.h: sizes and the offset of every field."""
+    import subprocess
+    mirrors = {'se_problem': _lib.SeProblem, 'se_cem_config': _lib.SeCemConfig, 'se_cem_outputs': _lib.SeCemOutputs}
+    lines = []
+    for cname, cls in mirrors.items():
+        lines.append(f'printf("{cname} %zu\\n", sizeof({cname}));')
+        for field, _ in cls._fields_:
+            lines.append(f'printf("{cname}.{field} %zu\\n", offsetof({cname}, {field}));')
+    src = tmp_path / 'layout.c'
+    src.write_text('#include <stdio.h>\n#include <stddef.h>\n#include "secem.h"\nint main(void) {\n' +
+                   '\n'.join(lines) + '\nreturn 0; }\n')
+    exe = tmp_path / 'layout'
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    subprocess.run(['gcc', '-I', os.path.join(root, 'include'), str(src), '-o', str(exe)], check=True)
+    got = dict(line.split() for line in subprocess.run([str(exe)], check=True, capture_output=True,
+                                                       text=True).stdout.splitlines())
+    for cname, cls in mirrors.items():
+        assert int(got[cname]) == ctypes.sizeof(cls), cname
+        for field, _ in cls._fields_:
+            assert int(got[f'{cname}.{field}']) == getattr(cls, field).offset, f'{cname}.{field}'
+    assert ctypes.sizeof(_lib.SeProblem) == 160  # 144 before the obstacle polytope (m_obs, h_mat_obs, h_vec_obs)
 
 
 def test_argument_errors_are_reported_without_a_gpu():
