@@ -330,6 +330,40 @@ class B200CemSafeMPC(SafeMPC):
             result = MpcResult.SAFE_CONTROLLER
         return action, result
 
+    def get_action_batch(self, states: ndarray) -> Tuple[ndarray, List[MpcResult]]:
+        """M scenarios side by side: what episode_runner.do_rollout (episode_runner.py:206-231) does when it calls
+        `solver.get_action(state)` once per scenario and step, as ONE device call (BASELINE config C4: independent MPC
+        solves batched).  Every scenario keeps its own stored plan, so the FOUND / PREVIOUS / SAFE_CONTROLLER state
+        machine of safempc_cem.py:231-263 runs per scenario exactly as in get_action.
+
+        :param states: [M, n_s]; call it with the same M every step of a batched rollout
+        :returns: actions [M, n_u], one MpcResult per scenario
+        """
+        states = np.asarray(states, dtype=np.float64)
+        m = states.shape[0]
+        assert_shape(states, (m, self._state_dimen))
+        if getattr(self, '_batch_plans', None) is None or len(self._batch_plans) != m:
+            self._batch_plans = [np.empty((0, self.action_dimen)) for _ in range(m)]
+            self._batch_executed = [0] * m
+        dev_states = torch.as_tensor(states, dtype=self._ssm.dtype, device=self._ssm.device)
+        plans, found = self._mpc.get_actions_batch(dev_states)
+        plans, found = plans.detach().cpu().numpy(), found.cpu().numpy()
+        actions = np.empty((m, self.action_dimen))
+        results = []
+        for i in range(m):
+            if found[i]:
+                actions[i] = plans[i, 0]
+                self._batch_plans[i], self._batch_executed[i] = plans[i].copy(), 1
+                results.append(MpcResult.FOUND_SOLUTION)
+            elif self._batch_executed[i] < self._batch_plans[i].shape[0]:
+                actions[i] = self._batch_plans[i][self._batch_executed[i]]
+                self._batch_executed[i] += 1
+                results.append(MpcResult.PREVIOUS_SOLUTION)
+            else:
+                actions[i] = self._safe_policy(states[i])
+                results.append(MpcResult.SAFE_CONTROLLER)
+        return actions, results
+
     def _say(self, msg: str) -> None:
         if self._verbose:
             print(msg)

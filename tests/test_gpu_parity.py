@@ -449,6 +449,51 @@ def test_safempc_get_action_state_machine(golden_cem):
     assert mean.shape == (2, 3) and var.shape == (2, 3)
 
 
+def test_safempc_batched_scenarios_keep_their_own_plans(golden_cem):
+    """get_action_batch: M scenarios in one device call; each runs the FOUND -> PREVIOUS -> SAFE_CONTROLLER state
+    machine on its own stored plan, and a scenario's first solve equals the single-scenario solve with that seed."""
+    g = golden_cem
+
+    class Env:
+        n_s, n_u = 2, 1
+        l_mu, l_sigm = g['l_mu'], g['l_sigma']
+        objective_spec = None
+
+    class Conf:
+        mpc_time_horizon, cem_num_rollouts, cem_num_elites, cem_num_iterations = 3, 64, 8, 2
+        use_prior_model = True
+
+    gp = make_gp(g['x_train'], g['y_train'], g['lengthscale'], g['outputscale'], g['noise_var'])
+    cons = [se.ActionConstraint(se.TorchPolytope((g['act_a'], g['act_b']))),
+            se.EllipsoidTerminalConstraint(2, g['h_mat'], g['h_vec'])]
+    mk = lambda: se.B200CemSafeMPC(gp, cons, Env, Conf, {'lin_model': (g['a'], g['b'])}, np.diag([1., 2.]),
+                                   25 * np.eye(1), beta_safety=2.0, safe_policy=lambda s: np.array([-7.0 + s[0]]),
+                                   verbose=False)
+    solver = mk()
+    # scenario 1 starts far outside the safe set: nothing feasible there from the very first step
+    states = np.stack([g['p0'], g['p0'] + np.array([50.0, 50.0]), g['p0'] + np.array([0.01, -0.01])])
+    actions, results = solver.get_action_batch(states)
+    assert actions.shape == (3, 1)
+    assert results[0] == results[2] == se.MpcResult.FOUND_SOLUTION and results[1] == se.MpcResult.SAFE_CONTROLLER
+    assert actions[1, 0] == -7.0 + states[1, 0]
+    plans = [p.copy() for p in solver._batch_plans]
+    assert np.array_equal(actions[0], plans[0][0]) and np.array_equal(actions[2], plans[2][0])
+    # later solves infeasible for everybody: stored plans are replayed per scenario, then the safe policy takes over
+    cons_bad = [cons[0], se.EllipsoidTerminalConstraint(2, g['h_mat'], 1e-3 * g['h_vec'])]
+    solver._mpc = se.B200ConstrainedCemMpc(solver._dynamics, cons_bad, 6, 1, 3, 64, 8, 2)
+    for step in (1, 2):
+        actions, results = solver.get_action_batch(states)
+        assert results == [se.MpcResult.PREVIOUS_SOLUTION, se.MpcResult.SAFE_CONTROLLER, se.MpcResult.PREVIOUS_SOLUTION]
+        assert np.array_equal(actions[0], plans[0][step]) and np.array_equal(actions[2], plans[2][step])
+    actions, results = solver.get_action_batch(states)
+    assert results == [se.MpcResult.SAFE_CONTROLLER] * 3
+    # same seed, one scenario at a time -> the same first plan as in the batch (instances draw independent streams
+    # keyed by instance id, so compare scenario 0 only)
+    single = mk()
+    a0, r0 = single.get_action(states[0])
+    assert r0 == se.MpcResult.FOUND_SOLUTION and np.array_equal(single._last_mpc_actions, plans[0])
+
+
 # ---- full-size, size-independent properties -----------------------------------------------------------------------
 def test_full_size_c2_properties():
     """BASELINE config C2 (pendulum, n = 2000, T = 10, N = 16384): properties that need no oracle run."""
