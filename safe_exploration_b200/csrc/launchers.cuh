@@ -30,6 +30,13 @@ int launch_var(const GpDev<T>& gp, const T* partial, int nb, int rows_pad, int64
 
 template <typename T>
 int launch_reach_step(const ProbDev<T>& pr, const StepIO<T>& io, int64_t N, cudaStream_t stream);
+template <typename T>
+struct RolloutIO;
+template <typename T>
+int launch_transpose_w(const T* w, int n_pad, int ns, T* wt, cudaStream_t stream);
+template <typename T>
+int launch_rollout_small(const GpDev<T>& gp, const T* wt, const ProbDev<T>& pr, const RolloutIO<T>& io,
+                         cudaStream_t stream);
 
 template <typename T>
 int launch_safety_distance(const ProbDev<T>& pr, const T* p, const T* q, int64_t N, T* d, uint8_t* inside,

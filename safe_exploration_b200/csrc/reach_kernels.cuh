@@ -167,25 +167,18 @@ struct StepIO {
   int64_t first;   // first candidate of this launch (all arrays are indexed by the absolute candidate id)
 };
 
+// One ellipsoid step on register operands (gp_reachability_pytorch.py:18-181): (p, q | point) + GP posterior at
+// [p, u] -> (p1, q1), sg = the variances after _fix_zeros_nans.  Shared by reach_step_kernel (one thread per candidate)
+// and the fused small-model rollout kernel (rollout_kernels.cuh).
 template <typename T, int NS, int NU>
-__global__ void __launch_bounds__(128)
-reach_step_kernel(ProbDev<T> pr, StepIO<T> io, int64_t N) {
-  constexpr int D = NS + NU;
-  const int64_t c = io.first + blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
-  if (c >= io.first + N) return;
-
-  T p[NS], u[NU], mu[NS], sg[NS];
+__device__ __forceinline__ void ellipsoid_step_core(const ProbDev<T>& pr, const T (&p)[NS], const T (&q)[NS][NS],
+                                                    bool point, const T (&u)[NU], const T (&mu)[NS],
+                                                    const T (&var)[NS], const T (&jac)[NS][NS + NU], int32_t* flags,
+                                                    T (&p1)[NS], T (&q1)[NS][NS], T (&sg)[NS]) {
 #pragma unroll
-  for (int i = 0; i < NS; ++i) {
-    p[i] = io.p_in[c * NS + i];
-    mu[i] = io.mean[c * NS + i];
-    sg[i] = fix_zero_nan<T>(io.var[c * NS + i], io.flags);  // sigm_0 (:76, :117)
-  }
-#pragma unroll
-  for (int j = 0; j < NU; ++j) u[j] = io.u[c * io.u_stride + j];
+  for (int i = 0; i < NS; ++i) sg[i] = fix_zero_nan<T>(var[i], flags);  // sigm_0 (:76, :117)
 
   // p_0 = mu_0 + a p + b u   (:93-94, :132)
-  T p1[NS];
 #pragma unroll
   for (int i = 0; i < NS; ++i) {
     T s = mu[i];
@@ -196,8 +189,7 @@ reach_step_kernel(ProbDev<T> pr, StepIO<T> io, int64_t N) {
     p1[i] = s;
   }
 
-  T q1[NS][NS];
-  if (io.point) {
+  if (point) {
     // q_1 = diag(n_s (c_safety sqrt(sigm_0))^2)   (:82-91, utils_ellipsoid.py:302-309)
 #pragma unroll
     for (int i = 0; i < NS; ++i)
@@ -205,23 +197,19 @@ reach_step_kernel(ProbDev<T> pr, StepIO<T> io, int64_t N) {
       for (int j = 0; j < NS; ++j) q1[i][j] = T(0);
 #pragma unroll
     for (int i = 0; i < NS; ++i) {
-      const T rk = fix_zero_nan<T>(pr.c_safety * Num<T>::sqrt_(sg[i]), io.flags);
+      const T rk = fix_zero_nan<T>(pr.c_safety * Num<T>::sqrt_(sg[i]), flags);
       q1[i][i] = T(NS) * rk * rk;
     }
   } else {
-    T q[NS][NS], h[NS][NS];
-#pragma unroll
-    for (int i = 0; i < NS; ++i)
-#pragma unroll
-      for (int j = 0; j < NS; ++j) q[i][j] = io.q_in[(c * NS + i) * NS + j];
+    T h[NS][NS];
     // H = a + a_mu + (b_mu + b) k_fb   (:127-131)
 #pragma unroll
     for (int i = 0; i < NS; ++i)
 #pragma unroll
       for (int j = 0; j < NS; ++j) {
-        T s = pr.a[i][j] + io.jac[(c * NS + i) * D + j];
+        T s = pr.a[i][j] + jac[i][j];
 #pragma unroll
-        for (int k = 0; k < NU; ++k) s += (io.jac[(c * NS + i) * D + NS + k] + pr.b[i][k]) * pr.k_fb[k][j];
+        for (int k = 0; k < NU; ++k) s += (jac[i][NS + k] + pr.b[i][k]) * pr.k_fb[k][j];
         h[i][j] = s;
       }
     // Q_0 = H q H^T   (:134)
@@ -255,7 +243,7 @@ reach_step_kernel(ProbDev<T> pr, StepIO<T> io, int64_t N) {
     for (int i = 0; i < NS; ++i) {
       const T ub_mean = pr.l_mu[i] * r_sqr;
       const T ub_sigma = pr.l_sigma[i] * r;
-      const T bse = fix_zero_nan<T>(pr.c_safety * (Num<T>::sqrt_(sg[i]) + ub_sigma), io.flags);
+      const T bse = fix_zero_nan<T>(pr.c_safety * (Num<T>::sqrt_(sg[i]) + ub_sigma), flags);
       d_sig[i] = T(NS) * bse * bse;
       d_mu[i] = T(NS) * ub_mean * ub_mean;
       tr_sig += d_sig[i];
@@ -277,6 +265,80 @@ reach_step_kernel(ProbDev<T> pr, StepIO<T> io, int64_t N) {
 #pragma unroll
       for (int j = 0; j < NS; ++j) q1[i][j] = f_0 * q1[i][j] + (i == j ? f_l * d_l[i] : T(0));
   }
+}
+
+// cost of one step for the CEM objective (safempc_cem.py:304-312; environments.py:505-510; lunarlander.py:111-113)
+template <typename T, int NS>
+__device__ __forceinline__ T step_objective(const ProbDev<T>& pr, const T (&p1)[NS], const T (&sg)[NS]) {
+  if (pr.objective == SE_OBJ_NEG_VARIANCE) {
+    T cost = T(0);
+#pragma unroll
+    for (int i = 0; i < NS; ++i) cost -= sg[i];  // -sum of variances incl. noise (quirk Q7)
+    return cost;
+  }
+  if (pr.objective == SE_OBJ_ABS_STATE1) return Num<T>::abs_(pr.objective_theta - p1[NS > 1 ? 1 : 0]);
+  return -p1[NS - 1];
+}
+
+// constraint cost added by the ellipsoid (p1, q1) produced by step t (last = terminal step): safety polytope on the
+// terminal (or every) ellipsoid, obstacle polytope on the intermediate ones, action box at the end
+template <typename T, int NS, int NU>
+__device__ __forceinline__ T step_constraint(const ProbDev<T>& pr, const T (&p1)[NS], const T (&q1)[NS][NS], bool last,
+                                             const T* act_row, int t_len) {
+  T cc = T(0);
+  if (pr.m_safe > 0 && (last || pr.all_states)) {
+    const bool inside = inside_polytope<T, NS>(p1, q1, pr, T(1), nullptr);
+    if (!inside) cc += pr.state_penalty;  // 10 * (1 - inside), safempc_cem.py:132
+  }
+  if (pr.m_obs > 0 && !last) {
+    // intermediate ellipsoids against the obstacle polytope (safempc_simple.py:373-383, as a penalty)
+    if (!inside_faces<T, NS, SE_MAX_OBS_FACES>(p1, q1, pr.hobs_mat, pr.hobs_vec, pr.m_obs, T(1), nullptr))
+      cc += pr.state_penalty;
+  }
+  if (last && pr.m_act > 0) {
+    // ActionConstraint: penalty * #{t : some face has A u_t - b > 0}  (constrained_cem_mpc.py:29-41, 100-110)
+    int bad = 0;
+    for (int t = 0; t < t_len; ++t) {
+      bool out = false;
+      for (int f = 0; f < pr.m_act; ++f) {
+        T s = -pr.act_b[f];
+#pragma unroll
+        for (int k = 0; k < NU; ++k) s += pr.act_a[f][k] * act_row[t * NU + k];
+        if (s > T(0)) out = true;
+      }
+      bad += out ? 1 : 0;
+    }
+    cc += pr.act_penalty * T(bad);
+  }
+  return cc;
+}
+
+template <typename T, int NS, int NU>
+__global__ void __launch_bounds__(128)
+reach_step_kernel(ProbDev<T> pr, StepIO<T> io, int64_t N) {
+  constexpr int D = NS + NU;
+  const int64_t c = io.first + blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (c >= io.first + N) return;
+
+  T p[NS], u[NU], mu[NS], var[NS], sg[NS];
+#pragma unroll
+  for (int i = 0; i < NS; ++i) {
+    p[i] = io.p_in[c * NS + i];
+    mu[i] = io.mean[c * NS + i];
+    var[i] = io.var[c * NS + i];
+  }
+#pragma unroll
+  for (int j = 0; j < NU; ++j) u[j] = io.u[c * io.u_stride + j];
+  T q[NS][NS], jac[NS][D];
+#pragma unroll
+  for (int i = 0; i < NS; ++i) {
+#pragma unroll
+    for (int j = 0; j < NS; ++j) q[i][j] = io.point ? T(0) : io.q_in[(c * NS + i) * NS + j];
+#pragma unroll
+    for (int j = 0; j < D; ++j) jac[i][j] = io.point ? T(0) : io.jac[(c * NS + i) * D + j];
+  }
+  T p1[NS], q1[NS][NS];
+  ellipsoid_step_core<T, NS, NU>(pr, p, q, io.point != 0, u, mu, var, jac, io.flags, p1, q1, sg);
 
   // ---- write the new ellipsoid ----
 #pragma unroll
@@ -325,46 +387,13 @@ reach_step_kernel(ProbDev<T> pr, StepIO<T> io, int64_t N) {
 
   // ---- CEM bookkeeping ----
   if (io.objective) {
-    T cost;
-    if (pr.objective == SE_OBJ_NEG_VARIANCE) {
-      cost = T(0);
-#pragma unroll
-      for (int i = 0; i < NS; ++i) cost -= sg[i];  // -sum of variances incl. noise (quirk Q7)
-    } else if (pr.objective == SE_OBJ_ABS_STATE1) {
-      cost = Num<T>::abs_(pr.objective_theta - p1[NS > 1 ? 1 : 0]);
-    } else {
-      cost = -p1[NS - 1];
-    }
     const T prev = io.first_step ? T(0) : io.objective[c];
-    io.objective[c] = prev + cost;
+    io.objective[c] = prev + step_objective<T, NS>(pr, p1, sg);
   }
   if (io.constraint) {
-    T cc = io.first_step ? T(0) : io.constraint[c];
-    if (pr.m_safe > 0 && (io.last_step || pr.all_states)) {
-      const bool inside = inside_polytope<T, NS>(p1, q1, pr, T(1), nullptr);
-      if (!inside) cc += pr.state_penalty;  // 10 * (1 - inside), safempc_cem.py:132
-    }
-    if (pr.m_obs > 0 && !io.last_step) {
-      // intermediate ellipsoids against the obstacle polytope (safempc_simple.py:373-383, as a penalty)
-      if (!inside_faces<T, NS, SE_MAX_OBS_FACES>(p1, q1, pr.hobs_mat, pr.hobs_vec, pr.m_obs, T(1), nullptr))
-        cc += pr.state_penalty;
-    }
-    if (io.last_step && pr.m_act > 0) {
-      // ActionConstraint: penalty * #{t : some face has A u_t - b > 0}  (constrained_cem_mpc.py:29-41, 100-110)
-      int bad = 0;
-      for (int t = 0; t < io.T_len; ++t) {
-        bool out = false;
-        for (int f = 0; f < pr.m_act; ++f) {
-          T s = -pr.act_b[f];
-#pragma unroll
-          for (int k = 0; k < NU; ++k) s += pr.act_a[f][k] * io.act_all[(c * io.T_len + t) * NU + k];
-          if (s > T(0)) out = true;
-        }
-        bad += out ? 1 : 0;
-      }
-      cc += pr.act_penalty * T(bad);
-    }
-    io.constraint[c] = cc;
+    const T cc = io.first_step ? T(0) : io.constraint[c];
+    io.constraint[c] = cc + step_constraint<T, NS, NU>(pr, p1, q1, io.last_step != 0,
+                                                       io.act_all ? io.act_all + c * io.T_len * NU : nullptr, io.T_len);
   }
 }
 

@@ -9,6 +9,7 @@
 #include "gp_kernels.cuh"
 #include "launchers.cuh"
 #include "reach_kernels.cuh"
+#include "rollout_kernels.cuh"
 
 namespace se {
 thread_local char g_last_error[1024] = "";
@@ -42,6 +43,7 @@ struct se_gp_s {
   int64_t post_cap = 0;
   int* counter = nullptr;
   se_gemm_impl impl = SE_GEMM_AUTO;
+  bool impl_explicit = false;  // se_gp_set_gemm_impl named an engine: the solve then keeps the four-kernel step
   int sm_count = 148;
   // tcgen05 digit-sliced variance GEMM: digit image of L^-1, per-row scales (built on first use)
   int tc_digits_req = 0;  // 0 = chosen from the prior / noise ratio (tc_auto_digits)
@@ -50,6 +52,8 @@ struct se_gp_s {
   int8_t* b_img = nullptr;
   int* exp_ab = nullptr;  // [ns] exponents of the output scales, then [ns][n_pad] row exponents of L^-1
   double* scale_b = nullptr;
+  // fused small-model rollout (n_pad == 128): L^-T, built on first use
+  void* wt = nullptr;
   // second stream + events of the two-part pipeline in se_cem_solve (created on first use)
   cudaStream_t side = nullptr;
   cudaEvent_t ev_fork = nullptr, ev_join = nullptr, ev_k[2] = {nullptr, nullptr}, ev_g[2] = {nullptr, nullptr};
@@ -168,7 +172,7 @@ extern "C" int se_gp_create(se_gp_t* out, int n_s, int n_u, int n, se_dtype dtyp
 extern "C" int se_gp_destroy(se_gp_t g) {
   if (!g) return 0;
   for (void* p : {g->xt, g->alpha, g->w, g->kst, g->partial, g->post_mean, g->post_var, g->post_jac, (void*)g->counter,
-                  (void*)g->b_img, (void*)g->exp_ab, (void*)g->scale_b})
+                  (void*)g->b_img, (void*)g->exp_ab, (void*)g->scale_b, g->wt})
     if (p) cudaFree(p);
   for (auto e : g->ev_gemm) cudaEventDestroy(e);
   for (auto e : g->ev_kstar) cudaEventDestroy(e);
@@ -188,6 +192,7 @@ extern "C" int se_gp_set_gemm_impl(se_gp_t g, se_gemm_impl impl) {
   SE_REQUIRE(g, "NULL handle");
   SE_REQUIRE(impl != SE_GEMM_TC || g->dtype == SE_F64, "SE_GEMM_TC evaluates float64 models");
   g->impl = resolve_impl(g, impl);
+  g->impl_explicit = impl != SE_GEMM_AUTO;
   return 0;
 }
 extern "C" int se_gp_set_tc_digits(se_gp_t g, int digits) {
@@ -787,7 +792,14 @@ static int cem_solve_t(se_cem_s* c, const ProbDev<T>& pr, const T* p0, const T* 
   const int64_t half0_rows = round_up((cand + 1) / 2, kTile);
   const int64_t two_part_rows = half0_rows + round_up(cand - half0_rows > 0 ? cand - half0_rows : 1, kTile);
   const bool pipelined = pipe_env != 0 && cand >= 4 * kTile && chunk_rows(g, two_part_rows) >= two_part_rows;
-  SE_TRY(gp_reserve(g, pipelined ? two_part_rows : cand));
+  // Models of at most 128 training points: the fused rollout kernel (SE_ROLLOUT_FUSED=0 keeps the four-kernel step).
+  const int fused_env = getenv("SE_ROLLOUT_FUSED") ? atoi(getenv("SE_ROLLOUT_FUSED")) : 1;
+  const bool fused = fused_env != 0 && g->n_pad == kSmallN && !g->timing && !g->impl_explicit;
+  if (fused && !g->wt) {
+    SE_CUDA(cudaMalloc(&g->wt, (size_t)ns * g->n_pad * g->n_pad * g->esz));
+    SE_TRY(launch_transpose_w<T>((const T*)g->w, g->n_pad, ns, (T*)g->wt, st));
+  }
+  if (!fused) SE_TRY(gp_reserve(g, pipelined ? two_part_rows : cand));
   if (g->impl == SE_GEMM_TC) SE_TRY(tc_prepare(g, st));
   if (pipelined && !g->side) {
     SE_CUDA(cudaStreamCreateWithFlags(&g->side, cudaStreamNonBlocking));
@@ -826,7 +838,14 @@ static int cem_solve_t(se_cem_s* c, const ProbDev<T>& pr, const T* p0, const T* 
       io.first = first;
       return io;
     };
-    if (!pipelined) {
+    if (fused) {
+      // small model: one warp carries a candidate through all T steps (rollout_kernels.cuh), one launch per iteration
+      RolloutIO<T> rio;
+      memset(&rio, 0, sizeof(rio));
+      rio.p0 = p, rio.actions = actions, rio.T_len = T_len, rio.objective = objective, rio.constraint = constraint;
+      rio.traj = rec_traj, rio.flags = out->flags, rio.N = cand;
+      SE_TRY(launch_rollout_small<T>(gp_dev<T>(g), (const T*)g->wt, pr, rio, st));
+    } else if (!pipelined) {
       for (int t = 0; t < T_len; ++t) {
         SE_TRY(gp_posterior<T>(g, p, ns, actions + (int64_t)t * nu, tnu, cand, mean, var, t == 0 ? nullptr : jac, st));
         SE_TRY(launch_reach_step<T>(pr, make_io(t, 0), cand, st));

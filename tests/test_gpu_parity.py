@@ -573,3 +573,34 @@ def test_cem_obstacle_polytope_matches_oracle():
     traj, act = res['trajectories'][0, 0], res['rollout_actions'][0, 0]
     for i in (0, 7, 123, 499):
         assert float(obstacle(traj[i], act[i])) == float(extra[i])
+
+
+@pytest.mark.parametrize('which,dtype', [('pendulum', torch.float64), ('cartpole', torch.float64),
+                                         ('box3', torch.float64), ('pendulum', torch.float32)])
+def test_fused_small_model_rollout_equals_the_four_kernel_step(which, dtype, monkeypatch):
+    """n_train <= 128: se_cem_solve runs the whole rollout of a candidate in one kernel (rollout_kernels.cuh).  Same
+    solve with SE_ROLLOUT_FUSED=0 (kernel rows -> variance GEMM -> variance -> ellipsoid step per horizon step):
+    identical decisions, trajectories and costs to rounding (only the summation order inside the GP differs)."""
+    if which == 'pendulum':
+        w = workloads.pendulum_workload(n_train=100, num_rollouts=300, time_horizon=5, num_elites=12, num_iterations=3)
+    elif which == 'cartpole':
+        w = workloads.cartpole_workload(n_train=128, num_rollouts=257, time_horizon=4, num_elites=10, num_iterations=3)
+    else:
+        w = workloads.reach_microbench_workload(n_train=90, n_s=3, num_ellipsoids=200, time_horizon=4)
+        w.num_rollouts, w.num_elites, w.num_iterations = 200, 8, 2
+    out = {}
+    for fused in ('1', '0'):
+        monkeypatch.setenv('SE_ROLLOUT_FUSED', fused)
+        ssm, mpc = workloads.build_solver(w, dtype=dtype, record='full', seed=11)
+        out[fused] = mpc.solve(torch.as_tensor(w.p0, dtype=dtype, device=DEV).unsqueeze(0), seed=11)
+        torch.cuda.synchronize()
+    a, b = out['1'], out['0']
+    tol = 1e-9 if dtype == torch.float64 else 2e-3
+    if dtype == torch.float64:
+        assert torch.equal(a['elite_ids'], b['elite_ids']) and torch.equal(a['best_id'], b['best_id'])
+        assert torch.equal(a['constraint'], b['constraint'])
+    assert torch.equal(a['rollout_actions'][0], b['rollout_actions'][0])  # same candidates in the first iteration
+    scale = float(b['trajectories'][0].abs().max())
+    assert rel_err(a['trajectories'][0].cpu(), b['trajectories'][0].cpu(), 1e-3 * scale) < tol
+    assert rel_err(a['objective'][0].cpu(), b['objective'][0].cpu()) < tol
+    assert torch.equal(a['flags'], b['flags'])
