@@ -126,6 +126,7 @@ __device__ __forceinline__ uint64_t orderable(double x) {
 
 constexpr int kSelThreads = 1024;
 constexpr int kMaxElites = 4096;
+constexpr int kRankSelectMax = 1024;  // populations up to this size are selected by rank counting (<= kMaxElites keys)
 
 template <typename T>
 struct SelectArgs {
@@ -182,6 +183,23 @@ cem_select_refit_kernel(SelectArgs<T> a) {
     return orderable((double)a.costs.get(1, inst, g));
   };
 
+  if (n <= kRankSelectMax) {
+    // Small populations (the reference's own sizes, N = 20 .. 500): rank every key by counting.  Keys are made unique
+    // by the index tie-break, so rank < E  <=>  elite, and the rank IS the position in the sorted elite list: no
+    // radix passes, no compaction, no sort -- two barriers instead of ~40.
+    for (int g = tid; g < n; g += kSelThreads) s_key[g] = key_of(g);
+    __syncthreads();
+    for (int g = tid; g < n; g += kSelThreads) {
+      const uint64_t k = s_key[g];
+      int rank = 0;
+      for (int h = 0; h < n; ++h) {
+        const uint64_t kh = s_key[h];  // same address for the whole warp: broadcast
+        rank += (kh < k || (kh == k && h < g)) ? 1 : 0;
+      }
+      if (rank < E) s_idx[rank] = g;
+    }
+    __syncthreads();
+  } else {
   // radix select: the E-th smallest key, most significant byte first
   if (tid == 0) {
     s_prefix = 0;
@@ -283,6 +301,7 @@ cem_select_refit_kernel(SelectArgs<T> a) {
       __syncthreads();
     }
   }
+  }  // n > kRankSelectMax
   if (a.elite_ids)
     for (int i = tid; i < E; i += kSelThreads) a.elite_ids[(int64_t)inst * E + i] = s_idx[i];
 

@@ -64,6 +64,7 @@ rollout_small_kernel(GpDev<T> gp, const T* __restrict__ wt, ProbDev<T> pr, Rollo
   __shared__ T red[M][NRED];                    // per-warp partial sums of mean and Jacobian
   __shared__ T part[NS][kRolloutWarps][32];     // per-block partial products L^-1[i][jb block] k[jb block]
   __shared__ T ssq[NS][M];                      // per-row-block sums of v_i^2
+  __shared__ T pbuf[NS];                        // centre of the current ellipsoid (warp 0 -> kernel-row threads)
   const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
   const int64_t c = blockIdx.x;
   int32_t* const flags = tid == 0 ? io.flags : nullptr;  // every thread walks the same ellipsoid: count once
@@ -101,7 +102,7 @@ rollout_small_kernel(GpDev<T> gp, const T* __restrict__ wt, ProbDev<T> pr, Rollo
 #pragma unroll
     for (int k = 0; k < NU; ++k) u[k] = act[t * NU + k];
 #pragma unroll
-    for (int dd = 0; dd < D; ++dd) z[dd] = dd < NS ? p[dd] : u[dd - NS];
+    for (int dd = 0; dd < D; ++dd) z[dd] = dd < NS ? (point ? p[dd] : pbuf[dd]) : u[dd - NS];
 
     // ---- kernel rows, mean, mean-Jacobian (gp_ssm_cem.py:45-94; ssm_pytorch/utilities.py:54-85) ----
     if (tid < NP) {
@@ -131,17 +132,6 @@ rollout_small_kernel(GpDev<T> gp, const T* __restrict__ wt, ProbDev<T> pr, Rollo
       }
     }
     __syncthreads();
-    T mean[NS], var[NS], jac[NS][D];
-#pragma unroll
-    for (int o = 0; o < NS; ++o) {
-      mean[o] = (red[0][o * (1 + D)] + red[1][o * (1 + D)]) + (red[2][o * (1 + D)] + red[3][o * (1 + D)]);
-#pragma unroll
-      for (int dd = 0; dd < D; ++dd) {
-        const int r = o * (1 + D) + 1 + dd;
-        jac[o][dd] = point ? T(0) : -((red[0][r] + red[1][r]) + (red[2][r] + red[3][r])) * gp.inv_l2[o][dd];
-      }
-    }
-
     // ---- variance s + noise - || L^-1 k ||^2: this warp's 32 x 32 block, rows 32 mb + lane, columns 32 jb .. ----
 #pragma unroll
     for (int o = 0; o < NS; ++o) {
@@ -171,33 +161,41 @@ rollout_small_kernel(GpDev<T> gp, const T* __restrict__ wt, ProbDev<T> pr, Rollo
       }
     }
     __syncthreads();
+    // ---- ellipsoid step, costs: a serial chain of sqrt / divide, one warp walks it (lanes redundantly) ----
+    if (wid == 0) {
+      T mean[NS], var[NS], jac[NS][D];
 #pragma unroll
-    for (int o = 0; o < NS; ++o)
-      var[o] = gp.outputscale[o] + gp.noise[o] - ((ssq[o][0] + ssq[o][1]) + (ssq[o][2] + ssq[o][3]));
-
-    // ---- ellipsoid step, costs ----
-    T p1[NS], q1[NS][NS], sg[NS];
-    ellipsoid_step_core<T, NS, NU>(pr, p, q, point, u, mean, var, jac, flags, p1, q1, sg);
-    obj += step_objective<T, NS>(pr, p1, sg);
-    cc += step_constraint<T, NS, NU>(pr, p1, q1, t == io.T_len - 1, act, io.T_len);
-    if (io.traj && tid == 0) {
-      T* dst = io.traj + (c * (io.T_len + 1) + t + 1) * (NS + NS * NS);
+      for (int o = 0; o < NS; ++o) {
+        mean[o] = (red[0][o * (1 + D)] + red[1][o * (1 + D)]) + (red[2][o * (1 + D)] + red[3][o * (1 + D)]);
 #pragma unroll
-      for (int i = 0; i < NS; ++i) dst[i] = p1[i];
+        for (int dd = 0; dd < D; ++dd) {
+          const int r = o * (1 + D) + 1 + dd;
+          jac[o][dd] = point ? T(0) : -((red[0][r] + red[1][r]) + (red[2][r] + red[3][r])) * gp.inv_l2[o][dd];
+        }
+        var[o] = gp.outputscale[o] + gp.noise[o] - ((ssq[o][0] + ssq[o][1]) + (ssq[o][2] + ssq[o][3]));
+      }
+      T p1[NS], q1[NS][NS], sg[NS];
+      ellipsoid_step_core<T, NS, NU>(pr, p, q, point, u, mean, var, jac, flags, p1, q1, sg);
+      obj += step_objective<T, NS>(pr, p1, sg);
+      cc += step_constraint<T, NS, NU>(pr, p1, q1, t == io.T_len - 1, act, io.T_len);
+      if (io.traj && tid == 0) {
+        T* dst = io.traj + (c * (io.T_len + 1) + t + 1) * (NS + NS * NS);
 #pragma unroll
-      for (int i = 0; i < NS; ++i)
+        for (int i = 0; i < NS; ++i) dst[i] = p1[i];
 #pragma unroll
-        for (int j = 0; j < NS; ++j) dst[NS + i * NS + j] = q1[i][j];
+        for (int i = 0; i < NS; ++i)
+#pragma unroll
+          for (int j = 0; j < NS; ++j) dst[NS + i * NS + j] = q1[i][j];
+      }
+#pragma unroll
+      for (int i = 0; i < NS; ++i) {
+        p[i] = p1[i];
+        if (lane == 0) pbuf[i] = p1[i];
+#pragma unroll
+        for (int j = 0; j < NS; ++j) q[i][j] = q1[i][j];
+      }
     }
-#pragma unroll
-    for (int i = 0; i < NS; ++i) {
-      p[i] = p1[i];
-#pragma unroll
-      for (int j = 0; j < NS; ++j) q[i][j] = q1[i][j];
-    }
-    // ks / red / part / ssq of this step were last read before the barrier above or by every thread's own ellipsoid
-    // step; the next step writes ks and red before its first barrier, and red was read right after barrier 1, so one
-    // more barrier keeps a fast warp from overwriting what a slow one still reads
+    // publishes pbuf; also keeps a fast warp from overwriting ks / red / part / ssq while warp 0 still reads them
     __syncthreads();
   }
   if (tid == 0) {
