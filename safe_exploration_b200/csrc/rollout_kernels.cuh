@@ -8,7 +8,7 @@
 // only N ~ 500 candidates in flight the kernel is a latency chain, so the work of a step is spread as wide as it goes:
 //
 //   threads 0 .. 127 own training point j          kernel rows k_o(z, x_j) -> shared memory; partial mean / Jacobian
-//   10 warps own the 10 lower 32 x 32 blocks        v_i += L^-1[i][j] k_j: 32 independent coalesced loads of L^-T per
+//   5 warps own the 10 lower 32 x 32 blocks         v_i += L^-1[i][j] k_j: 32 independent coalesced loads of L^-T per
 //   (jb <= m) of L^-1                               thread (all in flight at once), k_j broadcast from shared memory
 //   threads 0 .. 127 own row i                      v_i = sum of its blocks' partials, |v|^2 -> var = s + noise - |v|^2
 //   every thread (redundantly, no divergence)       the ellipsoid step, objective and constraint bookkeeping
@@ -16,24 +16,29 @@
 // One launch per CEM iteration replaces 4 T launches.  Arithmetic and reference citations are those of gp_kernels.cuh and
 // reach_kernels.cuh (ellipsoid_step_core is shared with reach_step_kernel).
 #pragma once
+#include "cem_kernels.cuh"
 #include "common.cuh"
 #include "reach_kernels.cuh"
 
 namespace se {
 
 constexpr int kSmallN = 128;        // n_pad of every model with n_train <= 128 (kTile)
-constexpr int kRolloutWarps = 10;   // one per lower 32 x 32 block of the 128 x 128 factor
+constexpr int kRolloutBlocks = 10;  // lower 32 x 32 blocks of the 128 x 128 factor
+constexpr int kRolloutWarps = 5;    // two blocks per warp: 160 threads, 4 CTAs per SM -> 592 candidates in flight
 
 template <typename T>
 struct RolloutIO {
-  const T* p0;        // [N, NS]      initial point state of every candidate (written by cem_sample_kernel)
-  const T* actions;   // [N, T, NU]
+  ActionSrc<T> src;   // where the candidates come from: the kernel draws its own action sequence (cem_sample fused in)
+  int first, n_local; // this rank's shard of every instance: local candidate cl = inst * n_local + l, global id first + l
+  const T* p0;        // [M, NS]      initial point state of every instance
   int T_len;
-  T* objective;       // [N]
-  T* constraint;      // [N]
+  T* pack;            // [2][N]       (objective, constraint) planes, the all-gather send buffer (cem_pack_costs fused in)
+  T* rec_obj;         // [N] or null  per-iteration records
+  T* rec_con;
+  T* rec_actions;     // [N, T, NU] or null
   T* traj;            // [N, T+1, NS + NS*NS] or null
   int32_t* flags;
-  int64_t N;
+  int64_t N;          // local candidates over all instances
 };
 
 // wt[o][j][i] = w[o][i][j]: L^-T, so that a warp reads 32 consecutive ROWS of column j in one transaction
@@ -56,27 +61,35 @@ __device__ __forceinline__ T warp_sum(T v) {
 }
 
 template <typename T, int NS, int NU>
-__global__ void __launch_bounds__(32 * kRolloutWarps, 2)
+__global__ void __launch_bounds__(32 * kRolloutWarps, 4)
 rollout_small_kernel(GpDev<T> gp, const T* __restrict__ wt, ProbDev<T> pr, RolloutIO<T> io) {
   constexpr int D = NS + NU, NP = kSmallN, M = NP / 32, NRED = NS * (1 + D);
-  static_assert(M == 4 && kRolloutWarps == M * (M + 1) / 2, "one warp per lower block of a 4 x 4 block triangle");
+  static_assert(M == 4 && kRolloutBlocks == M * (M + 1) / 2 && kRolloutBlocks == 2 * kRolloutWarps && kRolloutWarps > M,
+                "two lower blocks of a 4 x 4 block triangle per warp; warps 0 .. 3 also own the kernel rows");
   __shared__ T ks[NS][NP];                      // kernel rows of this step
   __shared__ T red[M][NRED];                    // per-warp partial sums of mean and Jacobian
-  __shared__ T part[NS][kRolloutWarps][32];     // per-block partial products L^-1[i][jb block] k[jb block]
+  __shared__ T part[NS][kRolloutBlocks][32];    // per-block partial products L^-1[i][jb block] k[jb block]
   __shared__ T ssq[NS][M];                      // per-row-block sums of v_i^2
   __shared__ T pbuf[NS];                        // centre of the current ellipsoid (warp 0 -> kernel-row threads)
+  __shared__ T act[SE_MAX_T * NU];              // this candidate's action sequence
   const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
   const int64_t c = blockIdx.x;
   int32_t* const flags = tid == 0 ? io.flags : nullptr;  // every thread walks the same ellipsoid: count once
-  // block (jb, m), jb <= m, of warp wid in the order (0,0) (0,1) (0,2) (0,3) (1,1) (1,2) (1,3) (2,2) (2,3) (3,3)
-  const int jb = wid < 4 ? 0 : wid < 7 ? 1 : wid < 9 ? 2 : 3;
-  const int mb = wid < 4 ? wid : wid < 7 ? wid - 3 : wid < 9 ? wid - 5 : 3;
+  // blocks (jb, m), jb <= m, in the order (0,0) (0,1) (0,2) (0,3) (1,1) (1,2) (1,3) (2,2) (2,3) (3,3): warp w owns 2w, 2w+1
   const int first_of_jb[M] = {0, 4, 7, 9};
 
+  const int inst = (int)(c / io.n_local), gid = io.first + (int)(c % io.n_local);
+  // actions = means + stds * eps (constrained_cem_mpc.py:167), drawn here instead of by a separate launch
+  for (int e = tid; e < io.T_len * NU; e += blockDim.x) {
+    const T a = candidate_action<T>(io.src, inst, gid, e);
+    act[e] = a;
+    if (io.rec_actions) io.rec_actions[c * io.T_len * NU + e] = a;
+  }
+  __syncthreads();
   T p[NS], q[NS][NS];
 #pragma unroll
   for (int i = 0; i < NS; ++i) {
-    p[i] = io.p0[c * NS + i];
+    p[i] = io.p0[inst * NS + i];
 #pragma unroll
     for (int j = 0; j < NS; ++j) q[i][j] = T(0);
   }
@@ -93,7 +106,6 @@ rollout_small_kernel(GpDev<T> gp, const T* __restrict__ wt, ProbDev<T> pr, Rollo
     for (int i = 0; i < NS * NS; ++i) d0[NS + i] = T(0);
   }
 
-  const T* const act = io.actions + c * io.T_len * NU;
   T obj = T(0), cc = T(0);
 #pragma unroll 1
   for (int t = 0; t < io.T_len; ++t) {
@@ -134,18 +146,24 @@ rollout_small_kernel(GpDev<T> gp, const T* __restrict__ wt, ProbDev<T> pr, Rollo
     __syncthreads();
     // ---- variance s + noise - || L^-1 k ||^2: this warp's 32 x 32 block, rows 32 mb + lane, columns 32 jb .. ----
 #pragma unroll
-    for (int o = 0; o < NS; ++o) {
-      const T* const wo = wt + ((int64_t)o * NP + 32 * jb) * NP + 32 * mb + lane;
-      T wv[32];
+    for (int bi = 0; bi < 2; ++bi) {
+      const int blk = 2 * wid + bi;
+      const int jb = blk < 4 ? 0 : blk < 7 ? 1 : blk < 9 ? 2 : 3;
+      const int mb = blk < 4 ? blk : blk < 7 ? blk - 3 : blk < 9 ? blk - 5 : 3;
 #pragma unroll
-      for (int jj = 0; jj < 32; ++jj) wv[jj] = wo[jj * NP];  // 32 independent coalesced loads in flight
-      T v0 = T(0), v1 = T(0);
+      for (int o = 0; o < NS; ++o) {
+        const T* const wo = wt + ((int64_t)o * NP + 32 * jb) * NP + 32 * mb + lane;
+        T wv[32];
 #pragma unroll
-      for (int jj = 0; jj < 32; jj += 2) {
-        v0 += wv[jj] * ks[o][32 * jb + jj];
-        v1 += wv[jj + 1] * ks[o][32 * jb + jj + 1];
+        for (int jj = 0; jj < 32; ++jj) wv[jj] = wo[jj * NP];  // 32 independent coalesced loads in flight
+        T v0 = T(0), v1 = T(0);
+#pragma unroll
+        for (int jj = 0; jj < 32; jj += 2) {
+          v0 += wv[jj] * ks[o][32 * jb + jj];
+          v1 += wv[jj + 1] * ks[o][32 * jb + jj + 1];
+        }
+        part[o][blk][lane] = v0 + v1;
       }
-      part[o][wid][lane] = v0 + v1;
     }
     __syncthreads();
     if (tid < NP) {
@@ -199,8 +217,10 @@ rollout_small_kernel(GpDev<T> gp, const T* __restrict__ wt, ProbDev<T> pr, Rollo
     __syncthreads();
   }
   if (tid == 0) {
-    io.objective[c] = obj;
-    io.constraint[c] = cc;
+    io.pack[c] = obj;
+    io.pack[io.N + c] = cc;
+    if (io.rec_obj) io.rec_obj[c] = obj;
+    if (io.rec_con) io.rec_con[c] = cc;
   }
 }
 

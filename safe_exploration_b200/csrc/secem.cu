@@ -820,7 +820,7 @@ static int cem_solve_t(se_cem_s* c, const ProbDev<T>& pr, const T* p0, const T* 
     src.stdv = c->stdv + (size_t)it * dist;
     T* rec_act = out->rollout_actions ? (T*)out->rollout_actions + (size_t)it * cand * tnu : nullptr;
     T* rec_traj = out->trajectories ? (T*)out->trajectories + (size_t)it * cand * (T_len + 1) * S : nullptr;
-    SE_TRY(launch_cem_sample<T>(src, M, cf.first_rollout, Nl, ns, p0, actions, p, rec_act, st));
+    if (!fused) SE_TRY(launch_cem_sample<T>(src, M, cf.first_rollout, Nl, ns, p0, actions, p, rec_act, st));
 
     // RolloutFunction._sample_trajectory (constrained_cem_mpc.py:175-183): T sequential ellipsoid steps
     auto make_io = [&](int t, int64_t first) {
@@ -842,8 +842,10 @@ static int cem_solve_t(se_cem_s* c, const ProbDev<T>& pr, const T* p0, const T* 
       // small model: one warp carries a candidate through all T steps (rollout_kernels.cuh), one launch per iteration
       RolloutIO<T> rio;
       memset(&rio, 0, sizeof(rio));
-      rio.p0 = p, rio.actions = actions, rio.T_len = T_len, rio.objective = objective, rio.constraint = constraint;
-      rio.traj = rec_traj, rio.flags = out->flags, rio.N = cand;
+      rio.src = src, rio.first = cf.first_rollout, rio.n_local = Nl, rio.p0 = p0, rio.T_len = T_len;
+      rio.pack = pack_local, rio.rec_obj = out->objective ? (T*)out->objective + (size_t)it * cand : nullptr;
+      rio.rec_con = out->constraint ? (T*)out->constraint + (size_t)it * cand : nullptr;
+      rio.rec_actions = rec_act, rio.traj = rec_traj, rio.flags = out->flags, rio.N = cand;
       SE_TRY(launch_rollout_small<T>(gp_dev<T>(g), (const T*)g->wt, pr, rio, st));
     } else if (!pipelined) {
       for (int t = 0; t < T_len; ++t) {
@@ -878,7 +880,7 @@ static int cem_solve_t(se_cem_s* c, const ProbDev<T>& pr, const T* p0, const T* 
 
     T* rec_obj = out->objective ? (T*)out->objective + (size_t)it * cand : nullptr;
     T* rec_con = out->constraint ? (T*)out->constraint + (size_t)it * cand : nullptr;
-    SE_TRY(launch_cem_pack_costs<T>(objective, constraint, cand, pack_local, rec_obj, rec_con, st));
+    if (!fused) SE_TRY(launch_cem_pack_costs<T>(objective, constraint, cand, pack_local, rec_obj, rec_con, st));
     if (c->world > 1) {
       // the one collective of the path: per-candidate (objective, constraint) costs of every rank
       const int r = g_nccl.AllGather(pack_local, pack_all, (size_t)(2 * cand), sizeof(T) == 8 ? 8 : 7, c->comm, st);
