@@ -218,7 +218,11 @@ def run_b200(args):
     barrier()
 
     # ---- device-resident timing: K solves between two events, max over ranks ----
-    _lib.check(lib.se_gp_timing_enable(ssm.handle, 1))
+    # models of <= 128 training points run the fused rollout kernel (one launch per CEM iteration); the per-kernel
+    # event timing below would switch the library back to the four-kernel step, so it stays off for them
+    fused_small = w.n_train <= 128 and args.gemm == 'auto' and os.environ.get('SE_ROLLOUT_FUSED', '1') != '0'
+    if not fused_small:
+        _lib.check(lib.se_gp_timing_enable(ssm.handle, 1))
     lib.se_launch_count_reset()
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     with ClockSampler(local_rank) as clocks:
@@ -325,6 +329,18 @@ def run_b200(args):
         'hbm': {'algorithmic_bytes_per_launch': (w.n_s * rows_local * w.n_train + w.n_s * w.n_train ** 2 / 2) * op_bytes,
                 'peak_gbs': peaks.get('hbm_gbs')},
     }
+
+    if fused_small:
+        # no separate variance GEMM: the whole rollout is one latency-bound kernel; quote the solve's FP64 work rate
+        f_step = w.n_s * (w.n_train ** 2 + w.n_train * (5 * (w.n_s + w.n_u) + 8))
+        ach = (cand_steps / world) * f_step / (ms_per_step * 1e-3) / 1e12
+        roofline = {'bound': 'tensor', 'kernel': 'rollout_small_kernel (kernel rows + variance + ellipsoid step of a whole '
+                    'rollout, one CTA per candidate)', 'impl': 'fused-rollout', 'pipe': 'FP64 (DFMA)', 'achieved': ach,
+                    'peak': fp64_peak, 'unit': 'TFLOP/s', 'frac': (ach / fp64_peak) if fp64_peak else None,
+                    'peak_source': 'se_measure_peak (register-resident DFMA / DMMA loop on every SM)',
+                    'note': 'latency-bound by construction: N x T x I = %d candidate-steps of %.2e flop each; the figure '
+                            'is algorithmic flop of the whole solve over its time' % (cand_steps, f_step),
+                    'work_per_launch': (cand_steps / world / w.num_iterations) * f_step, 'traffic': None}
 
     # ---- accuracy of the variance path actually timed, against the float64 DMMA kernel, on 2048 visited inputs ----
     variance_check = None
