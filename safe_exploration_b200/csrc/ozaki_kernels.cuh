@@ -414,7 +414,9 @@ gp_kstar_slices_kernel(GpDev<double> gp, const double* __restrict__ p, int64_t p
 // L1 per candidate at n = 2048 and sits at 84 % L1 throughput with the FP64 pipe at 41 %).
 // ---------------------------------------------------------------------------------------------------------------------
 template <int NS, int D, bool JAC>
-__global__ void __launch_bounds__(64, 8)
+// CTAs per SM: 8 (128 registers) is the measured optimum for n_s <= 3 (C2: 0.216 ms; 6 -> 0.279, 10 -> 0.226, 12 -> 0.240);
+// with 4 and more outputs the accumulators no longer fit and 6 (168 registers) wins (C3: 3.10 vs 3.82 ms)
+__global__ void __launch_bounds__(64, NS <= 3 ? 8 : 6)
 gp_kstar_slices8_kernel(GpDev<double> gp, const double* __restrict__ p, int64_t p_stride, const double* __restrict__ u,
                         int64_t u_stride, int64_t row0, int nrows, int rows_pad, const int* __restrict__ exp_a, int S,
                         int8_t* __restrict__ a_img, double* __restrict__ mean, double* __restrict__ jac) {
