@@ -405,10 +405,13 @@ gp_trisumsq_dmma_kernel(const double* __restrict__ kst, const double* __restrict
   }
 }
 
-// var[c][o] = s_o + noise_o - sum_ib partial[o][ib][row]  (fixed summation order => run-to-run reproducible)
+// var[c][o] = s_o + noise_o - sum_ib partial[o][ib][row]  (fixed summation order => run-to-run reproducible).
+// When the kernel-row kernel split the training set over CTAs (small batches), kpart [nseg][rows_pad][ns][1 + d] holds
+// its per-segment mean / Jacobian sums; they are added here in segment order, exactly as the unsplit kernel adds them.
 template <typename T>
 __global__ void gp_var_kernel(GpDev<T> gp, const T* __restrict__ partial, int nb, int rows_pad, int64_t row0,
-                              int nrows, T* __restrict__ var) {
+                              int nrows, T* __restrict__ var, const T* __restrict__ kpart, int nseg,
+                              T* __restrict__ mean, T* __restrict__ jac) {
   const int64_t idx = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
   if (idx >= (int64_t)nrows * gp.ns) return;
   const int o = idx % gp.ns;
@@ -416,6 +419,20 @@ __global__ void gp_var_kernel(GpDev<T> gp, const T* __restrict__ partial, int nb
   T s = T(0);
   for (int ib = 0; ib < nb; ++ib) s += partial[((int64_t)o * nb + ib) * rows_pad + r];
   var[(row0 + r) * gp.ns + o] = gp.outputscale[o] - s + gp.noise[o];
+  if (nseg > 0) {
+    const int w = 1 + gp.d;
+    const T* src = kpart + (r * gp.ns + o) * w;
+    const int64_t seg_stride = (int64_t)rows_pad * gp.ns * w;
+    T m = T(0);
+    for (int sg = 0; sg < nseg; ++sg) m += src[sg * seg_stride];
+    mean[(row0 + r) * gp.ns + o] = m;
+    if (jac)
+      for (int dd = 0; dd < gp.d; ++dd) {
+        T g = T(0);
+        for (int sg = 0; sg < nseg; ++sg) g += src[sg * seg_stride + 1 + dd];
+        jac[((row0 + r) * gp.ns + o) * gp.d + dd] = -g * gp.inv_l2[o][dd];
+      }
+  }
 }
 
 }  // namespace se

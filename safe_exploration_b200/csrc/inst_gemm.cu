@@ -89,14 +89,16 @@ int launch_trisumsq<double>(se_gemm_impl impl, const double* kst, const double* 
 
 template <typename T>
 int launch_var(const GpDev<T>& gp, const T* partial, int nb, int rows_pad, int64_t row0, int nrows, T* var,
-               cudaStream_t stream) {
+               const T* kpart, int nseg, T* mean, T* jac, cudaStream_t stream) {
   const int64_t total = (int64_t)nrows * gp.ns;
   SE_LAUNCH((gp_var_kernel<T>), (int)ceil_div(total, 256), 256, 0, stream, gp, partial, nb, rows_pad, row0, nrows,
-            var);
+            var, kpart, nseg, mean, jac);
   return 0;
 }
-template int launch_var<float>(const GpDev<float>&, const float*, int, int, int64_t, int, float*, cudaStream_t);
-template int launch_var<double>(const GpDev<double>&, const double*, int, int, int64_t, int, double*, cudaStream_t);
+template int launch_var<float>(const GpDev<float>&, const float*, int, int, int64_t, int, float*, const float*, int,
+                               float*, float*, cudaStream_t);
+template int launch_var<double>(const GpDev<double>&, const double*, int, int, int64_t, int, double*, const double*, int,
+                                double*, double*, cudaStream_t);
 
 template <typename T>
 int launch_pack_model(const T* x, const T* alpha, const T* linv, int n, int d, int ns, int n_pad, T* xt, T* alpha_p,

@@ -30,22 +30,26 @@ int launch_oz_pack_model(const double* w, int n_pad, int ns, const double* host_
 
 int launch_kstar_slices(const GpDev<double>& gp, const double* p, int64_t p_stride, const double* u, int64_t u_stride,
                         int64_t row0, int nrows, int rows_pad, const int* exp_a, int S, int8_t* a_img, double* mean,
-                        double* jac, cudaStream_t stream) {
+                        double* jac, int seg_per_cta, double* kpart, cudaStream_t stream) {
   // SE_KSTAR_R = 1 / 2: the one-warp-per-row(-pair) kernels, kept for comparison; default: the row-group kernel
   static const int r_env = getenv("SE_KSTAR_R") ? atoi(getenv("SE_KSTAR_R")) : 8;
   const bool want_jac = jac != nullptr;
   if (r_env != 1 && r_env != 2) {
     static const int nostore = getenv("SE_KSTAR_NOSTORE") ? atoi(getenv("SE_KSTAR_NOSTORE")) : 0;  // measurement only
     if (nostore) S = 0;
-    const int grid8 = (int)ceil_div(rows_pad / 8, 2);
+    // seg_per_cta > 0: the training set is split over blockIdx.y in runs of seg_per_cta 128-point segments (small
+    // batches); 0: one CTA walks all of it
+    const int segs = gp.n_pad / 128;
+    const int spc = seg_per_cta > 0 ? seg_per_cta : segs;
+    dim3 grid8((unsigned)ceil_div(rows_pad / 8, 2), (unsigned)ceil_div(segs, spc));
 #define SE_CASE8(NS_, NU_)                                                                                          \
   if (gp.ns == NS_ && gp.nu == NU_) {                                                                               \
     if (want_jac)                                                                                                   \
       SE_LAUNCH((oz::gp_kstar_slices8_kernel<NS_, NS_ + NU_, true>), grid8, 64, 0, stream, gp, p, p_stride, u,      \
-                u_stride, row0, nrows, rows_pad, exp_a, S, a_img, mean, jac);                                       \
+                u_stride, row0, nrows, rows_pad, exp_a, S, a_img, mean, jac, spc, kpart);                           \
     else                                                                                                            \
       SE_LAUNCH((oz::gp_kstar_slices8_kernel<NS_, NS_ + NU_, false>), grid8, 64, 0, stream, gp, p, p_stride, u,     \
-                u_stride, row0, nrows, rows_pad, exp_a, S, a_img, mean, jac);                                       \
+                u_stride, row0, nrows, rows_pad, exp_a, S, a_img, mean, jac, spc, kpart);                           \
     return 0;                                                                                                       \
   }
     SE_FOR_NS_NU(SE_CASE8)

@@ -26,7 +26,7 @@ int launch_trisumsq(se_gemm_impl impl, const T* kst, const T* w, int n_pad, int 
 
 template <typename T>
 int launch_var(const GpDev<T>& gp, const T* partial, int nb, int rows_pad, int64_t row0, int nrows, T* var,
-               cudaStream_t stream);
+               const T* kpart, int nseg, T* mean, T* jac, cudaStream_t stream);
 
 template <typename T>
 int launch_reach_step(const ProbDev<T>& pr, const StepIO<T>& io, int64_t N, cudaStream_t stream);
@@ -71,7 +71,7 @@ int launch_oz_pack_model(const double* w, int n_pad, int ns, const double* host_
                          int* exp_b, double* scale_b, int8_t* b_img, cudaStream_t stream);
 int launch_kstar_slices(const GpDev<double>& gp, const double* p, int64_t p_stride, const double* u, int64_t u_stride,
                         int64_t row0, int nrows, int rows_pad, const int* exp_a, int S, int8_t* a_img, double* mean,
-                        double* jac, cudaStream_t stream);
+                        double* jac, int seg_per_cta, double* kpart, cudaStream_t stream);
 int launch_trisumsq_ozaki(const int8_t* a_img, const int8_t* b_img, const double* scale_b, int n, int n_pad,
                           int rows_pad, int ns, int S, double* partial, int sm_count, int* nb_out, cudaStream_t stream);
 int launch_oz_probe(const int8_t* a_img, const int8_t* b_img, int nk, int S, int lbo, int sbo, int32_t* out,

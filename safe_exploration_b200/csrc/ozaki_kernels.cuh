@@ -419,7 +419,8 @@ template <int NS, int D, bool JAC>
 __global__ void __launch_bounds__(64, NS <= 3 ? 8 : 6)
 gp_kstar_slices8_kernel(GpDev<double> gp, const double* __restrict__ p, int64_t p_stride, const double* __restrict__ u,
                         int64_t u_stride, int64_t row0, int nrows, int rows_pad, const int* __restrict__ exp_a, int S,
-                        int8_t* __restrict__ a_img, double* __restrict__ mean, double* __restrict__ jac) {
+                        int8_t* __restrict__ a_img, double* __restrict__ mean, double* __restrict__ jac,
+                        int seg_per_cta, double* __restrict__ kpart) {
   const int lane = threadIdx.x & 31;
   const int64_t warp = blockIdx.x * (int64_t)(blockDim.x >> 5) + (threadIdx.x >> 5);
   const int64_t r0 = warp * 8;  // rows_pad is a multiple of 128 and the grid is rows_pad / 16 CTAs: every warp has rows
@@ -456,12 +457,16 @@ gp_kstar_slices8_kernel(GpDev<double> gp, const double* __restrict__ p, int64_t 
 #pragma unroll
     for (int dd = 0; dd < D; ++dd) poison |= !finite_f64(nh_inv_l2[o][dd]);
   }
-  double m_acc[NS], j_acc[NS][JAC ? D : 1];
+  // Mean and Jacobian sums are formed per 128-point segment (lane partials folded over the four quads) and the
+  // segments are added in order -- by this CTA, or, when the training set is split over blockIdx.y because the batch
+  // is too small to fill the machine, by gp_var_kernel from kpart.  Same additions in the same order either way, so
+  // the result does not depend on how a batch was chunked or split.
+  double m_acc[NS], j_acc[NS][JAC ? D : 1], m_tot[NS], j_tot[NS][JAC ? D : 1];
 #pragma unroll
   for (int o = 0; o < NS; ++o) {
-    m_acc[o] = 0.0;
+    m_acc[o] = m_tot[o] = 0.0;
 #pragma unroll
-    for (int dd = 0; dd < (JAC ? D : 1); ++dd) j_acc[o][dd] = 0.0;
+    for (int dd = 0; dd < (JAC ? D : 1); ++dd) j_acc[o][dd] = j_tot[o][dd] = 0.0;
   }
   // byte offset of (this lane's row, K index 4 quad) inside a digit-plane block; the K half adds 128
   const int ct = (int)(r0 / TM), rl = (int)(r0 % TM) + r8;
@@ -484,11 +489,13 @@ gp_kstar_slices8_kernel(GpDev<double> gp, const double* __restrict__ p, int64_t 
     }
     asm volatile("cp.async.commit_group;\n" ::: "memory");
   };
-  const int chunks = n_pad / CH;
-  fill(0, 0);
+  const int ch0 = blockIdx.y * seg_per_cta;
+  const int chunks = min(n_pad / CH, ch0 + seg_per_cta);
+  const bool split = gridDim.y > 1;
+  fill(ch0, 0);
 #pragma unroll 1
-  for (int ch = 0; ch < chunks; ++ch) {
-    const int buf = ch & 1;
+  for (int ch = ch0; ch < chunks; ++ch) {
+    const int buf = (ch - ch0) & 1;
     if (ch + 1 < chunks) {
       fill(ch + 1, buf ^ 1);
       asm volatile("cp.async.wait_group 1;\n" ::: "memory");
@@ -548,23 +555,49 @@ gp_kstar_slices8_kernel(GpDev<double> gp, const double* __restrict__ p, int64_t 
         if (t < S) *reinterpret_cast<uint32_t*>(dst + t * A_BLK) = word[t];
     }
   }
+    // segment done: fold the quads (lanes r8, r8 + 8, r8 + 16, r8 + 24 hold disjoint training points), then add the
+    // segment to the running total or hand it to gp_var_kernel
+#pragma unroll
+    for (int o = 0; o < NS; ++o) {
+      double v = m_acc[o];
+      v += __shfl_xor_sync(0xffffffffu, v, 8);
+      v += __shfl_xor_sync(0xffffffffu, v, 16);
+      m_acc[o] = 0.0;
+      if (poison) v = __longlong_as_double(0x7ff8000000000000ll);
+      if (split) {
+        if (quad == 0) kpart[(((int64_t)ch * rows_pad + row) * NS + o) * (1 + D)] = v;
+      } else {
+        m_tot[o] += v;
+      }
+      if (JAC) {
+#pragma unroll
+        for (int dd = 0; dd < D; ++dd) {
+          double g = j_acc[o][dd];
+          g += __shfl_xor_sync(0xffffffffu, g, 8);
+          g += __shfl_xor_sync(0xffffffffu, g, 16);
+          j_acc[o][dd] = 0.0;
+          if (poison) g = __longlong_as_double(0x7ff8000000000000ll);
+          if (split) {
+            if (quad == 0) kpart[(((int64_t)ch * rows_pad + row) * NS + o) * (1 + D) + 1 + dd] = g;
+          } else {
+            j_tot[o][dd] += g;
+          }
+        }
+      }
+    }
     __syncthreads();  // everyone is done with this buffer before the chunk after next lands in it
   }
+  if (split) return;  // gp_var_kernel adds the segments
 
-  // the four quads of a row hold disjoint training points: fold them (lanes r8, r8 + 8, r8 + 16, r8 + 24)
 #pragma unroll
   for (int o = 0; o < NS; ++o) {
-    double v = m_acc[o];
-    v += __shfl_xor_sync(0xffffffffu, v, 8);
-    v += __shfl_xor_sync(0xffffffffu, v, 16);
+    double v = m_tot[o];
     if (poison) v = __longlong_as_double(0x7ff8000000000000ll);
     if (quad == 0 && valid) mean[(row0 + row) * NS + o] = v;
     if (JAC) {
 #pragma unroll
       for (int dd = 0; dd < D; ++dd) {
-        double g = j_acc[o][dd];  // sum_i alpha_i k_i (z_d - x_id); d mean / d z_d = -that / l_d^2
-        g += __shfl_xor_sync(0xffffffffu, g, 8);
-        g += __shfl_xor_sync(0xffffffffu, g, 16);
+        double g = j_tot[o][dd];  // sum_i alpha_i k_i (z_d - x_id); d mean / d z_d = -that / l_d^2
         if (poison) g = __longlong_as_double(0x7ff8000000000000ll);
         if (quad == 0 && valid) jac[((row0 + row) * NS + o) * D + dd] = -g * gp.inv_l2[o][dd];
       }

@@ -21,6 +21,8 @@ using namespace se;
 // -------------------------------------------------------------------------------------------------------------------
 // handles
 // -------------------------------------------------------------------------------------------------------------------
+constexpr int64_t kSplitRows = 4096;  // below this a kernel-row launch splits the training set over CTAs
+
 struct se_gp_s {
   se_dtype dtype = SE_F64;
   int ns = 0, nu = 0, d = 0, n = 0, n_pad = 0;
@@ -37,6 +39,8 @@ struct se_gp_s {
   size_t kst_bytes = 0;
   void* partial = nullptr;
   size_t partial_bytes = 0;
+  void* kpart = nullptr;  // per-segment mean / Jacobian sums of a split kernel-row launch (small batches, tcgen05 path)
+  size_t kpart_bytes = 0;
   void* post_mean = nullptr;  // [cap, ns]
   void* post_var = nullptr;
   void* post_jac = nullptr;  // [cap, ns, d]
@@ -171,7 +175,7 @@ extern "C" int se_gp_create(se_gp_t* out, int n_s, int n_u, int n, se_dtype dtyp
 
 extern "C" int se_gp_destroy(se_gp_t g) {
   if (!g) return 0;
-  for (void* p : {g->xt, g->alpha, g->w, g->kst, g->partial, g->post_mean, g->post_var, g->post_jac, (void*)g->counter,
+  for (void* p : {g->xt, g->alpha, g->w, g->kst, g->partial, g->kpart, g->post_mean, g->post_var, g->post_jac, (void*)g->counter,
                   (void*)g->b_img, (void*)g->exp_ab, (void*)g->scale_b, g->wt})
     if (p) cudaFree(p);
   for (auto e : g->ev_gemm) cudaEventDestroy(e);
@@ -300,7 +304,24 @@ static int gp_reserve(se_gp_s* g, int64_t N) {
   const int64_t rows = chunk_rows(g, N);
   SE_TRY(grow(&g->kst, &g->kst_bytes, (size_t)g->ns * rows * g->n_pad * g->esz));
   SE_TRY(grow(&g->partial, &g->partial_bytes, (size_t)g->ns * (g->n_pad / 32) * rows * g->esz));
+  if (g->impl == SE_GEMM_TC) {
+    const int64_t split_rows = rows < kSplitRows ? rows : kSplitRows;
+    SE_TRY(grow(&g->kpart, &g->kpart_bytes, (size_t)(g->n_pad / 128) * split_rows * g->ns * (1 + g->d) * sizeof(double)));
+  }
   return 0;
+}
+// Kernel-row launches of fewer than kSplitRows candidates do not fill the machine with one CTA per 16 rows (148 SMs x
+// 8 CTAs); the training set is then split over CTAs in runs of 128-point segments.  Returns segments per CTA, 0 = none.
+static int kstar_segments_per_cta(const se_gp_s* g, int rows_pad) {
+  static const int env = getenv("SE_KSTAR_SPLIT") ? atoi(getenv("SE_KSTAR_SPLIT")) : 1;
+  const int segs = g->n_pad / 128;
+  if (!env || g->impl != SE_GEMM_TC || rows_pad >= kSplitRows || segs < 2) return 0;
+  const int row_ctas = rows_pad / 16;
+  int ways = (2 * g->sm_count + row_ctas - 1) / row_ctas;  // ~2 CTAs per SM in total
+  if (ways > segs) ways = segs;
+  if (ways < 2) return 0;
+  const int spc = (segs + ways - 1) / ways;
+  return spc < segs ? spc : 0;
 }
 static int gp_reserve_posterior(se_gp_s* g, int64_t N) {
   if (g->post_cap >= N) return 0;
@@ -333,6 +354,8 @@ struct PostPart {
   int nrows, rows_pad, nb;
   void* kst;      // this part's kernel rows (plain) or digit image (tcgen05 path)
   void* partial;  // this part's partial sums
+  void* kpart;    // this part's per-segment mean / Jacobian sums (split kernel-row launch)
+  int seg_per_cta, nseg;  // 0 / 0: the kernel-row kernel wrote mean and Jacobian itself
 };
 
 template <typename T>
@@ -342,6 +365,11 @@ static PostPart post_part(se_gp_s* g, int64_t row0, int nrows, int64_t slot_row0
   // slot_row0: first (padded) row of this part inside the workspace
   pp.kst = (char*)g->kst + (size_t)g->ns * slot_row0 * g->n_pad * g->esz;
   pp.partial = (char*)g->partial + (size_t)g->ns * (g->n_pad / 32) * slot_row0 * g->esz;
+  pp.seg_per_cta = kstar_segments_per_cta(g, pp.rows_pad);
+  pp.nseg = pp.seg_per_cta > 0 ? g->n_pad / 128 : 0;
+  pp.kpart = g->kpart ? (char*)g->kpart + (size_t)(g->n_pad / 128) * slot_row0 * g->ns * (1 + g->d) * sizeof(double)
+                      : nullptr;
+  if (pp.nseg > 0 && (slot_row0 + pp.rows_pad > kSplitRows || !g->kpart)) pp.seg_per_cta = pp.nseg = 0;
   return pp;
 }
 
@@ -353,7 +381,7 @@ static int post_kstar(se_gp_s* g, const GpDev<T>& gd, const PostPart& pp, const 
   if constexpr (sizeof(T) == 8) {
     if (tc)  // kernel rows as int8 digit planes (<= 8 bytes per element, like the float64 rows they replace)
       SE_TRY(launch_kstar_slices(gd, p, p_stride, u, u_stride, pp.row0, pp.nrows, pp.rows_pad, g->exp_ab,
-                                 g->tc_digits, (int8_t*)pp.kst, mean, jac, st));
+                                 g->tc_digits, (int8_t*)pp.kst, mean, jac, pp.seg_per_cta, (double*)pp.kpart, st));
   }
   if (!tc)
     SE_TRY(launch_kstar<T>(gd, p, p_stride, u, u_stride, pp.row0, pp.nrows, pp.rows_pad, (T*)pp.kst, mean, jac, st));
@@ -378,8 +406,9 @@ static int post_gemm(se_gp_s* g, const GpDev<T>& gd, PostPart& pp, cudaStream_t 
 }
 
 template <typename T>
-static int post_var(se_gp_s* g, const GpDev<T>& gd, const PostPart& pp, T* var, cudaStream_t st) {
-  return launch_var<T>(gd, (const T*)pp.partial, pp.nb, pp.rows_pad, pp.row0, pp.nrows, var, st);
+static int post_var(se_gp_s* g, const GpDev<T>& gd, const PostPart& pp, T* var, T* mean, T* jac, cudaStream_t st) {
+  return launch_var<T>(gd, (const T*)pp.partial, pp.nb, pp.rows_pad, pp.row0, pp.nrows, var, (const T*)pp.kpart,
+                       pp.nseg, mean, jac, st);
 }
 
 // GP posterior for N candidates whose inputs are z_c = [p[c*p_stride : +ns] | u[c*u_stride : +nu]]
@@ -396,7 +425,7 @@ static int gp_posterior(se_gp_s* g, const T* p, int64_t p_stride, const T* u, in
     PostPart pp = post_part<T>(g, row0, nrows, 0);
     SE_TRY(post_kstar<T>(g, gd, pp, p, p_stride, u, u_stride, mean, jac, st));
     SE_TRY(post_gemm<T>(g, gd, pp, st));
-    SE_TRY(post_var<T>(g, gd, pp, var, st));
+    SE_TRY(post_var<T>(g, gd, pp, var, mean, jac, st));
   }
   return 0;
 }
@@ -871,7 +900,7 @@ static int cem_solve_t(se_cem_s* c, const ProbDev<T>& pr, const T* p0, const T* 
           SE_TRY(post_gemm<T>(g, gd, pp, st));
           SE_CUDA(cudaEventRecord(g->ev_g[h], st));
           SE_CUDA(cudaStreamWaitEvent(g->side, g->ev_g[h], 0));
-          SE_TRY(post_var<T>(g, gd, pp, var, g->side));
+          SE_TRY(post_var<T>(g, gd, pp, var, mean, t == 0 ? nullptr : jac, g->side));
           SE_TRY(launch_reach_step<T>(pr, make_io(t, pp.row0), pp.nrows, g->side));
         }
       SE_CUDA(cudaEventRecord(g->ev_join, g->side));
