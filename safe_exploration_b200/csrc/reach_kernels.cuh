@@ -165,6 +165,14 @@ struct StepIO {
   T* sigma_all;    // [N, T, NS]
   int32_t* flags;
   int64_t first;   // first candidate of this launch (all arrays are indexed by the absolute candidate id)
+  // Fused variance reduction (se_cem_solve): when `partial` is set, the kernel forms var = s + noise - sum_ib partial
+  // itself (what gp_var_kernel does, same order) instead of reading `var`, and, when the kernel-row launch was split
+  // (nseg > 0), also the mean / Jacobian from the per-segment sums in kpart.  Rows are local: candidate c <-> c - first.
+  const T* partial;  // [ns][nb][rows_pad]
+  int nb, rows_pad;
+  const T* kpart;    // [nseg][rows_pad][ns][1 + d]
+  int nseg;
+  T gp_outputscale[SE_MAX_NS], gp_noise[SE_MAX_NS], gp_inv_l2[SE_MAX_NS][SE_MAX_D];
 };
 
 // One ellipsoid step on register operands (gp_reachability_pytorch.py:18-181): (p, q | point) + GP posterior at
@@ -321,22 +329,42 @@ reach_step_kernel(ProbDev<T> pr, StepIO<T> io, int64_t N) {
   if (c >= io.first + N) return;
 
   T p[NS], u[NU], mu[NS], var[NS], sg[NS];
+  T q[NS][NS], jac[NS][D];
+  const bool split_sums = io.partial && io.nseg > 0;
 #pragma unroll
   for (int i = 0; i < NS; ++i) {
     p[i] = io.p_in[c * NS + i];
-    mu[i] = io.mean[c * NS + i];
-    var[i] = io.var[c * NS + i];
+    if (io.partial) {  // gp_var_kernel, fused
+      const int64_t r = c - io.first;
+      T s = T(0);
+      for (int ib = 0; ib < io.nb; ++ib) s += io.partial[((int64_t)i * io.nb + ib) * io.rows_pad + r];
+      var[i] = io.gp_outputscale[i] - s + io.gp_noise[i];
+    } else {
+      var[i] = io.var[c * NS + i];
+    }
+    if (split_sums) {
+      const T* src = io.kpart + ((c - io.first) * NS + i) * (1 + D);
+      const int64_t seg_stride = (int64_t)io.rows_pad * NS * (1 + D);
+      T m = T(0);
+      for (int sgi = 0; sgi < io.nseg; ++sgi) m += src[sgi * seg_stride];
+      mu[i] = m;
+#pragma unroll
+      for (int j = 0; j < D; ++j) {
+        T g = T(0);
+        if (!io.point)
+          for (int sgi = 0; sgi < io.nseg; ++sgi) g += src[sgi * seg_stride + 1 + j];
+        jac[i][j] = -g * io.gp_inv_l2[i][j];
+      }
+    } else {
+      mu[i] = io.mean[c * NS + i];
+#pragma unroll
+      for (int j = 0; j < D; ++j) jac[i][j] = io.point ? T(0) : io.jac[(c * NS + i) * D + j];
+    }
+#pragma unroll
+    for (int j = 0; j < NS; ++j) q[i][j] = io.point ? T(0) : io.q_in[(c * NS + i) * NS + j];
   }
 #pragma unroll
   for (int j = 0; j < NU; ++j) u[j] = io.u[c * io.u_stride + j];
-  T q[NS][NS], jac[NS][D];
-#pragma unroll
-  for (int i = 0; i < NS; ++i) {
-#pragma unroll
-    for (int j = 0; j < NS; ++j) q[i][j] = io.point ? T(0) : io.q_in[(c * NS + i) * NS + j];
-#pragma unroll
-    for (int j = 0; j < D; ++j) jac[i][j] = io.point ? T(0) : io.jac[(c * NS + i) * D + j];
-  }
   T p1[NS], q1[NS][NS];
   ellipsoid_step_core<T, NS, NU>(pr, p, q, io.point != 0, u, mu, var, jac, io.flags, p1, q1, sg);
 

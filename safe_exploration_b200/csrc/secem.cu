@@ -877,10 +877,25 @@ static int cem_solve_t(se_cem_s* c, const ProbDev<T>& pr, const T* p0, const T* 
       rio.rec_actions = rec_act, rio.traj = rec_traj, rio.flags = out->flags, rio.N = cand;
       SE_TRY(launch_rollout_small<T>(gp_dev<T>(g), (const T*)g->wt, pr, rio, st));
     } else if (!pipelined) {
-      for (int t = 0; t < T_len; ++t) {
-        SE_TRY(gp_posterior<T>(g, p, ns, actions + (int64_t)t * nu, tnu, cand, mean, var, t == 0 ? nullptr : jac, st));
-        SE_TRY(launch_reach_step<T>(pr, make_io(t, 0), cand, st));
-      }
+      // per horizon step and workspace chunk: kernel rows -> variance GEMM -> ellipsoid step (which also reduces the
+      // GEMM's partial sums, so there is no separate variance launch)
+      const GpDev<T> gd = gp_dev<T>(g);
+      const int64_t rows_chunk = chunk_rows(g, cand);
+      for (int t = 0; t < T_len; ++t)
+        for (int64_t row0 = 0; row0 < cand; row0 += rows_chunk) {
+          const int nrows = (int)((cand - row0) < rows_chunk ? (cand - row0) : rows_chunk);
+          PostPart pp = post_part<T>(g, row0, nrows, 0);
+          SE_TRY(post_kstar<T>(g, gd, pp, p, ns, actions + (int64_t)t * nu, tnu, mean, t == 0 ? nullptr : jac, st));
+          SE_TRY(post_gemm<T>(g, gd, pp, st));
+          StepIO<T> io = make_io(t, row0);
+          io.partial = (const T*)pp.partial, io.nb = pp.nb, io.rows_pad = pp.rows_pad;
+          io.kpart = (const T*)pp.kpart, io.nseg = pp.nseg;
+          for (int o = 0; o < ns; ++o) {
+            io.gp_outputscale[o] = (T)g->outputscale[o], io.gp_noise[o] = (T)g->noise[o];
+            for (int dd = 0; dd < g->d; ++dd) io.gp_inv_l2[o][dd] = (T)g->inv_l2[o][dd];
+          }
+          SE_TRY(launch_reach_step<T>(pr, io, nrows, st));
+        }
     } else {
       // Two-part software pipeline: the population is cut in halves; the main stream runs nothing but the variance
       // GEMMs (tensor pipe) while the side stream prepares the other half (kernel rows: FP64 pipe) and advances the
