@@ -142,6 +142,7 @@ class B200ConstrainedCemMpc:
         self._handle_key = None
         self._comm = None
         self.last_info = {}
+        self._out_cache = {}  # persistent result tensors of solve(reuse_outputs=True)
 
     # ---- handle -------------------------------------------------------------------------------------------------
     def _destroy(self):
@@ -181,11 +182,15 @@ class B200ConstrainedCemMpc:
         self._handle, self._handle_key = handle, key
 
     # ---- solve ----------------------------------------------------------------------------------------------------
-    def solve(self, p0: Tensor, noise: Optional[Tensor] = None, seed: Optional[int] = None, sync: bool = True):
+    def solve(self, p0: Tensor, noise: Optional[Tensor] = None, seed: Optional[int] = None, sync: bool = True,
+              reuse_outputs: bool = False):
         """Run the CEM optimisation for M = p0.shape[0] instances.
 
         :param p0: [M, n_s] initial point states on the device
         :param noise: None (on-device Philox) or [I, M, N, T, n_u] standard-normal noise
+        :param reuse_outputs: write into this object's persistent result tensors (and stage p0 in a persistent
+               buffer) instead of fresh ones: the returned tensors are overwritten by the next such call, and the
+               library sees the same buffers every time, so it replays its captured CUDA graph of the solve
         :returns: dict of device tensors: actions [M, T, n_u], found [M], best_id [M], means / stds [I, M, T, n_u],
                   elite_ids [I, M, E], and per `record`: objective / constraint [I, M, N_local],
                   rollout_actions [I, M, N_local, T, n_u], trajectories [I, M, N_local, T+1, S]
@@ -202,15 +207,26 @@ class B200ConstrainedCemMpc:
         n_local = self._num_rollouts // self.world_size
         S = n_s + n_s * n_s
         new = lambda shape, dtype=dt: torch.empty(shape, dtype=dtype, device=dev)
-        res = dict(actions=new((M, T, n_u)), found=new((M,), torch.int32), best_id=new((M,), torch.int32),
-                   means=new((I, M, T, n_u)), stds=new((I, M, T, n_u)), elite_ids=new((I, M, E), torch.int32),
-                   flags=torch.zeros(4, dtype=torch.int32, device=dev))
-        if self.record in ('full', 'costs'):
-            res['objective'] = new((I, M, n_local))
-            res['constraint'] = new((I, M, n_local))
-        if self.record == 'full':
-            res['rollout_actions'] = new((I, M, n_local, T, n_u))
-            res['trajectories'] = new((I, M, n_local, T + 1, S))
+        cache_key = (M, self.record, dt, str(dev), n_local)
+        cached = self._out_cache.get(cache_key) if reuse_outputs else None
+        if cached is not None:
+            res, p0_buf = cached
+            p0_buf.copy_(p0)
+            p0 = p0_buf
+        else:
+            res = dict(actions=new((M, T, n_u)), found=new((M,), torch.int32), best_id=new((M,), torch.int32),
+                       means=new((I, M, T, n_u)), stds=new((I, M, T, n_u)), elite_ids=new((I, M, E), torch.int32),
+                       flags=torch.zeros(4, dtype=torch.int32, device=dev))
+            if self.record in ('full', 'costs'):
+                res['objective'] = new((I, M, n_local))
+                res['constraint'] = new((I, M, n_local))
+            if self.record == 'full':
+                res['rollout_actions'] = new((I, M, n_local, T, n_u))
+                res['trajectories'] = new((I, M, n_local, T + 1, S))
+            if reuse_outputs:
+                p0_buf = p0.clone()
+                self._out_cache = {cache_key: (res, p0_buf)}  # one live set: a new shape replaces the old buffers
+                p0 = p0_buf
         if noise is not None:
             assert_shape(noise, (I, M, self._num_rollouts, T, n_u))
             noise = ssm._prep(noise, 'noise')
@@ -251,19 +267,20 @@ class B200ConstrainedCemMpc:
         self.last_info = res
         return self._rollouts_of(res)
 
-    def get_actions(self, state: Tensor, noise: Optional[Tensor] = None
+    def get_actions(self, state: Tensor, noise: Optional[Tensor] = None, reuse_outputs: bool = False
                     ) -> Tuple[Union[Tensor, None], List[Rollouts]]:
         """constrained_cem_mpc.py:259-280: (actions [T, n_u] of a feasible rollout of the last iteration | None,
         rollouts by iteration).  `noise` [I, N, T, n_u] fixes the candidates (parity tests)."""
-        res = self.solve(self._flat_state_to_p0(state), None if noise is None else noise.unsqueeze(1))
+        res = self.solve(self._flat_state_to_p0(state), None if noise is None else noise.unsqueeze(1),
+                         reuse_outputs=reuse_outputs)
         self.last_info = res
         actions = res['actions'][0] if int(res['found'][0]) == 1 else None
         return actions, self._rollouts_of(res)
 
-    def get_actions_batch(self, states: Tensor, noise: Optional[Tensor] = None):
+    def get_actions_batch(self, states: Tensor, noise: Optional[Tensor] = None, reuse_outputs: bool = False):
         """M independent MPC problems side by side (BASELINE config "batched independent MPC solves").
         :param states: [M, n_s] point states -> actions [M, T, n_u], found [M] (bool)"""
-        res = self.solve(states, noise)
+        res = self.solve(states, noise, reuse_outputs=reuse_outputs)
         self.last_info = res
         return res['actions'], res['found'].bool()
 

@@ -42,6 +42,7 @@ template <typename T>
 struct ActionSrc {
   int mode;          // 0 = Philox, 1 = external standard-normal noise, 2 = explicit action tensor
   uint64_t seed;
+  const uint64_t* seed_dev;  // when set, the seed is read from device memory (a replayed CUDA graph gets a new one)
   int iteration;
   int n_global;      // rollouts per instance over all ranks
   int tnu;           // T * n_u
@@ -59,7 +60,7 @@ __device__ __forceinline__ T candidate_action(const ActionSrc<T>& s, int inst, i
     z = (double)s.ext[flat];
   } else {
     double z0, z1;
-    philox_normal_pair(s.seed, (uint32_t)s.iteration, (uint32_t)(inst * s.n_global + gid), (uint32_t)(e >> 1), z0, z1);
+    philox_normal_pair(s.seed_dev ? *s.seed_dev : s.seed, (uint32_t)s.iteration, (uint32_t)(inst * s.n_global + gid), (uint32_t)(e >> 1), z0, z1);
     z = (e & 1) ? z1 : z0;
   }
   // actions = means + stds * eps  ==  Normal(means, stds).sample()   (constrained_cem_mpc.py:167)
@@ -383,6 +384,8 @@ __global__ void cem_pack_costs_kernel(const T* __restrict__ objective, const T* 
   if (rec_obj) rec_obj[i] = o;
   if (rec_con) rec_con[i] = c;
 }
+
+static __global__ void cem_set_seed_kernel(uint64_t* dst, uint64_t seed) { *dst = seed; }
 
 static __global__ void cem_init_dist_kernel(double* mean, double* stdv, int count) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;

@@ -52,6 +52,11 @@ int launch_cem_pack_costs(const T* objective, const T* constraint, int64_t count
   return 0;
 }
 
+int launch_cem_set_seed(uint64_t* dst, uint64_t seed, cudaStream_t stream) {
+  SE_LAUNCH(cem_set_seed_kernel, 1, 1, 0, stream, dst, seed);
+  return 0;
+}
+
 int launch_cem_init_dist(double* mean, double* stdv, int count, cudaStream_t stream) {
   SE_LAUNCH(cem_init_dist_kernel, (int)ceil_div(count, 256), 256, 0, stream, mean, stdv, count);
   return 0;

@@ -62,6 +62,7 @@ template <typename T>
 int launch_cem_pack_costs(const T* objective, const T* constraint, int64_t count, T* pack, T* rec_obj, T* rec_con,
                           cudaStream_t stream);
 int launch_cem_init_dist(double* mean, double* stdv, int count, cudaStream_t stream);
+int launch_cem_set_seed(uint64_t* dst, uint64_t seed, cudaStream_t stream);
 
 int measure_peak(int kind, double* flops_out);
 int measure_peak_i8(int sustained, int n_mma, double* ops_out);

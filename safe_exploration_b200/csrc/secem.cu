@@ -697,6 +697,17 @@ extern "C" int se_nccl_comm_destroy(void* comm) {
 // -------------------------------------------------------------------------------------------------------------------
 // CEM
 // -------------------------------------------------------------------------------------------------------------------
+struct GraphKey {
+  const void* ptr[32];
+  int64_t val[8];
+};
+struct GraphEntry {
+  GraphKey key;
+  cudaGraphExec_t exec = nullptr;  // null: buffer set seen once, not captured yet
+  uint64_t kernels = 0;            // kernel launches inside the graph (for se_launch_count)
+  uint64_t stamp = 0;
+};
+
 struct se_cem_s {
   se_gp_s* gp = nullptr;
   se_cem_config cfg{};
@@ -710,6 +721,12 @@ struct se_cem_s {
   double *mean = nullptr, *stdv = nullptr;  // [I + 1][M][T * nu]
   void* act_out = nullptr;                   // scratch outputs when the caller passes NULL
   int32_t *found = nullptr, *best = nullptr;
+  // CUDA-graph replay of the enqueue phase (se_cem_solve)
+  uint64_t* seed_dev = nullptr;
+  cudaStream_t gstream = nullptr;
+  std::vector<GraphEntry> graphs;
+  uint64_t graph_clock = 0;
+  bool graph_failed = false;
 };
 
 extern "C" int se_cem_destroy(se_cem_t c) {
@@ -717,6 +734,10 @@ extern "C" int se_cem_destroy(se_cem_t c) {
   for (void* p : {c->actions, c->p, c->q, c->objective, c->constraint, c->pack_local, c->pack_all, (void*)c->mean,
                   (void*)c->stdv, c->act_out, (void*)c->found, (void*)c->best})
     if (p) cudaFree(p);
+  if (c->seed_dev) cudaFree(c->seed_dev);
+  for (auto& e : c->graphs)
+    if (e.exec) cudaGraphExecDestroy(e.exec);
+  if (c->gstream) cudaStreamDestroy(c->gstream);
   delete c;
   return 0;
 }
@@ -791,7 +812,9 @@ extern "C" int se_cem_set_comm(se_cem_t c, void* nccl_comm, int rank, int world_
 
 template <typename T>
 static int cem_solve_t(se_cem_s* c, const ProbDev<T>& pr, const T* p0, const T* noise, uint64_t seed,
-                       const se_cem_outputs* out, cudaStream_t st) {
+                       const uint64_t* seed_dev, const se_cem_outputs* out, cudaStream_t st, int phase) {
+  // phase bit 0: prepare (allocations, digit image, L^-T -- everything that may allocate or synchronise);
+  // phase bit 1: enqueue the solve on `st` (pure stream work: this part is what se_cem_solve captures into a graph)
   se_gp_s* g = c->gp;
   const se_cem_config& cf = c->cfg;
   const int M = cf.num_instances, Nl = cf.local_rollouts, Ng = cf.num_rollouts, T_len = cf.time_horizon;
@@ -811,9 +834,6 @@ static int cem_solve_t(se_cem_s* c, const ProbDev<T>& pr, const T* p0, const T* 
   T* jac = (T*)g->post_jac;
   const size_t dist = (size_t)M * tnu;
 
-  if (out->flags) SE_CUDA(cudaMemsetAsync(out->flags, 0, 4 * sizeof(int32_t), st));
-  SE_TRY(launch_cem_init_dist(c->mean, c->stdv, (int)dist, st));
-
   // pipeline the population in two halves when it is large enough and fits the workspace in one piece
   // (off by default: on the 1 kW B200 both the int8 GEMM and the FP64 kernel-row kernel run into the power cap, so
   // overlapping them does not shorten the solve -- measured 132 ms pipelined vs 124 ms sequential at C2)
@@ -824,21 +844,29 @@ static int cem_solve_t(se_cem_s* c, const ProbDev<T>& pr, const T* p0, const T* 
   // Models of at most 128 training points: the fused rollout kernel (SE_ROLLOUT_FUSED=0 keeps the four-kernel step).
   const int fused_env = getenv("SE_ROLLOUT_FUSED") ? atoi(getenv("SE_ROLLOUT_FUSED")) : 1;
   const bool fused = fused_env != 0 && g->n_pad == kSmallN && !g->timing && !g->impl_explicit;
-  if (fused && !g->wt) {
-    SE_CUDA(cudaMalloc(&g->wt, (size_t)ns * g->n_pad * g->n_pad * g->esz));
-    SE_TRY(launch_transpose_w<T>((const T*)g->w, g->n_pad, ns, (T*)g->wt, st));
+  if (phase & 1) {
+    if (fused && !g->wt) {
+      SE_CUDA(cudaMalloc(&g->wt, (size_t)ns * g->n_pad * g->n_pad * g->esz));
+      SE_TRY(launch_transpose_w<T>((const T*)g->w, g->n_pad, ns, (T*)g->wt, st));
+    }
+    if (!fused) SE_TRY(gp_reserve(g, pipelined ? two_part_rows : cand));
+    if (!fused && g->impl == SE_GEMM_TC) SE_TRY(tc_prepare(g, st));
+    if (pipelined && !g->side) {
+      SE_CUDA(cudaStreamCreateWithFlags(&g->side, cudaStreamNonBlocking));
+      for (cudaEvent_t* e : {&g->ev_fork, &g->ev_join, &g->ev_k[0], &g->ev_k[1], &g->ev_g[0], &g->ev_g[1]})
+        SE_CUDA(cudaEventCreateWithFlags(e, cudaEventDisableTiming));
+    }
   }
-  if (!fused) SE_TRY(gp_reserve(g, pipelined ? two_part_rows : cand));
-  if (g->impl == SE_GEMM_TC) SE_TRY(tc_prepare(g, st));
-  if (pipelined && !g->side) {
-    SE_CUDA(cudaStreamCreateWithFlags(&g->side, cudaStreamNonBlocking));
-    for (cudaEvent_t* e : {&g->ev_fork, &g->ev_join, &g->ev_k[0], &g->ev_k[1], &g->ev_g[0], &g->ev_g[1]})
-      SE_CUDA(cudaEventCreateWithFlags(e, cudaEventDisableTiming));
-  }
+  if (!(phase & 2)) return 0;
+  // the posterior buffers may have been re-allocated by the prepare phase
+  mean = (T*)g->post_mean, var = (T*)g->post_var, jac = (T*)g->post_jac;
+
+  if (out->flags) SE_CUDA(cudaMemsetAsync(out->flags, 0, 4 * sizeof(int32_t), st));
+  SE_TRY(launch_cem_init_dist(c->mean, c->stdv, (int)dist, st));
 
   ActionSrc<T> src;
   memset(&src, 0, sizeof(src));
-  src.seed = seed, src.n_global = Ng, src.tnu = tnu;
+  src.seed = seed, src.seed_dev = seed_dev, src.n_global = Ng, src.tnu = tnu;
   CostView<T> costs{pack_all, M, Nl};
 
   for (int it = 0; it < cf.num_iterations; ++it) {
@@ -949,13 +977,104 @@ static int cem_solve_t(se_cem_s* c, const ProbDev<T>& pr, const T* p0, const T* 
   return 0;
 }
 
+static int cem_solve_phase(se_cem_s* c, const void* dev_p0, const void* dev_noise, uint64_t seed,
+                           const uint64_t* seed_dev, const se_cem_outputs* out, cudaStream_t st, int phase) {
+  if (c->gp->dtype == SE_F64)
+    return cem_solve_t<double>(c, c->pd, (const double*)dev_p0, (const double*)dev_noise, seed, seed_dev, out, st, phase);
+  return cem_solve_t<float>(c, c->pf, (const float*)dev_p0, (const float*)dev_noise, seed, seed_dev, out, st, phase);
+}
+
+// Everything a captured solve bakes in: caller pointers and the library buffers its kernels were given.
+static GraphKey graph_key(const se_cem_s* c, const void* p0, const void* noise, const se_cem_outputs* out) {
+  GraphKey k;
+  memset(&k, 0, sizeof(k));
+  const se_gp_s* g = c->gp;
+  const void* ptrs[] = {p0, noise, out->actions, out->found, out->best_id, out->means, out->stds, out->elite_ids,
+                        out->objective, out->constraint, out->rollout_actions, out->trajectories, out->flags,
+                        g->xt, g->alpha, g->w, g->kst, g->partial, g->kpart, g->post_mean, g->post_var, g->post_jac,
+                        g->b_img, g->exp_ab, g->scale_b, g->wt};
+  static_assert(sizeof(ptrs) / sizeof(ptrs[0]) <= sizeof(k.ptr) / sizeof(k.ptr[0]), "GraphKey too small");
+  for (size_t i = 0; i < sizeof(ptrs) / sizeof(ptrs[0]); ++i) k.ptr[i] = ptrs[i];
+  k.val[0] = (int64_t)g->impl, k.val[1] = g->tc_digits, k.val[2] = (int64_t)g->ws_limit, k.val[3] = g->impl_explicit;
+  k.val[4] = getenv("SE_ROLLOUT_FUSED") ? atoi(getenv("SE_ROLLOUT_FUSED")) : 1;
+  k.val[5] = g->n_pad;
+  return k;
+}
+
+static void graph_cache_clear(se_cem_s* c) {
+  for (auto& e : c->graphs)
+    if (e.exec) cudaGraphExecDestroy(e.exec);
+  c->graphs.clear();
+}
+
+// One MPC solve.  Small and mid-size solves are bounded by launch gaps (tools/graph_probe.py), so the enqueue phase is
+// captured into a CUDA graph the second time the same buffers come back and replayed from then on; the candidate seed
+// lives in device memory so that a replay draws new candidates.  SE_CEM_GRAPH=0 disables it.
 extern "C" int se_cem_solve(se_cem_t c, const void* dev_p0, const void* dev_noise, uint64_t seed,
                             const se_cem_outputs* out, void* stream) {
   SE_REQUIRE(c && dev_p0 && out, "se_cem_solve: NULL argument");
   cudaStream_t st = static_cast<cudaStream_t>(stream);
-  if (c->gp->dtype == SE_F64)
-    return cem_solve_t<double>(c, c->pd, (const double*)dev_p0, (const double*)dev_noise, seed, out, st);
-  return cem_solve_t<float>(c, c->pf, (const float*)dev_p0, (const float*)dev_noise, seed, out, st);
+  const int graph_env = getenv("SE_CEM_GRAPH") ? atoi(getenv("SE_CEM_GRAPH")) : 1;
+  const int pipe_env = getenv("SE_PIPELINE") ? atoi(getenv("SE_PIPELINE")) : 0;
+  const bool eligible = graph_env != 0 && !c->graph_failed && c->world == 1 && !c->gp->timing && pipe_env == 0;
+  if (!eligible) return cem_solve_phase(c, dev_p0, dev_noise, seed, nullptr, out, st, 3);
+
+  SE_TRY(cem_solve_phase(c, dev_p0, dev_noise, seed, nullptr, out, st, 1));  // may allocate / synchronise
+  if (!c->seed_dev) SE_CUDA(cudaMalloc(&c->seed_dev, sizeof(uint64_t)));
+  SE_TRY(launch_cem_set_seed(c->seed_dev, seed, st));
+  const GraphKey key = graph_key(c, dev_p0, dev_noise, out);
+  for (auto& e : c->graphs)
+    if (e.exec && memcmp(&e.key, &key, sizeof(key)) == 0) {
+      SE_CUDA(cudaGraphLaunch(e.exec, st));
+      g_launches.fetch_add(e.kernels, std::memory_order_relaxed);
+      e.stamp = ++c->graph_clock;
+      return 0;
+    }
+  // not captured yet: the first sighting of a buffer set runs eagerly, the second is captured
+  bool seen = false;
+  for (auto& e : c->graphs)
+    if (!e.exec && memcmp(&e.key, &key, sizeof(key)) == 0) seen = true;
+  if (!seen) {
+    if (c->graphs.size() >= 8) {  // drop the least recently used entry
+      size_t lru = 0;
+      for (size_t i = 1; i < c->graphs.size(); ++i)
+        if (c->graphs[i].stamp < c->graphs[lru].stamp) lru = i;
+      if (c->graphs[lru].exec) cudaGraphExecDestroy(c->graphs[lru].exec);
+      c->graphs.erase(c->graphs.begin() + lru);
+    }
+    GraphEntry e;
+    e.key = key, e.stamp = ++c->graph_clock;
+    c->graphs.push_back(e);
+    return cem_solve_phase(c, dev_p0, dev_noise, seed, c->seed_dev, out, st, 2);
+  }
+  if (!c->gstream) SE_CUDA(cudaStreamCreateWithFlags(&c->gstream, cudaStreamNonBlocking));
+  cudaGraph_t graph = nullptr;
+  const uint64_t launches_before = g_launches.load();
+  cudaError_t ce = cudaStreamBeginCapture(c->gstream, cudaStreamCaptureModeRelaxed);
+  int rc = -1;
+  if (ce == cudaSuccess) {
+    rc = cem_solve_phase(c, dev_p0, dev_noise, seed, c->seed_dev, out, c->gstream, 2);
+    ce = cudaStreamEndCapture(c->gstream, &graph);
+  }
+  const uint64_t kernels = g_launches.load() - launches_before;
+  cudaGraphExec_t exec = nullptr;
+  if (ce == cudaSuccess && rc == 0 && graph) ce = cudaGraphInstantiate(&exec, graph, 0);
+  if (graph) cudaGraphDestroy(graph);
+  if (ce != cudaSuccess || rc != 0 || !exec) {
+    // capture is an optimisation: fall back to plain launches for the rest of this handle's life
+    cudaGetLastError();
+    c->graph_failed = true;
+    graph_cache_clear(c);
+    g_launches.store(launches_before);
+    return cem_solve_phase(c, dev_p0, dev_noise, seed, nullptr, out, st, 2);
+  }
+  for (auto& e : c->graphs)
+    if (!e.exec && memcmp(&e.key, &key, sizeof(key)) == 0) {
+      e.exec = exec, e.kernels = kernels, e.stamp = ++c->graph_clock;
+      break;
+    }
+  SE_CUDA(cudaGraphLaunch(exec, st));
+  return 0;
 }
 
 extern "C" int se_cem_noise(se_dtype dtype, uint64_t seed, int iteration, int num_instances, int num_rollouts_global,

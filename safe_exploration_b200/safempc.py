@@ -311,7 +311,8 @@ class B200CemSafeMPC(SafeMPC):
         """safempc_cem.py:231-263."""
         assert_shape(state, (self._state_dimen,))
         state_batch = torch.tensor(state, dtype=self._ssm.dtype, device=self._ssm.device).unsqueeze(0)
-        mpc_actions, _ = self._mpc.get_actions(self._pq_flattener.flatten(state_batch, None))
+        # results are consumed right here, so the solver may reuse its buffers (-> the library replays its CUDA graph)
+        mpc_actions, _ = self._mpc.get_actions(self._pq_flattener.flatten(state_batch, None), reuse_outputs=True)
         mpc_actions = mpc_actions.detach().cpu().numpy() if mpc_actions is not None else mpc_actions
         if mpc_actions is not None:
             self._say('Found solution')
@@ -346,7 +347,7 @@ class B200CemSafeMPC(SafeMPC):
             self._batch_plans = [np.empty((0, self.action_dimen)) for _ in range(m)]
             self._batch_executed = [0] * m
         dev_states = torch.as_tensor(states, dtype=self._ssm.dtype, device=self._ssm.device)
-        plans, found = self._mpc.get_actions_batch(dev_states)
+        plans, found = self._mpc.get_actions_batch(dev_states, reuse_outputs=True)
         plans, found = plans.detach().cpu().numpy(), found.cpu().numpy()
         actions = np.empty((m, self.action_dimen))
         results = []

@@ -604,3 +604,30 @@ def test_fused_small_model_rollout_equals_the_four_kernel_step(which, dtype, mon
     assert rel_err(a['trajectories'][0].cpu(), b['trajectories'][0].cpu(), 1e-3 * scale) < tol
     assert rel_err(a['objective'][0].cpu(), b['objective'][0].cpu()) < tol
     assert torch.equal(a['flags'], b['flags'])
+
+
+@pytest.mark.parametrize('n_train', [100, 300])
+def test_cuda_graph_replay_equals_plain_launches(n_train, monkeypatch):
+    """se_cem_solve captures its enqueue phase into a CUDA graph the second time it sees the same buffers and replays
+    it afterwards, with the candidate seed read from device memory: every replay must equal the plain-launch solve
+    with that seed (both the fused small-model path and the tcgen05 path), bit for bit."""
+    w = workloads.pendulum_workload(n_train=n_train, num_rollouts=256, time_horizon=4, num_elites=8, num_iterations=3)
+    p0 = G(w.p0).unsqueeze(0)
+    monkeypatch.setenv('SE_CEM_GRAPH', '0')
+    ssm, mpc = workloads.build_solver(w, record='costs', seed=0)
+    plain = {sd: {k: v.clone() for k, v in mpc.solve(p0, seed=sd).items()} for sd in (5, 6, 7, 8)}
+    monkeypatch.setenv('SE_CEM_GRAPH', '1')
+    ssm2, mpc2 = workloads.build_solver(w, record='costs', seed=0)
+    lib = _lib.load()
+    counts = []
+    for sd in (5, 6, 7, 8):  # same persistent buffers every call: eager, capture + launch, replay, replay
+        lib.se_launch_count_reset()
+        res = mpc2.solve(p0, seed=sd, reuse_outputs=True)
+        torch.cuda.synchronize()
+        counts.append(int(lib.se_launch_count()))
+        for k, v in plain[sd].items():
+            assert torch.equal(res[k], v), (sd, k)
+    # replays are counted like the launches they stand for (the first call may add one-off model preparation)
+    assert len(set(counts[1:])) == 1 and counts[1] > 0 and counts[0] >= counts[1]
+    # different seeds really produce different candidates
+    assert not torch.equal(plain[5]['objective'], plain[6]['objective'])
