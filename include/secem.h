@@ -92,6 +92,34 @@ int se_gp_predict(se_gp_t gp, const void* dev_z, int64_t N, void* dev_mean, void
                   void* stream);
 
 /* ---------------------------------------------------------------------------------------------------------------
+ * Model refresh: what happens between episodes in CemSafeMPC.update_model
+ * (safe_exploration/safempc_cem.py:314-327) -> CemSSM.update_model (ssm_cem.py:72-99) -> GpCemSSM._update_model /
+ * _train_model (gp_ssm_cem.py:96-129).  In the reference the arithmetic is GPyTorch's; here the covariance assembly and
+ * the marginal-log-likelihood gradient are kernels of this library, the Cholesky factorisation / inverse between them
+ * are cuSOLVER / cuBLAS calls made by the Python host through torch.linalg.  float64 only.
+ * ------------------------------------------------------------------------------------------------------------- */
+
+/* dev_k [n_s, n, n] = outputscale_o exp(-1/2 sum_c ((x_ic - x_jc) / lengthscale_oc)^2) + noise_o [i == j]: the
+ * covariance of ScaleKernel(RBFKernel(ard_num_dims=d, batch_size=n_s)) plus the GaussianLikelihood noise
+ * (gp_ssm_cem.py:33, 45-57) on the training inputs dev_x [n, d], for all n_s outputs in one launch. */
+int se_gp_kernel_matrix(int n_s, int d, int64_t n, const double* dev_x, const double* host_lengthscale,
+                        const double* host_outputscale, const double* host_noise, double* dev_k, void* stream);
+
+/* Gradient of the exact marginal log likelihood MLL_o = -1/2 y_o^T alpha_o - sum_i log L_o,ii - n/2 log 2 pi of each
+ * output's GP with respect to its MATERIALISED hyper-parameters:
+ *   dev_grad [n_s, d + 2] = d MLL_o / d (lengthscale_o1 .. lengthscale_od, outputscale_o, noise_o)
+ *                         = 1/2 sum_ij (alpha alpha^T - (K_o + noise_o I)^-1)_ij  d K_o,ij / d theta
+ * -- what loss.backward() computes in GpCemSSM._train_model (gp_ssm_cem.py:116-121) up to the chain rule through
+ * GPyTorch's softplus parametrisation and ExactMarginalLogLikelihood's 1/n, which the host applies.
+ *   dev_alpha [n_s, n], dev_kinv [n_s, n, n] (symmetric; only the lower triangle is read)
+ *   dev_workspace: se_gp_mll_grad_workspace(n_s, d, n) bytes of per-tile partial sums (reduced in a fixed order:
+ *   the result is deterministic). */
+int64_t se_gp_mll_grad_workspace(int n_s, int d, int64_t n);
+int se_gp_mll_grad(int n_s, int d, int64_t n, const double* dev_x, const double* dev_alpha, const double* dev_kinv,
+                   const double* host_lengthscale, const double* host_outputscale, const double* host_noise,
+                   double* dev_workspace, double* dev_grad, void* stream);
+
+/* ---------------------------------------------------------------------------------------------------------------
  * Problem constants: what CemSafeMPC._dynamics_func and construct_constraints close over
  * (safe_exploration/safempc_cem.py:135-146, 162-200, 288-312).  All host pointers, double.
  * ------------------------------------------------------------------------------------------------------------- */
