@@ -138,6 +138,52 @@ class OracleGpCemSSM:
         return {}
 
 
+def exact_mll(x: Tensor, y: Tensor, lengthscale: Tensor, outputscale: Tensor, noise: Tensor) -> Tensor:
+    """[n_s] exact marginal log likelihoods  -1/2 y^T (K + noise I)^-1 y - 1/2 log|K + noise I| - n/2 log 2 pi  of the n_s
+    independent GPs (what gpytorch's ExactMarginalLogLikelihood evaluates before it divides by n; call site
+    gp_ssm_cem.py:110, 120).  PARITY UNPINNED like the posterior: the arithmetic is gpytorch's, restated from the textbook.
+    :param x: [n, d], y: [n, n_s]"""
+    n = x.size(0)
+    k = rbf_ard(x, x, lengthscale, outputscale) + torch.diag_embed(noise.view(-1, 1).expand(-1, n))
+    chol = torch.linalg.cholesky(k)
+    yt = y.t()
+    alpha = torch.cholesky_solve(yt.unsqueeze(-1), chol).squeeze(-1)
+    return -0.5 * (yt * alpha).sum(-1) - chol.diagonal(dim1=1, dim2=2).log().sum(-1) - 0.5 * n * np.log(2 * np.pi)
+
+
+def exact_mll_and_grad(x, y, lengthscale, outputscale, noise) -> Tuple[Tensor, Tensor]:
+    """mll [n_s] and d mll_o / d (lengthscale_o[0..d), outputscale_o, noise_o) as [n_s, d + 2], by autograd through the
+    Cholesky factorisation -- the route loss.backward() takes in gp_ssm_cem.py:121."""
+    x, y = torch.as_tensor(x, dtype=F64), torch.as_tensor(y, dtype=F64)
+    ls = torch.as_tensor(lengthscale, dtype=F64).clone().requires_grad_(True)
+    os_ = torch.as_tensor(outputscale, dtype=F64).clone().requires_grad_(True)
+    nz = torch.as_tensor(noise, dtype=F64).clone().requires_grad_(True)
+    mll = exact_mll(x, y, ls, os_, nz)
+    mll.sum().backward()  # outputs are independent: the gradient of the sum is the per-output gradient
+    return mll.detach(), torch.cat((ls.grad, os_.grad.unsqueeze(1), nz.grad.unsqueeze(1)), dim=1)
+
+
+def train_hyperparameters(x, y, lengthscale, outputscale, noise, iterations: int, lr: float = 0.01):
+    """GpCemSSM._train_model (gp_ssm_cem.py:103-129): Adam(lr=0.01) for `iterations` steps on
+    loss = -sum_o mll_o / n, raw parameters through softplus (gpytorch's default positive constraint in 0.3.x).
+    :returns: (lengthscale [n_s, d], outputscale [n_s], noise [n_s], losses list)"""
+    x, y = torch.as_tensor(x, dtype=F64), torch.as_tensor(y, dtype=F64)
+    inv_softplus = lambda v: torch.log(torch.expm1(torch.as_tensor(v, dtype=F64)))
+    raw = [inv_softplus(t).clone().requires_grad_(True) for t in (lengthscale, outputscale, noise)]
+    opt = torch.optim.Adam(raw, lr=lr)
+    losses = []
+    for _ in range(iterations):
+        opt.zero_grad()
+        ls, os_, nz = (torch.nn.functional.softplus(r) for r in raw)
+        loss = -(exact_mll(x, y, ls, os_, nz) / x.size(0)).sum()
+        loss.backward()
+        losses.append(loss.item())
+        opt.step()
+    with torch.no_grad():
+        ls, os_, nz = (torch.nn.functional.softplus(r).clone() for r in raw)
+    return ls, os_, nz, losses
+
+
 # ----------------------------------------------------------------------------------------------------------
 # Ellipsoid algebra (a14-a20)
 # ----------------------------------------------------------------------------------------------------------

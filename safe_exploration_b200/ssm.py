@@ -194,9 +194,7 @@ class B200GpCemSSM(CemSSM):
         linv = self._append_rows(x, hyp) if self._incremental else None
         self.last_update = 'full' if linv is None else 'incremental'
         if linv is None:
-            ls = self.lengthscale.to(self.device)
-            k = _rbf_ard(x, x, ls, self.outputscale.to(self.device))
-            k.diagonal(dim1=1, dim2=2).add_(self.noise.to(self.device).view(-1, 1))
+            k = self.kernel_matrix(x)
             chol = torch.linalg.cholesky(k)
             del k
             eye = torch.eye(n, dtype=torch.float64, device=self.device).expand(self.num_states, -1, -1)
@@ -263,31 +261,83 @@ class B200GpCemSSM(CemSSM):
         linv[:, n_old:, n_old:] = c_inv
         return linv
 
+    # ---- model refresh kernels (SURVEY.md 8f ranks 1 and 2) -----------------------------------------------------
+    def _hyp_ptrs(self, ls: Tensor, os_: Tensor, nz: Tensor):
+        keep = [_lib.host_doubles(t.detach().cpu().numpy()) for t in (ls, os_, nz)]
+        return keep, [k[1] for k in keep]
+
+    def kernel_matrix(self, x: Tensor, lengthscale=None, outputscale=None, noise=None) -> Tensor:
+        """[n_s, n, n] float64 covariance K_o + noise_o I of the training inputs (`se_gp_kernel_matrix`): what GPyTorch
+        builds from ScaleKernel(RBFKernel(ard)) + GaussianLikelihood (gp_ssm_cem.py:33, 45-57)."""
+        _lib.require_cuda(x, 'x')
+        x = x.detach().to(torch.float64).contiguous()
+        n, d = x.shape
+        ls, os_, nz = (self.lengthscale if lengthscale is None else lengthscale,
+                       self.outputscale if outputscale is None else outputscale,
+                       self.noise if noise is None else noise)
+        keep, (p_ls, p_os, p_nz) = self._hyp_ptrs(ls, os_, nz)
+        k = torch.empty((self.num_states, n, n), dtype=torch.float64, device=x.device)
+        with torch.cuda.device(x.device):
+            _lib.check(self._lib.se_gp_kernel_matrix(self.num_states, d, n, _lib.ptr(x), p_ls, p_os, p_nz, _lib.ptr(k),
+                                                     _lib.stream_ptr(x.device)))
+        return k
+
+    def mll_and_grad(self, x: Tensor, y: Tensor, lengthscale=None, outputscale=None, noise=None):
+        """Exact marginal log likelihood of each output's GP and its gradient w.r.t. the materialised hyper-parameters.
+
+        :param x: [n, d] training inputs (CUDA), :param y: [n, n_s] training targets
+        :returns: mll [n_s] (not divided by n), grad [n_s, d + 2] = d mll_o / d (lengthscale_o[0..d), outputscale_o,
+                  noise_o), alpha [n_s, n].  Covariance assembly and gradient are kernels of libsecem.so
+                  (`se_gp_kernel_matrix`, `se_gp_mll_grad`); the Cholesky factorisation and inverse in between are
+                  cuSOLVER calls through torch.linalg."""
+        _lib.require_cuda(x, 'x')
+        x = x.detach().to(torch.float64).contiguous()
+        yt = y.detach().to(device=x.device, dtype=torch.float64).t().contiguous()
+        n, d = x.shape
+        ls, os_, nz = (self.lengthscale if lengthscale is None else lengthscale,
+                       self.outputscale if outputscale is None else outputscale,
+                       self.noise if noise is None else noise)
+        keep, (p_ls, p_os, p_nz) = self._hyp_ptrs(ls, os_, nz)
+        k = self.kernel_matrix(x, ls, os_, nz)
+        chol = torch.linalg.cholesky(k)
+        del k
+        alpha = torch.cholesky_solve(yt.unsqueeze(-1), chol).squeeze(-1).contiguous()
+        mll = -0.5 * (yt * alpha).sum(-1) - chol.diagonal(dim1=1, dim2=2).log().sum(-1) - 0.5 * n * math.log(2 * math.pi)
+        kinv = torch.cholesky_inverse(chol)
+        del chol
+        if not kinv.is_contiguous():  # cuSOLVER's column-major result: K^-1 is symmetric, so its transpose view serves
+            kinv = kinv.transpose(1, 2) if kinv.transpose(1, 2).is_contiguous() else kinv.contiguous()
+        ws = torch.empty(max(1, self._lib.se_gp_mll_grad_workspace(self.num_states, d, n) // 8), dtype=torch.float64,
+                         device=x.device)
+        grad = torch.empty((self.num_states, d + 2), dtype=torch.float64, device=x.device)
+        with torch.cuda.device(x.device):
+            _lib.check(self._lib.se_gp_mll_grad(self.num_states, d, n, _lib.ptr(x), _lib.ptr(alpha), _lib.ptr(kinv),
+                                                p_ls, p_os, p_nz, _lib.ptr(ws), _lib.ptr(grad),
+                                                _lib.stream_ptr(x.device)))
+        return mll, grad, alpha
+
     def _train_model(self, x_train: Tensor, y_train: Tensor) -> None:
-        """gp_ssm_cem.py:103-129: Adam(lr=0.01) on the exact marginal log likelihood, softplus-parametrised like
-        GPyTorch.  Host-side torch autograd (not part of the accelerated path yet)."""
-        x = x_train.detach().to(device=self.device, dtype=torch.float64)
-        y = y_train.detach().to(device=self.device, dtype=torch.float64).t()
+        """gp_ssm_cem.py:103-129: Adam(lr=0.01) on loss = -sum_o MLL_o / n (GPyTorch's ExactMarginalLogLikelihood
+        divides by the number of data points), raw parameters mapped through softplus like GPyTorch's.  The gradient
+        comes from `mll_and_grad` (analytic, one pass over K^-1) instead of autograd through the factorisation; the
+        chain rule through softplus and torch.optim.Adam's update on the n_s (d + 2) raw scalars stay in torch."""
+        x = x_train.detach().to(device=self.device, dtype=torch.float64).contiguous()
+        y = y_train.detach().to(device=self.device, dtype=torch.float64)
+        n, d = x.shape
         inv_softplus = lambda v: torch.log(torch.expm1(v))
-        raw = [inv_softplus(t.to(self.device)).requires_grad_(True)
-               for t in (self.lengthscale, self.outputscale, self.noise)]
-        opt = torch.optim.Adam(raw, lr=0.01)
-        n = x.size(0)
+        raw = torch.cat((inv_softplus(self.lengthscale), inv_softplus(self.outputscale).unsqueeze(1),
+                         inv_softplus(self.noise).unsqueeze(1)), dim=1).to(self.device).requires_grad_(True)
+        opt = torch.optim.Adam([raw], lr=0.01)
         losses = []
         for _ in range(self._training_iterations):
-            opt.zero_grad()
-            ls, os_, nz = (torch.nn.functional.softplus(r) for r in raw)
-            k = _rbf_ard(x, x, ls, os_) + torch.diag_embed(nz.view(-1, 1).expand(-1, n))
-            chol = torch.linalg.cholesky(k)
-            a = torch.cholesky_solve(y.unsqueeze(-1), chol).squeeze(-1)
-            mll = -0.5 * (y * a).sum(-1) - chol.diagonal(dim1=1, dim2=2).log().sum(-1) - 0.5 * n * math.log(2 * math.pi)
-            loss = -(mll / n).sum()  # GPyTorch's ExactMarginalLogLikelihood divides by the number of data points
-            loss.backward()
-            losses.append(loss.item())
+            host = torch.nn.functional.softplus(raw.detach()).cpu()
+            mll, grad, _ = self.mll_and_grad(x, y, host[:, :d], host[:, d], host[:, d + 1])
+            raw.grad = -(grad * torch.sigmoid(raw.detach())) / n
+            losses.append(-(mll / n).sum())
             opt.step()
-        self._last_training_losses = losses
-        with torch.no_grad():
-            self.lengthscale, self.outputscale, self.noise = (torch.nn.functional.softplus(r).cpu() for r in raw)
+        self._last_training_losses = torch.stack(losses).cpu().tolist() if losses else []
+        host = torch.nn.functional.softplus(raw.detach()).cpu()
+        self.lengthscale, self.outputscale, self.noise = host[:, :d].clone(), host[:, d].clone(), host[:, d + 1].clone()
         self._update_model(x_train, y_train)
 
     def _prep(self, t: Tensor, name: str) -> Tensor:

@@ -137,3 +137,27 @@ def test_philox_known_answers():
     assert f([0xffffffff] * 4, [0xffffffff] * 2) == [0x408f276d, 0x41c83b0e, 0xa20bc7c6, 0x6d5451fd]
     assert f([0x243f6a88, 0x85a308d3, 0x13198a2e, 0x03707344], [0xa4093822, 0x299f31d0]) == \
         [0xd16cfe09, 0x94fdcceb, 0x5001e420, 0x24126ea1]
+
+
+def test_oracle_mll_gradient_against_finite_differences():
+    """The oracle's marginal-likelihood gradient (autograd through the Cholesky factorisation, the route the
+    reference's loss.backward() takes, gp_ssm_cem.py:121) agrees with central differences; its Adam loop lowers the
+    loss.  (The RBF-ARD arithmetic itself is gpytorch's: parity unpinned, see oracle.py.)"""
+    g = torch.Generator().manual_seed(0)
+    x = torch.rand((40, 3), generator=g, dtype=torch.float64) * 2 - 1
+    y = torch.stack((torch.sin(2 * x[:, 0]), 0.3 * x[:, 1] * x[:, 2]), dim=1) + 0.05 * torch.randn((40, 2), generator=g, dtype=torch.float64)
+    ls = torch.full((2, 3), 0.7, dtype=torch.float64)
+    os_ = torch.tensor([0.5, 0.2], dtype=torch.float64)
+    nz = torch.tensor([0.01, 0.02], dtype=torch.float64)
+    mll, grad = oracle.exact_mll_and_grad(x, y, ls, os_, nz)
+    theta = torch.cat((ls, os_.unsqueeze(1), nz.unsqueeze(1)), dim=1)
+    for o in range(2):
+        for c in range(5):
+            e = torch.zeros_like(theta)
+            e[o, c] = 1e-6
+            hi, lo = theta + e, theta - e
+            fd = (oracle.exact_mll(x, y, hi[:, :3], hi[:, 3], hi[:, 4])[o] -
+                  oracle.exact_mll(x, y, lo[:, :3], lo[:, 3], lo[:, 4])[o]) / 2e-6
+            assert abs(fd - grad[o, c]) <= 1e-6 * max(1.0, abs(grad[o, c]))
+    _, _, _, losses = oracle.train_hyperparameters(x, y, ls, os_, nz, 30)
+    assert losses[-1] < losses[0]
