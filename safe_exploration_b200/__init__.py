@@ -8,6 +8,7 @@ Drop-in for the hot path of oscarkey/safe-exploration behind the reference's own
     gp_reachability_pytorch.onestep_reachability ...     reachability.onestep_reachability ...
     constrained_cem_mpc.ConstrainedCemMpc                cem.B200ConstrainedCemMpc
     safempc_cem.CemSafeMPC (SafeMPC)                     safempc.B200CemSafeMPC
+    utils_config.create_solver (safempc_cem branch)      utils_config.create_solver
 
 All numerics run in libsecem.so (csrc/, C ABI in include/secem.h); there is no CPU fallback.
 """
@@ -20,5 +21,6 @@ from .safempc import (B200CemSafeMPC, B200SafeDynamics, EllipsoidObstacleConstra
                       EllipsoidTerminalConstraint,
                       LqrFeedbackController, MpcResult, PQFlattener, SafeMPC, construct_constraints, dlqr)
 from .ssm import B200GpCemSSM, CemSSM, assert_shape
+from .utils_config import create_cem_ssm, create_solver
 
 __version__ = '0.1.0'

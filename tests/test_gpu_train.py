@@ -116,3 +116,40 @@ def test_pendulum_workload_gradient_at_full_size():
     fd = (f(theta * torch.exp(eps * direction)) - f(theta * torch.exp(-eps * direction))) / (2 * eps)
     an = (grad.cpu() * theta * direction).sum(1)
     assert float(((fd - an).abs() / an.abs()).max()) < 1e-5
+
+
+def test_create_solver_end_to_end_matches_oracle(golden_cem):
+    """The config-selected path (utils_config.py:58-135, cem_ssm = 'exact_gp_b200'): update_model with the prior
+    subtracted (safempc_cem.py:314-327), one get_action, and the same solve restated by the oracle on the candidates
+    the device drew (Philox stream of seed 0): identical constraint decisions, elites and returned plan."""
+    from test_host_cabi import _CemConf, _PendulumEnv
+    g = golden_cem
+
+    class Conf(_CemConf):
+        mpc_time_horizon, cem_num_rollouts, cem_num_elites, cem_num_iterations = 4, 128, 12, 3
+        cem_record = 'full'
+    solver, safe_policy = se.create_solver(Conf(), _PendulumEnv(), lengthscale=g['lengthscale'],
+                                           outputscale=g['outputscale'], noise=g['noise_var'], device=DEV)
+    a, b = solver.lin_model
+    x, y_res = g['x_train'], g['y_train']
+    solver.update_model(x, y_res + x[:, :2] @ np.asarray(a).T + x[:, 2:] @ np.asarray(b).T, replace_old=True)
+    action, result = solver.get_action(g['p0'])
+    info = solver._mpc.last_info
+
+    noise = np.stack([oracle.philox_normal_noise(0, i, 0, 128, 4, 1) for i in range(3)])
+    ogp = oracle.OracleGpCemSSM(2, 1, g['lengthscale'], g['outputscale'], g['noise_var'])
+    ogp.update_model(T(x), T(y_res), replace_old=True)
+    env = _PendulumEnv()
+    h, v = env.get_safety_constraints()[:2]
+    k, _, _ = se.dlqr(a, b, Conf.lqr_wx_cost, Conf.lqr_wu_cost)
+    prob = oracle.SafeCemProblem(ogp, env.l_mu, env.l_sigm, -k, a, b, 2.0, h, v[:, 0], g['act_a'], g['act_b'])
+    ref = oracle.cem_solve(prob, T(g['p0']), T(noise), 12)
+    assert np.array_equal(info['elite_ids'][:, 0].cpu().numpy(), ref['elite_ids'].numpy())
+    for i, r in enumerate(ref['rollouts']):
+        assert np.array_equal(info['constraint'][i, 0].cpu().numpy(), r.constraint_costs.numpy())
+        assert np.allclose(info['objective'][i, 0].cpu().numpy(), r.objective_costs.numpy(), rtol=1e-8, atol=0)
+    if ref['best_id'] >= 0:
+        assert result == se.MpcResult.FOUND_SOLUTION
+        assert np.allclose(action, ref['rollouts'][-1].actions[ref['best_id'], 0].numpy(), rtol=1e-12)
+    else:
+        assert result == se.MpcResult.SAFE_CONTROLLER and np.allclose(action, safe_policy(g['p0']))

@@ -188,3 +188,62 @@ def test_exp_polynomial_in_the_kernel_source_is_the_derived_one():
     got = [float(body[body.index('double p = ') + 11:].split(';')[0])]
     got += [float(v) for v in re.findall(r'p = fma\(p, r, ([0-9.e+-]+)\);', body)]
     assert got == coef[::-1]
+
+
+class _PendulumEnv:
+    """The attributes create_solver reads from an Environment (environments.py), with the pendulum constants that
+    workloads.py restates from the reference."""
+    n_s, n_u, dt = 2, 1, 0.05
+    l_mu, l_sigm = np.array([0.05, 0.02]), np.array([0.05, 0.02])
+    u_min_norm, u_max_norm = np.array([-1.0]), np.array([1.0])
+    objective_spec = None
+
+    def get_safety_constraints(self, normalize=True):
+        h, v = workloads.pendulum_polytope(True)
+        return h, v[:, None], None, None
+
+    def linearize_discretize(self):
+        return workloads.pendulum_linear_model()
+
+    @staticmethod
+    def objective_cost_function(ps):
+        return None
+
+
+class _CemConf:
+    solver_type, cem_ssm = 'safempc_cem', 'exact_gp_b200'
+    lin_prior, use_prior_model, use_state_constraint = True, True, True
+    lqr_wx_cost, lqr_wu_cost = np.diag([1., 2.]), 25 * np.eye(1)
+    cem_beta_safety = 2.0
+    mpc_time_horizon, cem_num_rollouts, cem_num_elites, cem_num_iterations = 3, 64, 8, 2
+    exact_gp_training_iterations, exact_gp_kernel = 10, 'rbf'
+    junk_state_dimen = junk_action_dimen = 0
+    verbose = 0
+
+
+def test_create_solver_wires_the_b200_classes():
+    """utils_config.py:58-135: the safempc_cem branch builds SSM, constraints and solver, and returns the LQR policy."""
+    solver, safe_policy = se.create_solver(_CemConf(), _PendulumEnv())
+    assert isinstance(solver, se.B200CemSafeMPC) and isinstance(solver._ssm, se.B200GpCemSSM)
+    assert solver.state_dimen == 2 and solver.action_dimen == 1 and solver.safety_trajectory_length == 3
+    a, b = workloads.pendulum_linear_model()
+    k, _, _ = se.dlqr(a, b, np.diag([1., 2.]), 25 * np.eye(1))
+    assert np.allclose(safe_policy(np.array([0.1, -0.2])), -k @ np.array([0.1, -0.2]))
+    assert np.allclose(solver.lin_model[0], a) and np.allclose(solver.lin_model[1], b)
+    cons = solver._mpc._rollout_function._constraints if hasattr(solver._mpc, '_rollout_function') else None
+    assert cons is None or isinstance(cons[1], se.EllipsoidStateConstraint)
+
+    class NoPrior(_CemConf):
+        lin_prior = False
+    with pytest.raises(ValueError, match='lin_prior'):
+        se.create_solver(NoPrior(), _PendulumEnv())
+
+    class Dropout(_CemConf):
+        cem_ssm = 'mc_dropout'
+    with pytest.raises(ValueError, match='Unknown value for cem_ssm'):
+        se.create_solver(Dropout(), _PendulumEnv())
+
+    class Casadi(_CemConf):
+        solver_type = 'safempc'
+    with pytest.raises(ValueError, match='Unknown solver type'):
+        se.create_solver(Casadi(), _PendulumEnv())
