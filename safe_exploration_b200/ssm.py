@@ -301,12 +301,15 @@ class B200GpCemSSM(CemSSM):
         k = self.kernel_matrix(x, ls, os_, nz)
         chol = torch.linalg.cholesky(k)
         del k
-        alpha = torch.cholesky_solve(yt.unsqueeze(-1), chol).squeeze(-1).contiguous()
-        mll = -0.5 * (yt * alpha).sum(-1) - chol.diagonal(dim1=1, dim2=2).log().sum(-1) - 0.5 * n * math.log(2 * math.pi)
-        kinv = torch.cholesky_inverse(chol)
+        logdet_half = chol.diagonal(dim1=1, dim2=2).log().sum(-1)
+        # K^-1 = L^-T L^-1 from one triangular solve and one DGEMM (potri is 3x slower at n = 2000 .. 5000)
+        eye = torch.eye(n, dtype=torch.float64, device=x.device).expand(self.num_states, -1, -1)
+        linv = torch.linalg.solve_triangular(chol, eye, upper=False)
         del chol
-        if not kinv.is_contiguous():  # cuSOLVER's column-major result: K^-1 is symmetric, so its transpose view serves
-            kinv = kinv.transpose(1, 2) if kinv.transpose(1, 2).is_contiguous() else kinv.contiguous()
+        kinv = torch.matmul(linv.transpose(1, 2), linv).contiguous()
+        alpha = torch.matmul(linv.transpose(1, 2), torch.matmul(linv, yt.unsqueeze(-1))).squeeze(-1).contiguous()
+        del linv
+        mll = -0.5 * (yt * alpha).sum(-1) - logdet_half - 0.5 * n * math.log(2 * math.pi)
         ws = torch.empty(max(1, self._lib.se_gp_mll_grad_workspace(self.num_states, d, n) // 8), dtype=torch.float64,
                          device=x.device)
         grad = torch.empty((self.num_states, d + 2), dtype=torch.float64, device=x.device)
