@@ -39,7 +39,7 @@ def parse_args():
     ap.add_argument('--dtype', default='f64', choices=['f64', 'f32'])
     ap.add_argument('--config', default='C2', choices=['C1', 'C2', 'C3'])
     ap.add_argument('--gemm', default='auto', choices=['auto', 'simt', 'mma', 'tc'])
-    ap.add_argument('--tc-digits', type=int, default=0, choices=[0, 5, 6, 7, 8],
+    ap.add_argument('--tc-digits', type=int, default=0, choices=[0, 3, 4, 5, 6, 7, 8],
                     help='digit planes of the tcgen05 variance GEMM (0 = chosen from outputscale / noise)')
     ap.add_argument('--cpu-sample', type=int, default=2048, help='candidates in the CPU-baseline sample')
     ap.add_argument('--no-cpu-baseline', action='store_true')
@@ -356,6 +356,12 @@ def run_b200(args):
         variance_check = {'against': 'float64 DMMA kernel', 'inputs': 2048, 'max_rel_err': float(rel.max()),
                           'median_rel_err': float(rel.median())}
 
+    accuracy_note = {}
+    if impl_name == 'tcgen05-i8':
+        accuracy_note = {'variance_digit_planes': digits,
+                         'accuracy_class': 'float64 (variance to 1e-8 relative)' if digits >= 6 else
+                         'reduced: %d digit planes (float32-tolerance dial of se_gp_set_tc_digits; achieved error in '
+                                           'variance_check)' % digits}
     cpu_baseline = None
     if rank == 0 and not args.no_cpu_baseline:
         w1 = make_workload(args.config, 1)
@@ -373,7 +379,7 @@ def run_b200(args):
             'metric': METRIC, 'value': value, 'unit': UNIT, 'n_gpus': world, 'steps': args.steps,
             'warmup': max(3, args.warmup), 'ms_per_step': ms_per_step, 'mpc_solve_ms': ms_per_step,
             'higher_is_better': True, 'scaling': 'weak', 'vs_baseline': None, 'dtype': args.dtype, 'data': 'synthetic',
-            'config': workload_desc(w, world, args.dtype), 'e2e': e2e, 'gpu_launches': launches, 'roofline': roofline,
+            'config': dict(workload_desc(w, world, args.dtype), **accuracy_note), 'e2e': e2e, 'gpu_launches': launches, 'roofline': roofline,
             'variance_check': variance_check, 'cpu_baseline': cpu_baseline, 'clocks': clocks.summary(), 'numeric_flags': flags,
             'found_solution': bool(int(res['found'][0])), 'last_result': result.name,
         }

@@ -78,8 +78,11 @@ int se_gp_destroy(se_gp_t gp);
 int se_gp_set_workspace_limit(se_gp_t gp, uint64_t bytes);
 int se_gp_set_gemm_impl(se_gp_t gp, se_gemm_impl impl);
 /* digit planes per operand of SE_GEMM_TC.  0 (default) = chosen from max_o outputscale_o / noise_o for a relative
- * variance error <= 1e-8; measured against the float64 DMMA path at outputscale / noise = 10^3: 6 planes 1.7e-9
- * (21 int8 MMAs per K step), 7 planes 1.5e-11 (28), 8 planes 7e-12 (36, float64 rounding level), 5 planes 3e-7 (15) */
+ * variance error <= 1e-8 (never fewer than 6); measured against the float64 DMMA path at outputscale / noise = 10^3:
+ * 6 planes 1.7e-9 (21 int8 MMAs per K step), 7 planes 1.5e-11 (28), 8 planes 7e-12 (36, float64 rounding level),
+ * 5 planes 3e-7 (15).  4 and 3 planes (10 / 6 MMAs) are the float32-TOLERANCE settings of BASELINE's "within 1e-4
+ * relative in fp32": the truncation is ~1e-7 / ~3e-5 of the prior scale outputscale + noise (float32 arithmetic itself
+ * reaches ~2e-7 of it at best), mean and Jacobian stay float64. */
 int se_gp_set_tc_digits(se_gp_t gp, int digits);
 /* which variance-GEMM implementation the handle resolved to, and the digit planes in use (0 until the first call) */
 int se_gp_get_gemm_info(se_gp_t gp, int* impl_out, int* tc_digits_out);

@@ -117,13 +117,15 @@ int launch_trisumsq_ozaki(const int8_t* a_img, const int8_t* b_img, const double
            : reuse ? launch_oz_gemm_s<S_, 1>(a_img, b_img, scale_b, n, n_pad, rows_pad, od, grid, partial, stream)     \
                    : launch_oz_gemm_s<S_, 0>(a_img, b_img, scale_b, n, n_pad, rows_pad, od, grid, partial, stream);
   switch (S) {
+    SE_OZ_CASE(3)
+    SE_OZ_CASE(4)
     SE_OZ_CASE(5)
     SE_OZ_CASE(6)
     SE_OZ_CASE(7)
     SE_OZ_CASE(8)
   }
 #undef SE_OZ_CASE
-  return fail("tcgen05 variance GEMM: digit planes S = %d not compiled (5 .. 8)", S);
+  return fail("tcgen05 variance GEMM: digit planes S = %d not compiled (3 .. 8)", S);
 }
 
 template <int S>
@@ -147,6 +149,8 @@ static int launch_probe_s(const int8_t* a_img, const int8_t* b_img, int nk, uint
 int launch_oz_probe(const int8_t* a_img, const int8_t* b_img, int nk, int S, int lbo, int sbo, int32_t* out,
                     cudaStream_t stream) {
   switch (S) {
+    case 3: return launch_probe_s<3>(a_img, b_img, nk, lbo, sbo, out, stream);
+    case 4: return launch_probe_s<4>(a_img, b_img, nk, lbo, sbo, out, stream);
     case 5: return launch_probe_s<5>(a_img, b_img, nk, lbo, sbo, out, stream);
     case 6: return launch_probe_s<6>(a_img, b_img, nk, lbo, sbo, out, stream);
     case 7: return launch_probe_s<7>(a_img, b_img, nk, lbo, sbo, out, stream);

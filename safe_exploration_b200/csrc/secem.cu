@@ -201,7 +201,7 @@ extern "C" int se_gp_set_gemm_impl(se_gp_t g, se_gemm_impl impl) {
 }
 extern "C" int se_gp_set_tc_digits(se_gp_t g, int digits) {
   SE_REQUIRE(g, "NULL handle");
-  SE_REQUIRE(digits == 0 || (digits >= 5 && digits <= 8), "se_gp_set_tc_digits: %d is neither 0 (auto) nor in [5, 8]",
+  SE_REQUIRE(digits == 0 || (digits >= 3 && digits <= 8), "se_gp_set_tc_digits: %d is neither 0 (auto) nor in [3, 8]",
              digits);
   g->tc_digits_req = digits;
   return 0;

@@ -34,7 +34,7 @@ def image(planes):
     return np.ascontiguousarray(planes.reshape(nk, S, R // 8, 8, 2, 16).transpose(0, 1, 2, 4, 3, 5)).reshape(-1)
 
 
-@pytest.mark.parametrize('S', [5, 6, 7, 8])
+@pytest.mark.parametrize('S', [3, 4, 5, 6, 7, 8])
 @pytest.mark.parametrize('nk', [1, 2, 5])
 def test_tile_primitive_is_bit_exact(S, nk):
     """One 128 x 64 tile: level sums D_l = sum_{t+u=l} A_t B_u^T over nk K steps, full signed-byte range."""
@@ -244,3 +244,51 @@ def test_non_finite_inputs_poison_the_mean():
     assert torch.isnan(mean[bad]).all() and torch.isnan(jac[bad]).all()
     assert torch.equal(mean[~bad], clean[0][~bad]) and torch.equal(var[~bad], clean[1][~bad])
     assert torch.equal(jac[~bad], clean[2][~bad])
+
+
+@pytest.mark.parametrize('digits,tol', [(4, 1e-6), (3, 1e-4)])
+@pytest.mark.parametrize('n_s,n_u,n,N', [(2, 1, 300, 1000), (4, 1, 700, 513), (6, 2, 257, 129)])
+def test_float32_tolerance_planes(digits, tol, n_s, n_u, n, N):
+    """4 / 3 digit planes: BASELINE's float32 tolerance (1e-4 relative, the variance taken relative to the prior scale
+    outputscale + noise like in the float32 tests of test_gpu_parity.py) on the tensor cores; 4 planes hold 1e-6.
+    Mean and Jacobian are float64 work and keep 1e-9."""
+    x, y, ls, os_, nz = _random_model(n_s, n_u, n, n + N)
+    z = np.random.default_rng(1).uniform(-1.1, 1.1, (N, n_s + n_u))
+    z[: N // 2] = x[np.random.default_rng(2).integers(0, n, N // 2)] + 1e-3
+    gp = se.B200GpCemSSM(None, n_s, n_u, ls, os_, nz, device=DEV, gemm_impl=_lib.SE_GEMM_TC, tc_digits=digits)
+    gp.update_model(G(x), G(y), replace_old=True)
+    ref = oracle.OracleGpCemSSM(n_s, n_u, ls, os_, nz)
+    ref.update_model(T(x), T(y), replace_old=True)
+    mean, var, jac = gp.predict_with_jacobians(G(z[:, :n_s]), G(z[:, n_s:]))
+    m0, v0, j0 = ref.predict_with_jacobians(T(z[:, :n_s]), T(z[:, n_s:]))
+    assert gp.gemm_info() == ('tcgen05-i8', digits)
+    prior = (os_ + nz)[None, :]
+    assert rel_err(var.cpu(), v0, prior) < tol
+    assert rel_err(mean.cpu(), m0, np.abs(m0.numpy()).max()) < 1e-9
+    assert rel_err(jac.cpu(), j0, np.abs(j0.numpy()).max()) < 1e-9
+
+
+def test_float32_tolerance_planes_same_decisions_outside_margin():
+    """A whole solve with 4 digit planes on RNG-fixed candidates: identical safe/unsafe decisions for every candidate
+    whose terminal safety distance is outside a 1e-4 margin band, ellipsoid centres / shapes within 1e-4 relative."""
+    w = workloads.pendulum_workload(n_train=400, num_rollouts=1024, time_horizon=6, num_elites=32, num_iterations=1,
+                                    name='tc4')
+    ssm, mpc = workloads.build_solver(w, record='full', seed=11)
+    ssm.set_tc_digits(4)
+    res = mpc.solve(G(w.p0).unsqueeze(0), seed=11)
+    assert ssm.gemm_info() == ('tcgen05-i8', 4)
+    noise = np.stack([oracle.philox_normal_noise(11, 0, 0, w.num_rollouts, w.time_horizon, 1)])
+    gp = oracle.OracleGpCemSSM(2, 1, w.lengthscale, w.outputscale, w.noise)
+    gp.update_model(T(w.x_train), T(w.y_train), replace_old=True)
+    prob = oracle.SafeCemProblem(gp, w.l_mu, w.l_sigma, w.k_fb, w.a, w.b, w.beta_safety, w.h_mat, w.h_vec, w.act_a,
+                                 w.act_b)
+    ref = oracle.cem_solve(prob, T(w.p0), T(noise), w.num_elites)
+    r = ref['rollouts'][0]
+    last = r.trajectories[:, -1]
+    d = oracle.lin_ellipsoid_safety_distance(last[:, :2], last[:, 2:].reshape(-1, 2, 2), T(w.h_mat),
+                                             T(w.h_vec).reshape(-1, 1))
+    clear = (d.abs().min(dim=1)[0] > 1e-4).numpy()
+    assert clear.sum() >= 0.9 * len(clear)
+    assert np.array_equal(res['constraint'][0, 0].cpu().numpy()[clear], r.constraint_costs.numpy()[clear])
+    traj = r.trajectories.numpy()
+    assert rel_err(res['trajectories'][0, 0].cpu().numpy(), traj, np.abs(traj).max(axis=(0, 1))[None, None, :]) < 1e-4
