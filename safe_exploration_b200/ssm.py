@@ -115,7 +115,11 @@ class B200GpCemSSM(CemSSM):
 
     :param conf: optional config object; `exact_gp_training_iterations` and `exact_gp_kernel` are read if present
                  (only 'rbf' is accelerated; the reference's 'linear' / 'nn' kernels stay on GPyTorch).
-    :param dtype: torch.float64 (reference precision, default) or torch.float32
+    :param dtype: torch.float64 (reference precision, default) or torch.float32 (the whole path in float32 FFMA
+                  arithmetic; kept for parity studies -- it is SLOWER than the default, whose variance contraction runs
+                  on the tensor cores).  For float32-class tolerance at higher speed keep float64 and pass tc_digits=4
+    :param tc_digits: digit planes of the tensor-core variance GEMM: 0 = float64-class, chosen from outputscale/noise
+                  (never fewer than 6); 7 / 8 = float64-equivalent; 4 / 3 = float32 tolerance (see set_tc_digits)
     :param incremental: keep the float64 inverse Cholesky factor on the device (n_s n^2 doubles) so that
                         `update_model(..., replace_old=False)` only computes the rows of the appended samples
     """
