@@ -14,6 +14,7 @@ static int make_hyp(int n_s, int d, const double* ls, const double* os, const do
       SE_REQUIRE(l > 0.0, "lengthscale[%d][%d] = %g is not positive", o, c, l);
       h->neg_half_inv_l2[o][c] = -0.5 / (l * l);
       h->inv_l3[o][c] = 1.0 / (l * l * l);
+      h->lengthscale[o][c] = l;
     }
     h->outputscale[o] = os[o];
     h->noise[o] = nz[o];

@@ -331,35 +331,70 @@ reach_step_kernel(ProbDev<T> pr, StepIO<T> io, int64_t N) {
   T p[NS], u[NU], mu[NS], var[NS], sg[NS];
   T q[NS][NS], jac[NS][D];
   const bool split_sums = io.partial && io.nseg > 0;
+  // The sums below add in ascending block / segment order (what gp_var_kernel does), but the loads of a batch are
+  // issued together for every output: a thread waits once per 8 blocks instead of once per block -- the kernel is a
+  // pure latency chain (one thread per candidate), and these loads were most of it.
+  if (io.partial) {  // gp_var_kernel, fused
+    const int64_t r = c - io.first;
+    T s[NS];
 #pragma unroll
-  for (int i = 0; i < NS; ++i) {
-    p[i] = io.p_in[c * NS + i];
-    if (io.partial) {  // gp_var_kernel, fused
-      const int64_t r = c - io.first;
-      T s = T(0);
-      for (int ib = 0; ib < io.nb; ++ib) s += io.partial[((int64_t)i * io.nb + ib) * io.rows_pad + r];
-      var[i] = io.gp_outputscale[i] - s + io.gp_noise[i];
-    } else {
-      var[i] = io.var[c * NS + i];
+    for (int i = 0; i < NS; ++i) s[i] = T(0);
+    for (int ib0 = 0; ib0 < io.nb; ib0 += 8) {
+      T v[NS][8];
+#pragma unroll
+      for (int i = 0; i < NS; ++i)
+#pragma unroll
+        for (int k = 0; k < 8; ++k)
+          v[i][k] = ib0 + k < io.nb ? io.partial[((int64_t)i * io.nb + ib0 + k) * io.rows_pad + r] : T(0);
+#pragma unroll
+      for (int i = 0; i < NS; ++i)
+#pragma unroll
+        for (int k = 0; k < 8; ++k) s[i] += v[i][k];  // + 0 for the blocks past nb: exact
     }
-    if (split_sums) {
-      const T* src = io.kpart + ((c - io.first) * NS + i) * (1 + D);
-      const int64_t seg_stride = (int64_t)io.rows_pad * NS * (1 + D);
-      T m = T(0);
-      for (int sgi = 0; sgi < io.nseg; ++sgi) m += src[sgi * seg_stride];
-      mu[i] = m;
 #pragma unroll
-      for (int j = 0; j < D; ++j) {
-        T g = T(0);
-        if (!io.point)
-          for (int sgi = 0; sgi < io.nseg; ++sgi) g += src[sgi * seg_stride + 1 + j];
-        jac[i][j] = -g * io.gp_inv_l2[i][j];
-      }
-    } else {
+    for (int i = 0; i < NS; ++i) var[i] = io.gp_outputscale[i] - s[i] + io.gp_noise[i];
+  } else {
+#pragma unroll
+    for (int i = 0; i < NS; ++i) var[i] = io.var[c * NS + i];
+  }
+  if (split_sums) {
+    constexpr int W = NS * (1 + D);  // values per (segment, candidate): mean and Jacobian sums of every output
+    const T* src = io.kpart + (c - io.first) * W;
+    const int64_t seg_stride = (int64_t)io.rows_pad * W;
+    T acc[W];
+#pragma unroll
+    for (int e = 0; e < W; ++e) acc[e] = T(0);
+    for (int sg0 = 0; sg0 < io.nseg; sg0 += 2) {
+      T v[2][W];
+#pragma unroll
+      for (int k = 0; k < 2; ++k)
+#pragma unroll
+        for (int e = 0; e < W; ++e) {
+          const bool want = sg0 + k < io.nseg && (!io.point || e % (1 + D) == 0);  // point branch: means only
+          v[k][e] = want ? src[(sg0 + k) * seg_stride + e] : T(0);
+        }
+#pragma unroll
+      for (int k = 0; k < 2; ++k)
+#pragma unroll
+        for (int e = 0; e < W; ++e) acc[e] += v[k][e];
+    }
+#pragma unroll
+    for (int i = 0; i < NS; ++i) {
+      mu[i] = acc[i * (1 + D)];
+#pragma unroll
+      for (int j = 0; j < D; ++j) jac[i][j] = -acc[i * (1 + D) + 1 + j] * io.gp_inv_l2[i][j];
+    }
+  } else {
+#pragma unroll
+    for (int i = 0; i < NS; ++i) {
       mu[i] = io.mean[c * NS + i];
 #pragma unroll
       for (int j = 0; j < D; ++j) jac[i][j] = io.point ? T(0) : io.jac[(c * NS + i) * D + j];
     }
+  }
+#pragma unroll
+  for (int i = 0; i < NS; ++i) {
+    p[i] = io.p_in[c * NS + i];
 #pragma unroll
     for (int j = 0; j < NS; ++j) q[i][j] = io.point ? T(0) : io.q_in[(c * NS + i) * NS + j];
   }
