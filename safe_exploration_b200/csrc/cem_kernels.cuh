@@ -127,7 +127,7 @@ __device__ __forceinline__ uint64_t orderable(double x) {
 
 constexpr int kSelThreads = 1024;
 constexpr int kMaxElites = 4096;
-constexpr int kRankSelectMax = 1024;  // populations up to this size are selected by rank counting (<= kMaxElites keys)
+constexpr int kSortAllMax = kMaxElites;  // populations up to this size go through the sorting network whole (smem arrays hold kMaxElites keys)
 
 template <typename T>
 struct SelectArgs {
@@ -184,22 +184,17 @@ cem_select_refit_kernel(SelectArgs<T> a) {
     return orderable((double)a.costs.get(1, inst, g));
   };
 
-  if (n <= kRankSelectMax) {
-    // Small populations (the reference's own sizes, N = 20 .. 500): rank every key by counting.  Keys are made unique
-    // by the index tie-break, so rank < E  <=>  elite, and the rank IS the position in the sorted elite list: no
-    // radix passes, no compaction, no sort -- two barriers instead of ~40.
-    for (int g = tid; g < n; g += kSelThreads) s_key[g] = key_of(g);
-    __syncthreads();
-    for (int g = tid; g < n; g += kSelThreads) {
-      const uint64_t k = s_key[g];
-      int rank = 0;
-      for (int h = 0; h < n; ++h) {
-        const uint64_t kh = s_key[h];  // same address for the whole warp: broadcast
-        rank += (kh < k || (kh == k && h < g)) ? 1 : 0;
-      }
-      if (rank < E) s_idx[rank] = g;
+  int P = 1;  // length of the (key, index) array the bitonic network below sorts
+  if (n <= kSortAllMax) {
+    // Populations up to 4096 (the reference's own sizes are N = 20 .. 500): no selection pass at all, the whole
+    // population goes through the sorting network (55 compare-exchange stages of one comparator per thread at
+    // N <= 1024, 78 of two at 4096).  Measured alternatives: ranking every key by counting costs N^2 64-bit comparisons
+    // on this one SM (9 us at N = 500), the radix select below re-reads the costs eight times (39 us at N = 2048).
+    while (P < n) P <<= 1;
+    for (int g = tid; g < P; g += kSelThreads) {
+      s_key[g] = g < n ? key_of(g) : ~0ull;
+      s_idx[g] = g < n ? g : 0x7FFFFFFF;
     }
-    __syncthreads();
   } else {
   // radix select: the E-th smallest key, most significant byte first
   if (tid == 0) {
@@ -276,14 +271,15 @@ cem_select_refit_kernel(SelectArgs<T> a) {
     base_less += tot_less;
     base_eq += tot_eq;
   }
-  // pad to a power of two and bitonic-sort by (key, index)
-  int P = 1;
+  // pad the E selected keys to a power of two
   while (P < E) P <<= 1;
   __syncthreads();
   for (int i = E + tid; i < P; i += kSelThreads) {
     s_key[i] = ~0ull;
     s_idx[i] = 0x7FFFFFFF;
   }
+  }  // n > kSortAllMax
+  // bitonic sort by (key, index): ascending (cost, global index)
   __syncthreads();
   for (int size = 2; size <= P; size <<= 1) {
     for (int stride = size >> 1; stride > 0; stride >>= 1) {
@@ -302,7 +298,6 @@ cem_select_refit_kernel(SelectArgs<T> a) {
       __syncthreads();
     }
   }
-  }  // n > kRankSelectMax
   if (a.elite_ids)
     for (int i = tid; i < E; i += kSelThreads) a.elite_ids[(int64_t)inst * E + i] = s_idx[i];
 
