@@ -157,10 +157,11 @@ __device__ __forceinline__ int block_sum_int(int v, int* s_warp) {
 // ties are the norm (constraint costs are small integers), so the index tie-break is fixed here and in the oracle.
 template <typename T>
 __global__ void __launch_bounds__(kSelThreads)
-cem_select_refit_kernel(SelectArgs<T> a) {
+cem_select_refit_kernel(SelectArgs<T> a, int cache_n) {
   extern __shared__ __align__(16) unsigned char sel_smem[];
   uint64_t* s_key = reinterpret_cast<uint64_t*>(sel_smem);          // [P]
   int* s_idx = reinterpret_cast<int*>(s_key + kMaxElites);           // [P]
+  uint64_t* s_all = reinterpret_cast<uint64_t*>(s_idx + kMaxElites); // [n] keys of the whole population when cache_n >= n
   __shared__ int s_hist[256];
   __shared__ int s_warp[kSelThreads / 32];
   __shared__ int s_warp2[kSelThreads / 32];
@@ -196,7 +197,13 @@ cem_select_refit_kernel(SelectArgs<T> a) {
       s_idx[g] = g < n ? g : 0x7FFFFFFF;
     }
   } else {
-  // radix select: the E-th smallest key, most significant byte first
+  // radix select: the E-th smallest key, most significant byte first.  The keys are formed once and kept in shared
+  // memory when the population fits (cache_n >= n: up to 16384 candidates), so the eight passes and the compaction do
+  // not go back to the cost planes in global memory.
+  const bool cached = cache_n >= n;
+  if (cached)
+    for (int g = tid; g < n; g += kSelThreads) s_all[g] = key_of(g);
+  auto key_at = [&](int g) -> uint64_t { return cached ? s_all[g] : key_of(g); };
   if (tid == 0) {
     s_prefix = 0;
     s_remaining = E;
@@ -207,10 +214,20 @@ cem_select_refit_kernel(SelectArgs<T> a) {
     if (tid < 256) s_hist[tid] = 0;
     __syncthreads();
     const uint64_t prefix = s_prefix;
+    // neighbouring costs share their leading bytes, so on the first passes every key lands in ONE bin: a thread counts
+    // runs of equal bins in a register and issues one atomic per run (16 same-address atomics per thread otherwise)
+    int run_bin = -1, run_len = 0;
     for (int g = tid; g < n; g += kSelThreads) {
-      const uint64_t k = key_of(g);
-      if ((k & mask) == prefix) atomicAdd(&s_hist[(int)((k >> shift) & 255)], 1);
+      const uint64_t k = key_at(g);
+      if ((k & mask) != prefix) continue;
+      const int bin = (int)((k >> shift) & 255);
+      if (bin != run_bin) {
+        if (run_len) atomicAdd(&s_hist[run_bin], run_len);
+        run_bin = bin, run_len = 0;
+      }
+      ++run_len;
     }
+    if (run_len) atomicAdd(&s_hist[run_bin], run_len);
     __syncthreads();
     if (tid == 0) {
       int rem = s_remaining, b = 0;
@@ -235,7 +252,7 @@ cem_select_refit_kernel(SelectArgs<T> a) {
     uint64_t k = ~0ull;
     bool f_less = false, f_eq = false;
     if (g < n) {
-      k = key_of(g);
+      k = key_at(g);
       f_less = k < vstar;
       f_eq = k == vstar;
     }

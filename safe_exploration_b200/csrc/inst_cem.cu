@@ -26,13 +26,15 @@ int launch_cem_noise(uint64_t seed, int iteration, int num_inst, int n_global, i
 
 template <typename T>
 int launch_cem_select_refit(const SelectArgs<T>& a, int num_inst, cudaStream_t stream) {
-  const int smem = kMaxElites * 12;
-  static bool attr_set = false;
-  if (!attr_set) {
+  // selected keys + indices, and (populations of 4097 .. 16384) a cache of every key
+  const int cache_n = a.n_global > kSortAllMax && a.n_global <= 16384 ? a.n_global : 0;
+  const int smem = kMaxElites * 12 + cache_n * 8;
+  static int attr_smem = 0;
+  if (smem > attr_smem) {
     SE_CUDA(cudaFuncSetAttribute(cem_select_refit_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-    attr_set = true;
+    attr_smem = smem;
   }
-  SE_LAUNCH((cem_select_refit_kernel<T>), num_inst, kSelThreads, smem, stream, a);
+  SE_LAUNCH((cem_select_refit_kernel<T>), num_inst, kSelThreads, smem, stream, a, cache_n);
   return 0;
 }
 
