@@ -30,7 +30,8 @@ int launch_oz_pack_model(const double* w, int n_pad, int ns, const double* host_
 
 int launch_kstar_slices(const GpDev<double>& gp, const double* p, int64_t p_stride, const double* u, int64_t u_stride,
                         int64_t row0, int nrows, int rows_pad, const int* exp_a, int S, int8_t* a_img, double* mean,
-                        double* jac, int seg_per_cta, double* kpart, cudaStream_t stream) {
+                        double* jac, int seg_per_cta, double* kpart, cudaStream_t stream, const ProbDev<double>* fuse_pr,
+                        const StepIO<double>* fuse_io) {
   // SE_KSTAR_R = 1 / 2: the one-warp-per-row(-pair) kernels, kept for comparison; default: the row-group kernel
   static const int r_env = getenv("SE_KSTAR_R") ? atoi(getenv("SE_KSTAR_R")) : 8;
   const bool want_jac = jac != nullptr;
@@ -44,12 +45,20 @@ int launch_kstar_slices(const GpDev<double>& gp, const double* p, int64_t p_stri
     dim3 grid8((unsigned)ceil_div(rows_pad / 8, 2), (unsigned)ceil_div(segs, spc));
 #define SE_CASE8(NS_, NU_)                                                                                          \
   if (gp.ns == NS_ && gp.nu == NU_) {                                                                               \
+    if (fuse_io) {                                                                                                  \
+      SE_REQUIRE(want_jac && fuse_pr, "the fused ellipsoid step precedes a kernel-row launch with Jacobians");      \
+      oz::FuseArgs<true> fa;                                                                                        \
+      fa.pr = *fuse_pr, fa.io = *fuse_io;                                                                           \
+      SE_LAUNCH((oz::gp_kstar_slices8_kernel<NS_, NS_ + NU_, true, true>), grid8, 64, 0, stream, gp, p, p_stride,   \
+                u, u_stride, row0, nrows, rows_pad, exp_a, S, a_img, mean, jac, spc, kpart, fa);                    \
+      return 0;                                                                                                     \
+    }                                                                                                               \
     if (want_jac)                                                                                                   \
       SE_LAUNCH((oz::gp_kstar_slices8_kernel<NS_, NS_ + NU_, true>), grid8, 64, 0, stream, gp, p, p_stride, u,      \
-                u_stride, row0, nrows, rows_pad, exp_a, S, a_img, mean, jac, spc, kpart);                           \
+                u_stride, row0, nrows, rows_pad, exp_a, S, a_img, mean, jac, spc, kpart, oz::FuseArgs<false>());    \
     else                                                                                                            \
       SE_LAUNCH((oz::gp_kstar_slices8_kernel<NS_, NS_ + NU_, false>), grid8, 64, 0, stream, gp, p, p_stride, u,     \
-                u_stride, row0, nrows, rows_pad, exp_a, S, a_img, mean, jac, spc, kpart);                           \
+                u_stride, row0, nrows, rows_pad, exp_a, S, a_img, mean, jac, spc, kpart, oz::FuseArgs<false>());    \
     return 0;                                                                                                       \
   }
     SE_FOR_NS_NU(SE_CASE8)

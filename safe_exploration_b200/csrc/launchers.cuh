@@ -72,7 +72,8 @@ int launch_oz_pack_model(const double* w, int n_pad, int ns, const double* host_
                          int* exp_b, double* scale_b, int8_t* b_img, cudaStream_t stream);
 int launch_kstar_slices(const GpDev<double>& gp, const double* p, int64_t p_stride, const double* u, int64_t u_stride,
                         int64_t row0, int nrows, int rows_pad, const int* exp_a, int S, int8_t* a_img, double* mean,
-                        double* jac, int seg_per_cta, double* kpart, cudaStream_t stream);
+                        double* jac, int seg_per_cta, double* kpart, cudaStream_t stream,
+                        const ProbDev<double>* fuse_pr = nullptr, const StepIO<double>* fuse_io = nullptr);
 int launch_trisumsq_ozaki(const int8_t* a_img, const int8_t* b_img, const double* scale_b, int n, int n_pad,
                           int rows_pad, int ns, int S, double* partial, int sm_count, int* nb_out, cudaStream_t stream);
 int launch_oz_probe(const int8_t* a_img, const int8_t* b_img, int nk, int S, int lbo, int sbo, int32_t* out,

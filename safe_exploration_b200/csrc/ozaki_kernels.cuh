@@ -20,6 +20,7 @@
 #pragma once
 #include "common.cuh"
 #include "gp_kernels.cuh"
+#include "reach_kernels.cuh"
 
 namespace se {
 namespace oz {
@@ -413,14 +414,27 @@ gp_kstar_slices_kernel(GpDev<double> gp, const double* __restrict__ p, int64_t p
 // is fetched once per 8 candidates instead of once per candidate (the one-row-per-warp kernel above pulls 80 KB through
 // L1 per candidate at n = 2048 and sits at 84 % L1 throughput with the FP64 pipe at 41 %).
 // ---------------------------------------------------------------------------------------------------------------------
-template <int NS, int D, bool JAC>
+// FUSE (small batches inside se_cem_solve): the kernel first advances its candidates' ellipsoids by the PREVIOUS
+// horizon step (reach_step_body: variance from the GEMM's partial sums, ellipsoid step, CEM bookkeeping) and takes the
+// new centres straight from registers -- one launch per horizon step less in a chain where every launch costs ~10 us.
+// All four lanes of a candidate (and every training-set segment's CTA) run the step; one of them writes.  The step reads
+// the old ellipsoids / segment sums and writes the new ones to different buffers (the host alternates them).
+template <bool FUSE>
+struct FuseArgs {};
+template <>
+struct FuseArgs<true> {
+  ProbDev<double> pr;
+  StepIO<double> io;
+};
+
+template <int NS, int D, bool JAC, bool FUSE = false>
 // CTAs per SM: 8 (128 registers) is the measured optimum for n_s <= 3 (C2: 0.216 ms; 6 -> 0.279, 10 -> 0.226, 12 -> 0.240);
 // with 4 and more outputs the accumulators no longer fit and 6 (168 registers) wins (C3: 3.10 vs 3.82 ms)
 __global__ void __launch_bounds__(64, NS <= 3 ? 8 : 6)
 gp_kstar_slices8_kernel(GpDev<double> gp, const double* __restrict__ p, int64_t p_stride, const double* __restrict__ u,
                         int64_t u_stride, int64_t row0, int nrows, int rows_pad, const int* __restrict__ exp_a, int S,
                         int8_t* __restrict__ a_img, double* __restrict__ mean, double* __restrict__ jac,
-                        int seg_per_cta, double* __restrict__ kpart) {
+                        int seg_per_cta, double* __restrict__ kpart, FuseArgs<FUSE> fa) {
   const int lane = threadIdx.x & 31;
   const int64_t warp = blockIdx.x * (int64_t)(blockDim.x >> 5) + (threadIdx.x >> 5);
   const int64_t r0 = warp * 8;  // rows_pad is a multiple of 128 and the grid is rows_pad / 16 CTAs: every warp has rows
@@ -431,11 +445,20 @@ gp_kstar_slices8_kernel(GpDev<double> gp, const double* __restrict__ p, int64_t 
   const int nkb = n_pad / KB, rt_count = rows_pad / TM;
 
   double z[D];
+  if constexpr (FUSE) {
+    double p1[NS];
 #pragma unroll
-  for (int dd = 0; dd < D; ++dd) {
-    double v = 0.0;
-    if (valid) v = dd < NS ? p[(row0 + row) * p_stride + dd] : u[(row0 + row) * u_stride + (dd - NS)];
-    z[dd] = v;
+    for (int dd = 0; dd < NS; ++dd) p1[dd] = 0.0;
+    if (valid) reach_step_body<double, NS, D - NS>(fa.pr, fa.io, row0 + row, quad == 0 && blockIdx.y == 0, p1);
+#pragma unroll
+    for (int dd = 0; dd < D; ++dd) z[dd] = dd < NS ? p1[dd] : (valid ? u[(row0 + row) * u_stride + (dd - NS)] : 0.0);
+  } else {
+#pragma unroll
+    for (int dd = 0; dd < D; ++dd) {
+      double v = 0.0;
+      if (valid) v = dd < NS ? p[(row0 + row) * p_stride + dd] : u[(row0 + row) * u_stride + (dd - NS)];
+      z[dd] = v;
+    }
   }
   double qscale[NS], log_s[NS], nh_inv_l2[NS][D];
 #pragma unroll

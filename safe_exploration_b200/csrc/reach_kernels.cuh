@@ -321,12 +321,14 @@ __device__ __forceinline__ T step_constraint(const ProbDev<T>& pr, const T (&p1)
   return cc;
 }
 
+// The ellipsoid step of candidate c with everything around it (variance / mean / Jacobian sums, outputs, CEM
+// bookkeeping).  reach_step_kernel runs it with one thread per candidate; the fused kernel-row kernel of small batches
+// (gp_kstar_slices8_kernel<..., FUSE>) runs it in every lane that works on the candidate, with `writer` set in exactly
+// one of them: the others only need the new centre p1.
 template <typename T, int NS, int NU>
-__global__ void __launch_bounds__(128)
-reach_step_kernel(ProbDev<T> pr, StepIO<T> io, int64_t N) {
+__device__ __forceinline__ void reach_step_body(const ProbDev<T>& pr, const StepIO<T>& io, int64_t c, bool writer,
+                                                T (&p1)[NS]) {
   constexpr int D = NS + NU;
-  const int64_t c = io.first + blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
-  if (c >= io.first + N) return;
 
   T p[NS], u[NU], mu[NS], var[NS], sg[NS];
   T q[NS][NS], jac[NS][D];
@@ -400,8 +402,9 @@ reach_step_kernel(ProbDev<T> pr, StepIO<T> io, int64_t N) {
   }
 #pragma unroll
   for (int j = 0; j < NU; ++j) u[j] = io.u[c * io.u_stride + j];
-  T p1[NS], q1[NS][NS];
-  ellipsoid_step_core<T, NS, NU>(pr, p, q, io.point != 0, u, mu, var, jac, io.flags, p1, q1, sg);
+  T q1[NS][NS];
+  ellipsoid_step_core<T, NS, NU>(pr, p, q, io.point != 0, u, mu, var, jac, writer ? io.flags : nullptr, p1, q1, sg);
+  if (!writer) return;
 
   // ---- write the new ellipsoid ----
 #pragma unroll
@@ -458,6 +461,15 @@ reach_step_kernel(ProbDev<T> pr, StepIO<T> io, int64_t N) {
     io.constraint[c] = cc + step_constraint<T, NS, NU>(pr, p1, q1, io.last_step != 0,
                                                        io.act_all ? io.act_all + c * io.T_len * NU : nullptr, io.T_len);
   }
+}
+
+template <typename T, int NS, int NU>
+__global__ void __launch_bounds__(128)
+reach_step_kernel(ProbDev<T> pr, StepIO<T> io, int64_t N) {
+  const int64_t c = io.first + blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (c >= io.first + N) return;
+  T p1[NS];
+  reach_step_body<T, NS, NU>(pr, io, c, true, p1);
 }
 
 // stand-alone polytope distance (se_safety_distance)

@@ -298,6 +298,9 @@ static int64_t chunk_rows(const se_gp_s* g, int64_t N) {
   return n_rows_pad < by_limit ? n_rows_pad : by_limit;
 }
 
+static size_t kpart_set_bytes(const se_gp_s* g, int64_t split_rows) {
+  return (size_t)(g->n_pad / 128) * split_rows * g->ns * (1 + g->d) * sizeof(double);
+}
 // Ensure workspace for a batch of N candidates.  Allocates (cudaMalloc) only when the batch grows, so a caller that
 // wants to capture a CUDA graph warms the handle up with one eager call first.
 static int gp_reserve(se_gp_s* g, int64_t N) {
@@ -306,7 +309,8 @@ static int gp_reserve(se_gp_s* g, int64_t N) {
   SE_TRY(grow(&g->partial, &g->partial_bytes, (size_t)g->ns * (g->n_pad / 32) * rows * g->esz));
   if (g->impl == SE_GEMM_TC) {
     const int64_t split_rows = rows < kSplitRows ? rows : kSplitRows;
-    SE_TRY(grow(&g->kpart, &g->kpart_bytes, (size_t)(g->n_pad / 128) * split_rows * g->ns * (1 + g->d) * sizeof(double)));
+    // two sets: the fused ellipsoid step reads one step's segment sums while the kernel rows of the next are written
+    SE_TRY(grow(&g->kpart, &g->kpart_bytes, 2 * kpart_set_bytes(g, split_rows)));
   }
   return 0;
 }
@@ -375,13 +379,15 @@ static PostPart post_part(se_gp_s* g, int64_t row0, int nrows, int64_t slot_row0
 
 template <typename T>
 static int post_kstar(se_gp_s* g, const GpDev<T>& gd, const PostPart& pp, const T* p, int64_t p_stride, const T* u,
-                      int64_t u_stride, T* mean, T* jac, cudaStream_t st) {
+                      int64_t u_stride, T* mean, T* jac, cudaStream_t st, const ProbDev<double>* fuse_pr = nullptr,
+                      const StepIO<double>* fuse_io = nullptr) {
   const bool tc = g->impl == SE_GEMM_TC;
   if (g->timing) SE_TRY(record_event(g->ev_kstar, st));
   if constexpr (sizeof(T) == 8) {
     if (tc)  // kernel rows as int8 digit planes (<= 8 bytes per element, like the float64 rows they replace)
       SE_TRY(launch_kstar_slices(gd, p, p_stride, u, u_stride, pp.row0, pp.nrows, pp.rows_pad, g->exp_ab,
-                                 g->tc_digits, (int8_t*)pp.kst, mean, jac, pp.seg_per_cta, (double*)pp.kpart, st));
+                                 g->tc_digits, (int8_t*)pp.kst, mean, jac, pp.seg_per_cta, (double*)pp.kpart, st,
+                                 fuse_pr, fuse_io));
   }
   if (!tc)
     SE_TRY(launch_kstar<T>(gd, p, p_stride, u, u_stride, pp.row0, pp.nrows, pp.rows_pad, (T*)pp.kst, mean, jac, st));
@@ -717,6 +723,7 @@ struct se_cem_s {
   int rank = 0, world = 1;
   // device buffers
   void *actions = nullptr, *p = nullptr, *q = nullptr, *objective = nullptr, *constraint = nullptr;
+  void *p2 = nullptr, *q2 = nullptr;  // second ellipsoid buffers: the fused step of small batches alternates them
   void *pack_local = nullptr, *pack_all = nullptr;
   double *mean = nullptr, *stdv = nullptr;  // [I + 1][M][T * nu]
   void* act_out = nullptr;                   // scratch outputs when the caller passes NULL
@@ -731,7 +738,7 @@ struct se_cem_s {
 
 extern "C" int se_cem_destroy(se_cem_t c) {
   if (!c) return 0;
-  for (void* p : {c->actions, c->p, c->q, c->objective, c->constraint, c->pack_local, c->pack_all, (void*)c->mean,
+  for (void* p : {c->actions, c->p, c->q, c->p2, c->q2, c->objective, c->constraint, c->pack_local, c->pack_all, (void*)c->mean,
                   (void*)c->stdv, c->act_out, (void*)c->found, (void*)c->best})
     if (p) cudaFree(p);
   if (c->seed_dev) cudaFree(c->seed_dev);
@@ -772,6 +779,8 @@ extern "C" int se_cem_create(se_cem_t* out, se_gp_t gp, const se_problem* prob, 
   alloc(&c->actions, cand * tnu * esz);
   alloc(&c->p, cand * ns * esz);
   alloc(&c->q, cand * ns * ns * esz);
+  alloc(&c->p2, cand * ns * esz);
+  alloc(&c->q2, cand * ns * ns * esz);
   alloc(&c->objective, cand * esz);
   alloc(&c->constraint, cand * esz);
   alloc(&c->pack_local, 2 * cand * esz);
@@ -844,6 +853,11 @@ static int cem_solve_t(se_cem_s* c, const ProbDev<T>& pr, const T* p0, const T* 
   // Models of at most 128 training points: the fused rollout kernel (SE_ROLLOUT_FUSED=0 keeps the four-kernel step).
   const int fused_env = getenv("SE_ROLLOUT_FUSED") ? atoi(getenv("SE_ROLLOUT_FUSED")) : 1;
   const bool fused = fused_env != 0 && g->n_pad == kSmallN && !g->timing && !g->impl_explicit;
+  // Small batches on the tensor-core path: the ellipsoid step rides on the next kernel-row launch (SE_STEP_FUSED=0 keeps
+  // the three-launch step)
+  const int step_env = getenv("SE_STEP_FUSED") ? atoi(getenv("SE_STEP_FUSED")) : 1;
+  const bool step_fused = step_env != 0 && !fused && !pipelined && sizeof(T) == 8 && g->impl == SE_GEMM_TC &&
+                          !g->timing && cand < kSplitRows && chunk_rows(g, cand) >= cand;
   if (phase & 1) {
     if (fused && !g->wt) {
       SE_CUDA(cudaMalloc(&g->wt, (size_t)ns * g->n_pad * g->n_pad * g->esz));
@@ -904,6 +918,43 @@ static int cem_solve_t(se_cem_s* c, const ProbDev<T>& pr, const T* p0, const T* 
       rio.rec_con = out->constraint ? (T*)out->constraint + (size_t)it * cand : nullptr;
       rio.rec_actions = rec_act, rio.traj = rec_traj, rio.flags = out->flags, rio.N = cand;
       SE_TRY(launch_rollout_small<T>(gp_dev<T>(g), (const T*)g->wt, pr, rio, st));
+    } else if (!pipelined && step_fused) {
+      // Small batches on the tensor-core path: two launches per horizon step.  The ellipsoid step of horizon step t - 1
+      // runs at the head of the kernel-row kernel of step t (gp_kstar_slices8_kernel<..., FUSE>), which takes the new
+      // centres from registers; ellipsoids and segment sums alternate between two buffers because every CTA that works
+      // on a candidate recomputes its step from the old ones.  Same arithmetic as the three-launch step below.
+      if constexpr (sizeof(T) == 8) {
+        const GpDev<T> gd = gp_dev<T>(g);
+        T* pb[2] = {p, (T*)c->p2};
+        T* qb[2] = {q, (T*)c->q2};
+        char* kp[2] = {(char*)g->kpart, (char*)g->kpart + g->kpart_bytes / 2};
+        auto step_io = [&](int t, const PostPart& pp) {  // the ellipsoid step of horizon step t, fed by pp's launches
+          StepIO<T> io = make_io(t, 0);
+          io.p_in = pb[t & 1], io.q_in = qb[t & 1], io.p_out = pb[(t + 1) & 1], io.q_out = qb[(t + 1) & 1];
+          io.partial = (const T*)pp.partial, io.nb = pp.nb, io.rows_pad = pp.rows_pad;
+          io.kpart = (const T*)pp.kpart, io.nseg = pp.nseg;
+          for (int o = 0; o < ns; ++o) {
+            io.gp_outputscale[o] = (T)g->outputscale[o], io.gp_noise[o] = (T)g->noise[o];
+            for (int dd = 0; dd < g->d; ++dd) io.gp_inv_l2[o][dd] = (T)g->inv_l2[o][dd];
+          }
+          return io;
+        };
+        PostPart prev;
+        for (int t = 0; t < T_len; ++t) {
+          PostPart pp = post_part<T>(g, 0, (int)cand, 0);
+          if (pp.nseg > 0) pp.kpart = kp[t & 1];
+          const T* u_t = actions + (int64_t)t * nu;
+          if (t == 0) {
+            SE_TRY(post_kstar<T>(g, gd, pp, p, ns, u_t, tnu, mean, nullptr, st));
+          } else {
+            const StepIO<T> io = step_io(t - 1, prev);
+            SE_TRY(post_kstar<T>(g, gd, pp, nullptr, ns, u_t, tnu, mean, jac, st, &pr, &io));
+          }
+          SE_TRY(post_gemm<T>(g, gd, pp, st));
+          prev = pp;
+        }
+        SE_TRY(launch_reach_step<T>(pr, step_io(T_len - 1, prev), (int)cand, st));
+      }
     } else if (!pipelined) {
       // per horizon step and workspace chunk: kernel rows -> variance GEMM -> ellipsoid step (which also reduces the
       // GEMM's partial sums, so there is no separate variance launch)
@@ -996,7 +1047,8 @@ static GraphKey graph_key(const se_cem_s* c, const void* p0, const void* noise, 
   static_assert(sizeof(ptrs) / sizeof(ptrs[0]) <= sizeof(k.ptr) / sizeof(k.ptr[0]), "GraphKey too small");
   for (size_t i = 0; i < sizeof(ptrs) / sizeof(ptrs[0]); ++i) k.ptr[i] = ptrs[i];
   k.val[0] = (int64_t)g->impl, k.val[1] = g->tc_digits, k.val[2] = (int64_t)g->ws_limit, k.val[3] = g->impl_explicit;
-  k.val[4] = getenv("SE_ROLLOUT_FUSED") ? atoi(getenv("SE_ROLLOUT_FUSED")) : 1;
+  k.val[4] = (getenv("SE_ROLLOUT_FUSED") ? atoi(getenv("SE_ROLLOUT_FUSED")) : 1) +
+             2 * (getenv("SE_STEP_FUSED") ? atoi(getenv("SE_STEP_FUSED")) : 1);
   k.val[5] = g->n_pad;
   return k;
 }

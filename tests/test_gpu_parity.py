@@ -631,3 +631,29 @@ def test_cuda_graph_replay_equals_plain_launches(n_train, monkeypatch):
     assert len(set(counts[1:])) == 1 and counts[1] > 0 and counts[0] >= counts[1]
     # different seeds really produce different candidates
     assert not torch.equal(plain[5]['objective'], plain[6]['objective'])
+
+
+@pytest.mark.parametrize('n_train,N,T_len', [(300, 256, 4), (400, 500, 5), (1000, 3000, 3), (300, 130, 1)])
+def test_fused_ellipsoid_step_equals_the_three_launch_step(n_train, N, T_len, monkeypatch):
+    """Small batches on the tensor-core path run the ellipsoid step of horizon step t - 1 at the head of the kernel-row
+    kernel of step t (two launches per step instead of three, ellipsoids alternating between two buffers): every
+    recorded quantity must equal the three-launch solve bit for bit -- with the training set split over CTAs
+    (N = 256, 500), without (N = 3000), and for a one-step horizon (no fused launch at all)."""
+    w = workloads.pendulum_workload(n_train=n_train, num_rollouts=N, time_horizon=T_len, num_elites=8, num_iterations=3)
+    p0 = G(w.p0).unsqueeze(0)
+    lib = _lib.load()
+    out = {}
+    launches = {}
+    for mode in ('0', '1'):
+        monkeypatch.setenv('SE_STEP_FUSED', mode)
+        monkeypatch.setenv('SE_CEM_GRAPH', '0')
+        ssm, mpc = workloads.build_solver(w, record='full', seed=0)
+        mpc.solve(p0, seed=3)  # model preparation out of the way
+        lib.se_launch_count_reset()
+        out[mode] = {k: v.clone() for k, v in mpc.solve(p0, seed=4).items()}
+        torch.cuda.synchronize()
+        launches[mode] = int(lib.se_launch_count())
+    for k, v in out['0'].items():
+        assert torch.equal(out['1'][k], v, ), k
+    if T_len > 1:  # one launch less per horizon step but the last, in each of the 3 iterations
+        assert launches['0'] - launches['1'] == 3 * (T_len - 1)
