@@ -275,7 +275,7 @@ def run_b200(args):
         e2e_sec = float(t.item())
     esz = 8 if args.dtype == 'f64' else 4
     e2e = {'value': cand_steps / e2e_sec, 'unit': UNIT, 'ms_per_solve': e2e_sec * 1e3,
-           'h2d_bytes_per_step': w.n_s * esz, 'd2h_bytes_per_step': w.time_horizon * w.n_u * esz + 4 + 16,
+           'h2d_bytes_per_step': w.n_s * esz, 'd2h_bytes_per_step': w.time_horizon * w.n_u * esz + 8 + 16,
            'api': 'B200CemSafeMPC.get_action(ndarray) -> (ndarray, MpcResult)'}
 
     # ---- roofline of the dominant kernel (variance GEMM) ----

@@ -211,12 +211,20 @@ class B200ConstrainedCemMpc:
         cached = self._out_cache.get(cache_key) if reuse_outputs else None
         if cached is not None:
             res, p0_buf = cached
-            p0_buf.copy_(p0)
+            if p0.data_ptr() != p0_buf.data_ptr():
+                p0_buf.copy_(p0)
             p0 = p0_buf
         else:
-            res = dict(actions=new((M, T, n_u)), found=new((M,), torch.int32), best_id=new((M,), torch.int32),
+            # actions | found | best_id | flags share one allocation, so a caller that only wants the outcome of the
+            # solve (get_actions_point) reads it back with a single device -> host copy
+            esz = torch.empty((), dtype=dt).element_size()
+            a_bytes = M * T * n_u * esz
+            pack = torch.zeros(a_bytes + 8 * M + 16, dtype=torch.uint8, device=dev)
+            res = dict(actions=pack[:a_bytes].view(dt).view(M, T, n_u),
+                       found=pack[a_bytes:a_bytes + 4 * M].view(torch.int32),
+                       best_id=pack[a_bytes + 4 * M:a_bytes + 8 * M].view(torch.int32),
                        means=new((I, M, T, n_u)), stds=new((I, M, T, n_u)), elite_ids=new((I, M, E), torch.int32),
-                       flags=torch.zeros(4, dtype=torch.int32, device=dev))
+                       flags=pack[a_bytes + 8 * M:].view(torch.int32), _pack=pack)
             if self.record in ('full', 'costs'):
                 res['objective'] = new((I, M, n_local))
                 res['constraint'] = new((I, M, n_local))
@@ -243,6 +251,42 @@ class B200ConstrainedCemMpc:
         if sync:
             check_flags(res['flags'].cpu(), 'CEM rollouts')
         return res
+
+    def get_actions_point(self, state) -> Optional['np.ndarray']:
+        """What CemSafeMPC.get_action needs from get_actions (safempc_cem.py:236-241) for a POINT state given on the
+        host: the action sequence [T, n_u] of a feasible rollout of the last iteration as a NumPy array, or None.
+        One pinned host -> device copy of the state, one device -> host copy of (actions, found, flags), one stream
+        synchronisation; no per-iteration records are exposed (use get_actions for those)."""
+        import numpy as np
+        ssm = self._ssm
+        n_s, T, n_u = ssm.num_states, self._time_horizon, ssm.num_actions
+        dev, dt = ssm.device, ssm.dtype
+        n_local = self._num_rollouts // self.world_size
+        cached = self._out_cache.get((1, self.record, dt, str(dev), n_local))
+        stage = getattr(self, '_point_stage', None)
+        if cached is None or stage is None or stage[2] is not cached[0]['_pack']:
+            # first call (or new buffers): the general path creates the persistent buffers
+            p0 = torch.as_tensor(np.asarray(state, dtype=np.float64).reshape(1, n_s), dtype=dt, device=dev)
+            res = self.solve(p0, sync=True, reuse_outputs=True)
+            self.last_info = res
+            pack = res['_pack']
+            self._point_stage = (torch.empty((1, n_s), dtype=dt).pin_memory(),
+                                 torch.empty(pack.numel(), dtype=torch.uint8).pin_memory(), pack)
+            return res['actions'][0].cpu().numpy() if int(res['found'][0]) == 1 else None
+        res, p0_buf = cached
+        h_p0, h_pack, pack = stage
+        h_p0.numpy()[0, :] = np.asarray(state, dtype=np.float64).reshape(n_s)
+        p0_buf.copy_(h_p0, non_blocking=True)
+        res = self.solve(p0_buf, sync=False, reuse_outputs=True)
+        self.last_info = res
+        h_pack.copy_(pack, non_blocking=True)
+        torch.cuda.current_stream(dev).synchronize()
+        a_bytes = T * n_u * h_p0.element_size()
+        tail = h_pack[a_bytes:].view(torch.int32)  # found, best_id, flags[4]
+        check_flags(tail[2:], 'CEM rollouts')
+        if int(tail[0]) != 1:
+            return None
+        return h_pack[:a_bytes].view(dt).view(T, n_u).numpy().copy()
 
     def _flat_state_to_p0(self, state: Tensor) -> Tensor:
         n_s = self._ssm.num_states

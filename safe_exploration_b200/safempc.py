@@ -310,10 +310,14 @@ class B200CemSafeMPC(SafeMPC):
     def get_action(self, state: ndarray) -> Tuple[ndarray, MpcResult]:
         """safempc_cem.py:231-263."""
         assert_shape(state, (self._state_dimen,))
-        state_batch = torch.tensor(state, dtype=self._ssm.dtype, device=self._ssm.device).unsqueeze(0)
-        # results are consumed right here, so the solver may reuse its buffers (-> the library replays its CUDA graph)
-        mpc_actions, _ = self._mpc.get_actions(self._pq_flattener.flatten(state_batch, None), reuse_outputs=True)
-        mpc_actions = mpc_actions.detach().cpu().numpy() if mpc_actions is not None else mpc_actions
+        if hasattr(self._mpc, 'get_actions_point'):
+            # point state in, plan out: one small copy each way (the solver reuses its buffers, so the library replays
+            # its CUDA graph of the solve)
+            mpc_actions = self._mpc.get_actions_point(state)
+        else:
+            state_batch = torch.tensor(state, dtype=self._ssm.dtype, device=self._ssm.device).unsqueeze(0)
+            mpc_actions, _ = self._mpc.get_actions(self._pq_flattener.flatten(state_batch, None), reuse_outputs=True)
+            mpc_actions = mpc_actions.detach().cpu().numpy() if mpc_actions is not None else mpc_actions
         if mpc_actions is not None:
             self._say('Found solution')
             action = mpc_actions[0]

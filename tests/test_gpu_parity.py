@@ -657,3 +657,21 @@ def test_fused_ellipsoid_step_equals_the_three_launch_step(n_train, N, T_len, mo
         assert torch.equal(out['1'][k], v, ), k
     if T_len > 1:  # one launch less per horizon step but the last, in each of the 3 iterations
         assert launches['0'] - launches['1'] == 3 * (T_len - 1)
+
+
+def test_get_actions_point_equals_get_actions():
+    """The host-state fast path of B200CemSafeMPC.get_action (one copy each way, persistent buffers, graph replay)
+    returns exactly what get_actions returns for the same seeds, call after call, including 'nothing feasible'."""
+    w = workloads.pendulum_workload(n_train=100, num_rollouts=256, time_horizon=4, num_elites=8, num_iterations=3)
+    ssm, mpc_a = workloads.build_solver(w, record='costs', seed=20)
+    _, mpc_b = workloads.build_solver(w, record='costs', seed=20)
+    flat = se.PQFlattener(2)
+    states = [np.asarray(w.p0, dtype=np.float64), np.array([0.02, -0.03]), np.array([5.0, 5.0]), np.array([-0.01, 0.01])]
+    for s in states:  # every solve draws the next seed (20, 21, ...) in both objects
+        want, _ = mpc_a.get_actions(flat.flatten(G(s).unsqueeze(0), None))
+        got = mpc_b.get_actions_point(s)
+        if want is None:
+            assert got is None
+        else:
+            assert got is not None and np.array_equal(got, want.cpu().numpy())
+    assert any(mpc_a.get_actions(flat.flatten(G(s).unsqueeze(0), None))[0] is None for s in states[2:3])
