@@ -12,7 +12,19 @@ if ROOT not in sys.path:
 GOLDEN = os.path.join(ROOT, 'tests', 'golden')
 
 
+def _ensure_library():
+    """The C-ABI tests load safe_exploration_b200/libsecem.so; build it if this checkout has not been built yet
+    (nvcc cross-compiles without a GPU, ~2 min).  The library is never replaced by a CPU path: a failed build fails
+    the tests that need it."""
+    lib = os.path.join(ROOT, 'safe_exploration_b200', 'libsecem.so')
+    if not os.path.exists(lib):
+        import subprocess
+        subprocess.run(['make', '-C', os.path.join(ROOT, 'safe_exploration_b200', 'csrc'), '-j',
+                        str(max(1, min(8, os.cpu_count() or 1)))], capture_output=True)
+
+
 def pytest_configure(config):
+    _ensure_library()
     config.addinivalue_line('markers', 'gpu: needs a CUDA device (B200); run with -m gpu')
     torch.set_default_dtype(torch.double)  # like the reference's hot-path test modules
 
