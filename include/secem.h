@@ -275,9 +275,11 @@ int se_gp_timing_read(se_gp_t gp, double* gemm_ms, int64_t* gemm_launches, doubl
 int se_debug_tc_probe(const int8_t* dev_a_img, const int8_t* dev_b_img, int nk, int digits, int lbo, int sbo,
                       int32_t* dev_out, void* stream);
 
-/* Test hook: out[i] = the branch-free double exp() the kernel-row kernels use (csrc/common.cuh exp_nb, polynomial from
+/* Test hook: out[i] = the branch-free double exp() of the model-refresh gradient kernel (csrc/common.cuh exp_nb, polynomial from
  * tools/exp_poly.py), for finite dev_x[i] <= 700.  Lets a test pin its accuracy against a libm exp. */
 int se_debug_exp(const double* dev_x, int64_t n, double* dev_out, void* stream);
+/* The same for the table-based variant (csrc/common.cuh exp_tab) of the kernel-row kernel of the tensor-core path. */
+int se_debug_exp_table(const double* dev_x, int64_t n, double* dev_out, void* stream);
 
 #ifdef __cplusplus
 }

@@ -58,6 +58,7 @@ SIGNATURES = {
     "se_gp_get_gemm_info": (_i, [_vp, C.POINTER(_i), C.POINTER(_i)]),
     "se_debug_tc_probe": (_i, [_vp, _vp, _i, _i, _i, _i, _vp, _vp]),
     "se_debug_exp": (_i, [_vp, _i64, _vp, _vp]),
+    "se_debug_exp_table": (_i, [_vp, _i64, _vp, _vp]),
     "se_gp_predict": (_i, [_vp, _vp, _i64, _vp, _vp, _vp, _vp]),
     "se_gp_kernel_matrix": (_i, [_i, _i, _i64, _vp, _dbl_p, _dbl_p, _dbl_p, _vp, _vp]),
     "se_gp_mll_grad_workspace": (_i64, [_i, _i, _i64]),

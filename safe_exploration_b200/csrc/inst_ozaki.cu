@@ -168,13 +168,16 @@ int launch_oz_probe(const int8_t* a_img, const int8_t* b_img, int nk, int S, int
   return fail("probe: S = %d not compiled", S);
 }
 
-static __global__ void debug_exp_kernel(const double* __restrict__ x, int64_t n, double* __restrict__ out) {
+static __global__ void debug_exp_kernel(const double* __restrict__ x, int64_t n, double* __restrict__ out, int table) {
   const int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
-  if (i < n) out[i] = exp_nb(x[i]);
+  __shared__ double etab[64];
+  if (threadIdx.x < 64) etab[threadIdx.x] = kExpTab[threadIdx.x];
+  __syncthreads();
+  if (i < n) out[i] = table ? exp_tab(x[i], etab) : exp_nb(x[i]);
 }
-int launch_debug_exp(const double* x, int64_t n, double* out, cudaStream_t stream) {
+int launch_debug_exp(const double* x, int64_t n, double* out, int table, cudaStream_t stream) {
   if (n <= 0) return 0;
-  SE_LAUNCH(debug_exp_kernel, (int)ceil_div(n, (int64_t)256), 256, 0, stream, x, n, out);
+  SE_LAUNCH(debug_exp_kernel, (int)ceil_div(n, (int64_t)256), 256, 0, stream, x, n, out, table);
   return 0;
 }
 

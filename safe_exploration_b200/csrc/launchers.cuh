@@ -78,7 +78,7 @@ int launch_trisumsq_ozaki(const int8_t* a_img, const int8_t* b_img, const double
                           int rows_pad, int ns, int S, double* partial, int sm_count, int* nb_out, cudaStream_t stream);
 int launch_oz_probe(const int8_t* a_img, const int8_t* b_img, int nk, int S, int lbo, int sbo, int32_t* out,
                     cudaStream_t stream);
-int launch_debug_exp(const double* x, int64_t n, double* out, cudaStream_t stream);
+int launch_debug_exp(const double* x, int64_t n, double* out, int table, cudaStream_t stream);
 
 }  // namespace se
 

@@ -502,6 +502,8 @@ gp_kstar_slices8_kernel(GpDev<double> gp, const double* __restrict__ p, int64_t 
   // ptxas sinks any register prefetch to the end of the loop body.
   constexpr int CH = 128;  // points per chunk: 1 KB per array
   __shared__ __align__(16) double stage[2][D + NS][CH];
+  __shared__ double etab[64];  // exp_tab's table; published by the first barrier of the chunk loop
+  if (threadIdx.x < 64) etab[threadIdx.x] = kExpTab[threadIdx.x];
   auto fill = [&](int chunk, int buf) {
 #pragma unroll
     for (int a = 0; a < D + NS; ++a) {
@@ -557,7 +559,7 @@ gp_kstar_slices8_kernel(GpDev<double> gp, const double* __restrict__ p, int64_t 
         double arg = log_s[o];
 #pragma unroll
         for (int dd = 0; dd < D; ++dd) arg = fma(sq[dd], nh_inv_l2[o][dd], arg);
-        const double k = exp_nb(arg);
+        const double k = exp_tab(arg, etab);
         q[o][e] = __double2ll_rn(k * qscale[o]);
         const double wk = al[o][e] * k;
         m_acc[o] += wk;

@@ -256,7 +256,11 @@ extern "C" int se_debug_tc_probe(const int8_t* dev_a_img, const int8_t* dev_b_im
 
 extern "C" int se_debug_exp(const double* dev_x, int64_t n, double* dev_out, void* stream) {
   SE_REQUIRE(n >= 0 && (n == 0 || (dev_x && dev_out)), "se_debug_exp: bad arguments");
-  return launch_debug_exp(dev_x, n, dev_out, static_cast<cudaStream_t>(stream));
+  return launch_debug_exp(dev_x, n, dev_out, 0, static_cast<cudaStream_t>(stream));
+}
+extern "C" int se_debug_exp_table(const double* dev_x, int64_t n, double* dev_out, void* stream) {
+  SE_REQUIRE(n >= 0 && (n == 0 || (dev_x && dev_out)), "se_debug_exp_table: bad arguments");
+  return launch_debug_exp(dev_x, n, dev_out, 1, static_cast<cudaStream_t>(stream));
 }
 
 extern "C" int se_gp_timing_enable(se_gp_t g, int enable) {

@@ -206,24 +206,27 @@ def test_tc_cem_solve_matches_oracle(pipeline, monkeypatch):
     assert int(res['best_id'][0]) == ref['best_id']
 
 
-def test_branch_free_exp_is_within_two_ulp_of_libm():
-    """csrc/common.cuh exp_nb (the exp of the kernel-row kernels): <= 2 ulp against numpy's exp over the range the
-    kernel rows use, exact powers at the reduction boundaries, and the clamp below -700 stays tiny and positive."""
+@pytest.mark.parametrize('hook', ['se_debug_exp', 'se_debug_exp_table'])
+def test_branch_free_exp_is_within_two_ulp_of_libm(hook):
+    """csrc/common.cuh exp_tab (the table-based exp of the kernel-row kernel) and exp_nb (the polynomial one of the
+    model-refresh gradient kernel): <= 2 ulp against numpy's exp over the range the kernel rows use, exact powers at the
+    reduction boundaries, and the clamp below -700 stays tiny and positive."""
     lib = _lib.load()
+    debug_exp = getattr(lib, hook)
     rng = np.random.default_rng(7)
     x = np.concatenate([rng.uniform(-60.0, 2.0, 400000), rng.uniform(-700.0, 700.0, 100000),
                         np.array([0.0, -0.0, 1e-300, -1e-300, np.log(2.0) / 2, -np.log(2.0) / 2, -699.999, 699.999]),
-                        np.arange(-1000, 1001) * np.log(2.0) / 2])
+                        np.arange(-1000, 1001) * np.log(2.0) / 2, np.arange(-40000, 40001, 7) * np.log(2.0) / 128])
     x = x[(x > -700.0) & (x < 700.0)]
     dx = torch.from_numpy(x).to(DEV)
     out = torch.empty_like(dx)
-    _lib.check(lib.se_debug_exp(_lib.ptr(dx), x.size, _lib.ptr(out), _lib.stream_ptr(DEV)))
+    _lib.check(debug_exp(_lib.ptr(dx), x.size, _lib.ptr(out), _lib.stream_ptr(DEV)))
     got, want = out.cpu().numpy(), np.exp(x)
     ulp = np.abs(got - want) / np.spacing(want)
     assert ulp.max() <= 2.0, (ulp.max(), x[ulp.argmax()])
     tiny = torch.tensor([-700.0, -750.0, -1e5, -1e300, -np.inf], dtype=torch.float64, device=DEV)
     out = torch.empty_like(tiny)
-    _lib.check(lib.se_debug_exp(_lib.ptr(tiny), tiny.numel(), _lib.ptr(out), _lib.stream_ptr(DEV)))
+    _lib.check(debug_exp(_lib.ptr(tiny), tiny.numel(), _lib.ptr(out), _lib.stream_ptr(DEV)))
     o = out.cpu().numpy()
     assert np.all(o > 0) and np.all(o < 1e-300)
 
