@@ -184,10 +184,20 @@ def test_exp_polynomial_in_the_kernel_source_is_the_derived_one():
     spec.loader.exec_module(mod)
     coef = mod.coefficients()
     src = open(os.path.join(root, 'safe_exploration_b200', 'csrc', 'common.cuh')).read()
-    body = src[src.index('double exp_nb(double x)'):src.index('finite_f64')]
+    body = src[src.index('double exp_nb(double x)'):src.index('// The same contract as exp_nb')]
     got = [float(body[body.index('double p = ') + 11:].split(';')[0])]
     got += [float(v) for v in re.findall(r'p = fma\(p, r, ([0-9.e+-]+)\);', body)]
     assert got == coef[::-1]
+    # exp_tab: the 64 table entries are 2^(j/64) correctly rounded, the reduction constants are 64 / ln 2 and ln 2 / 64
+    from decimal import Decimal, getcontext
+    getcontext().prec = 60
+    ln2 = Decimal(2).ln()
+    tab_src = src[src.index('kExpTab[64] = {') + 15:]
+    tab = [float(v) for v in tab_src[:tab_src.index('}')].replace('\n', ' ').split(',')]
+    assert tab == [float((ln2 * j / 64).exp()) for j in range(64)]
+    body = src[src.index('double exp_tab(double x'):src.index('finite_f64')]
+    hi = float(ln2 / 64)
+    assert repr(float(Decimal(64) / ln2)) in body and repr(hi) in body and repr(float(ln2 / 64 - Decimal(hi))) in body
 
 
 class _PendulumEnv:
