@@ -122,6 +122,41 @@ class ClockSampler:
         self._thread = threading.Thread(target=self._run, daemon=True)
 
     def _run(self):
+        if not self._run_nvml():
+            self._run_smi()
+
+    def _run_nvml(self) -> bool:
+        """In-process NVML (nvidia_ml_py): ~1 ms per sample, so even a 0.5 s timed region is sampled dozens of times."""
+        try:
+            import pynvml as nv
+            nv.nvmlInit()
+            vis = os.environ.get('CUDA_VISIBLE_DEVICES')
+            idx = self.index
+            if vis and len(vis.split(',')) > self.index and vis.split(',')[self.index].strip().isdigit():
+                idx = int(vis.split(',')[self.index])
+            h = nv.nvmlDeviceGetHandleByIndex(idx)
+            self.max_mhz = float(nv.nvmlDeviceGetMaxClockInfo(h, nv.NVML_CLOCK_SM))
+            const = lambda name: getattr(nv, 'nvmlClocksEventReason' + name, None) or \
+                getattr(nv, 'nvmlClocksThrottleReason' + name)
+            bits = {'hw_slowdown': const('HwSlowdown'), 'hw_thermal_slowdown': const('HwThermalSlowdown'),
+                    'sw_thermal_slowdown': const('SwThermalSlowdown'), 'sw_power_cap': const('SwPowerCap')}
+            get_reasons = getattr(nv, 'nvmlDeviceGetCurrentClocksEventReasons', None) or \
+                nv.nvmlDeviceGetCurrentClocksThrottleReasons
+        except Exception:
+            return False
+        while not self._stop.is_set():
+            try:
+                self.samples.append(float(nv.nvmlDeviceGetClockInfo(h, nv.NVML_CLOCK_SM)))
+                mask = int(get_reasons(h))
+                for n, bit in bits.items():
+                    if mask & int(bit):
+                        self.reasons.add(n)
+            except Exception:
+                pass
+            self._stop.wait(0.02)
+        return True
+
+    def _run_smi(self):
         q = ('clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,'
              'clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap')
         names = ['hw_slowdown', 'hw_thermal_slowdown', 'sw_thermal_slowdown', 'sw_power_cap']
