@@ -153,6 +153,13 @@ typedef struct {
   int m_obs;               /* faces of h_mat_obs x <= h_vec_obs, at most SE_MAX_OBS_FACES                  */
   const double* h_mat_obs; /* [m_obs, n_s]                                                                 */
   const double* h_vec_obs; /* [m_obs]                                                                      */
+  /* _fix_zeros_nans (gp_reachability_pytorch.py:234-243) sets EVERY x <= 0 of a batch to 1e-5 when the batch holds an
+   * exact zero.  se_reach_onestep / se_reach_multistep / se_reach_step apply that rule to the batch they are given
+   * (they scan it first).  Inside se_cem_solve the "batch" of the reference (all candidates of one step) never exists
+   * in one place, so the rule is a switch: 0 = only exact zeros are replaced, a negative variance surfaces as NaN at
+   * the next sqrt and the solve reports it (flags[0]) -- what the reference does when the batch holds no exact zero;
+   * 1 = every variance <= 0 becomes 1e-5 and is counted in flags[1] -- what it does when one is present. */
+  int clamp_nonpositive;
 } se_problem;
 
 /* ---------------------------------------------------------------------------------------------------------------
@@ -164,10 +171,20 @@ typedef struct {
  * sum_two_ellipsoids_pytorch (utils_ellipsoid.py:102-140, 282-309) and _fix_zeros_nans (:234-243).
  *   dev_p [N, n_s]; dev_q [N, n_s, n_s] or NULL (point states); dev_u [N, n_u] (= k_ff)
  *   dev_p1 [N, n_s], dev_q1 [N, n_s, n_s], dev_sigma [N, n_s]
- *   dev_flags: int32[4] device counters, incremented: [0] #NaN variances, [1] #exact-zero variances / bounds
- *              (the reference raises / warns on these; the Python wrapper reads them after the call) */
+ *   dev_flags: int32[4] device counters, incremented: [0] #NaN variances, [1] #variances / bounds replaced by 1e-5
+ *              (the reference raises / warns on these; the Python wrapper reads them after the call); [2] is scratch
+ *              ("the batch of the last step held an exact zero") */
 int se_reach_onestep(se_gp_t gp, const se_problem* prob, const void* dev_p, const void* dev_q, const void* dev_u,
                      int64_t N, void* dev_p1, void* dev_q1, void* dev_sigma, int32_t* dev_flags, void* stream);
+
+/* The ellipsoid algebra of one step alone, for a posterior the CALLER evaluated: the interface fallback for a CemSSM
+ * that is not the B200 GP (e.g. the MC-dropout models of ssm_cem/dropout_ssm_cem.py): the host calls
+ * ssm.predict_with_jacobians / predict_without_jacobians (ssm_cem.py:36-58) on device tensors and hands the result
+ * here.  Same arithmetic as se_reach_onestep after its GP stage (gp_reachability_pytorch.py:76-181).
+ *   dev_mean [N, n_s], dev_var [N, n_s], dev_jac [N, n_s, n_s + n_u] (ignored when dev_q == NULL: point branch) */
+int se_reach_step(se_dtype dtype, const se_problem* prob, const void* dev_p, const void* dev_q, const void* dev_u,
+                  const void* dev_mean, const void* dev_var, const void* dev_jac, int64_t N, void* dev_p1,
+                  void* dev_q1, void* dev_sigma, int32_t* dev_flags, void* stream);
 
 /* T steps for N ellipsoids: the loop of RolloutFunction._sample_trajectory (constrained_cem_mpc.py:175-183) with the
  * dynamics of CemSafeMPC._dynamics_func, equivalently the NumPy multistep_reachability
@@ -250,6 +267,13 @@ int se_cem_noise(se_dtype dtype, uint64_t seed, int iteration, int num_instances
 int se_cem_select_refit(se_dtype dtype, const void* dev_objective, const void* dev_constraint,
                         const void* dev_actions, int N, int T, int n_u, int E, int32_t* dev_elite_ids,
                         void* dev_mean, void* dev_std, void* stream);
+
+/* The return value of get_actions alone (constrained_cem_mpc.py:272-280) on given costs [N]: dev_best_id[0] = the
+ * first rollout with constraint cost 0 (quirk Q3; pick_best != 0: the one of lowest objective, ties by index), -1 if
+ * none.  With se_cem_noise and se_cem_select_refit this is what the interface fallback of B200ConstrainedCemMpc
+ * (arbitrary Python DynamicsFunc / Constraint objects) runs on the device. */
+int se_cem_pick(se_dtype dtype, const void* dev_objective, const void* dev_constraint, int N, int pick_best,
+                int32_t* dev_best_id, void* stream);
 
 /* ---------------------------------------------------------------------------------------------------------------
  * Measurement helpers (bench.py): launch counter and pipe-peak micro-benchmarks.

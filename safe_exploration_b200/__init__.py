@@ -13,13 +13,15 @@ Drop-in for the hot path of oscarkey/safe-exploration behind the reference's own
 All numerics run in libsecem.so (csrc/, C ABI in include/secem.h); there is no CPU fallback.
 """
 from ._lib import SE_F32, SE_F64, SE_GEMM_AUTO, SE_GEMM_MMA, SE_GEMM_SIMT, SecemError, load as load_library
-from .cem import (ActionConstraint, B200ConstrainedCemMpc, Constraint, DynamicsFunc, Rollouts, TorchPolytope,
-                  box2torchpoly, sample_noise, select_elites_refit)
+from .cem import (ActionConstraint, B200ConstrainedCemMpc, Constraint, DynamicsFunc, DynamicsFuncWrapper,
+                  RolloutFunction, Rollouts, TorchPolytope, box2torchpoly, pick_rollout, sample_noise,
+                  select_elites_refit)
 from .reachability import (SafeProblem, is_ellipsoid_inside_polytope, lin_ellipsoid_safety_distance,
                            multistep_reachability, onestep_reachability)
 from .safempc import (B200CemSafeMPC, B200SafeDynamics, EllipsoidObstacleConstraint, EllipsoidStateConstraint,
                       EllipsoidTerminalConstraint,
-                      LqrFeedbackController, MpcResult, PQFlattener, SafeMPC, construct_constraints, dlqr)
+                      LqrFeedbackController, MpcResult, PQFlattener, SafeMPC, classify_objective,
+                      construct_constraints, dlqr)
 from .ssm import B200GpCemSSM, CemSSM, assert_shape
 from .utils_config import create_cem_ssm, create_solver
 

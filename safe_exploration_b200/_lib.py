@@ -29,7 +29,7 @@ class SeProblem(C.Structure):
                 ("h_vec", _dbl_p), ("m_act", C.c_int), ("act_a", _dbl_p), ("act_b", _dbl_p),
                 ("act_penalty", C.c_double), ("state_penalty", C.c_double), ("objective", C.c_int),
                 ("objective_theta", C.c_double), ("all_states_constraint", C.c_int), ("m_obs", C.c_int),
-                ("h_mat_obs", _dbl_p), ("h_vec_obs", _dbl_p)]
+                ("h_mat_obs", _dbl_p), ("h_vec_obs", _dbl_p), ("clamp_nonpositive", C.c_int)]
 
 
 class SeCemConfig(C.Structure):
@@ -64,6 +64,7 @@ SIGNATURES = {
     "se_gp_mll_grad_workspace": (_i64, [_i, _i, _i64]),
     "se_gp_mll_grad": (_i, [_i, _i, _i64, _vp, _vp, _vp, _dbl_p, _dbl_p, _dbl_p, _vp, _vp, _vp]),
     "se_reach_onestep": (_i, [_vp, C.POINTER(SeProblem), _vp, _vp, _vp, _i64, _vp, _vp, _vp, _vp, _vp]),
+    "se_reach_step": (_i, [_i, C.POINTER(SeProblem), _vp, _vp, _vp, _vp, _vp, _vp, _i64, _vp, _vp, _vp, _vp, _vp]),
     "se_reach_multistep": (_i, [_vp, C.POINTER(SeProblem), _vp, _vp, _vp, _i64, _i, _dbl_p, _vp, _vp, _vp, _vp, _vp,
                                 _vp, _vp]),
     "se_safety_distance": (_i, [_i, _i, _i, _dbl_p, _dbl_p, _d, _vp, _vp, _i64, _vp, _vp, _vp]),
@@ -76,6 +77,7 @@ SIGNATURES = {
     "se_cem_solve": (_i, [_vp, _vp, _vp, _u64, C.POINTER(SeCemOutputs), _vp]),
     "se_cem_noise": (_i, [_i, _u64, _i, _i, _i, _i, _i, _i, _i, _vp, _vp]),
     "se_cem_select_refit": (_i, [_i, _vp, _vp, _vp, _i, _i, _i, _i, _vp, _vp, _vp, _vp]),
+    "se_cem_pick": (_i, [_i, _vp, _vp, _i, _i, _vp, _vp]),
     "se_launch_count": (_u64, []),
     "se_launch_count_reset": (None, []),
     "se_measure_peak": (_i, [_i, _dbl_p]),

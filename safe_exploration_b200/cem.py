@@ -80,6 +80,12 @@ class ActionConstraint(Constraint):
     def __call__(self, trajectory: Tensor, actions: Tensor) -> float:
         return self._penalty * (actions.shape[0] - self._self_region.contains_points(actions))
 
+    def batch_call(self, trajectories: Tensor, actions: Tensor) -> Tensor:
+        """The same rule for all rollouts at once: actions [N, T, n_u] -> costs [N] (device tensor ops)."""
+        region = self._self_region
+        viol = (torch.matmul(actions, region._A.to(actions).t()) - region._b.to(actions)) > 0
+        return self._penalty * viol.any(dim=2).sum(dim=1).to(actions.dtype)
+
 
 class DynamicsFunc(ABC):
     """constrained_cem_mpc.py:113-124."""
@@ -89,36 +95,108 @@ class DynamicsFunc(ABC):
         pass
 
 
+class DynamicsFuncWrapper(DynamicsFunc):
+    """Wraps a function as a DynamicsFunc (safempc_cem.py:149-156)."""
+
+    def __init__(self, func):
+        self._func = func
+
+    def __call__(self, states: Tensor, actions: Tensor) -> Tuple[Tensor, Tensor]:
+        return self._func(states, actions)
+
+
+class RolloutFunction:
+    """The reference's RolloutFunction (constrained_cem_mpc.py:130-192) on DEVICE tensors: the interface path of
+    `B200ConstrainedCemMpc` for dynamics / constraints that are arbitrary Python objects.  The candidates
+    are drawn by the library's sampler (`se_cem_noise`, Philox keyed by seed / iteration / rollout id), the dynamics
+    callback is called T times with [N, S] device tensors exactly as in the reference, constraints that know how to
+    evaluate a whole batch (`batch_call`) do so on the device and any other `Constraint` is called per rollout like the
+    reference does (:187-192)."""
+
+    def __init__(self, dynamics: DynamicsFunc, constraints: Sequence[Constraint], state_dimen: int, action_dimen: int,
+                 time_horizon: int, num_rollouts: int, seed: int = 0):
+        self._dynamics = dynamics
+        self._constraints = list(constraints)
+        self._state_dimen = state_dimen
+        self._action_dimen = action_dimen
+        self._time_horizon = time_horizon
+        self._num_rollouts = num_rollouts
+        self.seed = int(seed)
+        self.iteration = 0   # set by the optimiser before every call (the sampler's counter)
+        self.noise = None    # optional RNG-fixed standard-normal noise [N, T, n_u] of the next call
+
+    def perform_rollouts(self, args: Tuple[Tensor, Tensor, Tensor]) -> Rollouts:
+        """(initial_state [S], means [T, n_u], stds [T, n_u]) -> Rollouts (:145-156)."""
+        initial_state, means, stds = args
+        _lib.require_cuda(initial_state, 'initial_state')
+        initial_states = initial_state.reshape(1, -1).repeat((self._num_rollouts, 1))
+        trajectories, actions, objective_costs = self._sample_trajectory(initial_states, means, stds)
+        constraint_costs = self._compute_constraint_costs(trajectories, actions)
+        return Rollouts(trajectories, actions, objective_costs, constraint_costs)
+
+    def _sample_trajectory(self, initial_states: Tensor, means: Tensor, stds: Tensor):
+        N, T, n_u, S = self._num_rollouts, self._time_horizon, self._action_dimen, self._state_dimen
+        assert_shape(initial_states, (N, S))
+        assert_shape(means, (T, n_u))
+        assert_shape(stds, (T, n_u))
+        dt, dev = initial_states.dtype, initial_states.device
+        eps = self.noise if self.noise is not None else \
+            sample_noise(self.seed, self.iteration, 1, N, 0, N, T, n_u, dtype=dt, device=dev)[0]
+        assert_shape(eps, (N, T, n_u))
+        # Normal(means, stds).sample((N,)) == means + stds * eps  (:167)
+        actions = means.to(dt).unsqueeze(0) + stds.to(dt).unsqueeze(0) * eps.to(device=dev, dtype=dt)
+        rollout_batch = getattr(self._dynamics, 'rollout_batch', None)
+        if rollout_batch is not None:
+            out = rollout_batch(initial_states, actions)  # all T steps in one device call when the dynamics can
+            if out is not None:
+                return out[0], actions, out[1]
+        trajectories = torch.empty((N, T + 1, S), dtype=dt, device=dev)
+        trajectories[:, 0, :] = initial_states
+        objective_costs = torch.zeros((N,), dtype=dt, device=dev)
+        for t in range(T):
+            next_states, costs = self._dynamics(trajectories[:, t, :], actions[:, t, :])
+            assert_shape(next_states, (N, S))
+            assert_shape(costs, (N,))
+            trajectories[:, t + 1, :] = next_states
+            objective_costs += costs.to(dt)
+        return trajectories, actions, objective_costs
+
+    def _compute_constraint_costs(self, trajectories: Tensor, actions: Tensor) -> Tensor:
+        N = trajectories.shape[0]
+        costs = torch.zeros((N,), dtype=trajectories.dtype, device=trajectories.device)
+        for constraint in self._constraints:
+            batch = getattr(constraint, 'batch_call', None)
+            if batch is not None:
+                costs += batch(trajectories, actions).to(costs)
+            else:  # an arbitrary Constraint: one call per rollout, as the reference does (:187-192)
+                costs += torch.as_tensor([float(constraint(trajectories[i], actions[i])) for i in range(N)],
+                                         dtype=costs.dtype, device=costs.device)
+        return costs
+
+
 class B200ConstrainedCemMpc:
-    """Drop-in for `ConstrainedCemMpc` whose dynamics are GP ellipsoid reachability (CemSafeMPC._dynamics_func).
+    """Drop-in for `ConstrainedCemMpc` (constrained_cem_mpc.py:195-280).  Construction mirrors the reference (:204-220).
 
-    Construction mirrors the reference (:204-220).  `dynamics_func` must be a `safempc.B200SafeDynamics` (it carries
-    the GP handle and the problem constants the fused kernels need); `constraints` is the reference's list
-    [ActionConstraint, EllipsoidTerminalConstraint | EllipsoidStateConstraint] and is folded into the device-side
-    problem.  `state_dimen` is the flat dimension n_s + n_s^2 (PQFlattener).
+    Two evaluation paths behind the same methods:
+      * fused -- `dynamics_func` is a `safempc.B200SafeDynamics` on a `B200GpCemSSM` with a built-in objective, and every
+        constraint is one of ActionConstraint / Ellipsoid{Terminal,State,Obstacle}Constraint: dynamics and constraints
+        are folded into the device-side problem and the whole optimisation is one `se_cem_solve`.  `state_dimen` is
+        then the flat dimension n_s + n_s^2 (PQFlattener).
+      * interface -- anything else (an arbitrary `DynamicsFunc`, an unknown `Constraint`, a CemSSM that is not the B200
+        GP, an injected `rollout_function`): the reference-shaped loop of `optimize_trajectories` runs on device tensors
+        with the Python callbacks called exactly as the reference calls them, and everything that is not a callback stays
+        on the library's kernels (sampling `se_cem_noise`, elite selection + refit `se_cem_select_refit`, final pick
+        `se_cem_pick`).  It is an interface fallback, not a CPU fallback: tensors must live on a CUDA device.
 
-    Extras over the reference: `noise` (RNG-fixed candidates), `seed`, `pick_best`, `record`, batched instances and
-    population sharding over ranks (`set_comm`).
+    Extras over the reference: `noise` (RNG-fixed candidates), `seed`, `pick_best`, and on the fused path `record`,
+    batched instances and population sharding over ranks (`set_comm`).
     """
 
     def __init__(self, dynamics_func, constraints: Sequence[Constraint], state_dimen: int, action_dimen: int,
                  time_horizon: int, num_rollouts: int, num_elites: int, num_iterations: int, rollout_function=None,
                  seed: int = 0, pick_best: bool = False, record: str = 'full', num_instances: int = 1,
                  rank: int = 0, world_size: int = 1):
-        from .safempc import B200SafeDynamics, fold_constraints  # local import: safempc imports this module
-        if rollout_function is not None:
-            raise TypeError('rollout_function injection is a unit-test hook of the reference; the B200 path runs the '
-                            'rollouts on the device')
-        if not isinstance(dynamics_func, B200SafeDynamics):
-            raise TypeError('dynamics_func must be a B200SafeDynamics (GP reachability); arbitrary Python dynamics '
-                            'cannot run inside the fused kernels')
-        self._dyn = dynamics_func
-        self._ssm: B200GpCemSSM = dynamics_func.ssm
-        n_s = self._ssm.num_states
-        if state_dimen != n_s + n_s * n_s:
-            raise ValueError(f'Wanted state_dimen {n_s + n_s * n_s}, got {state_dimen}')
-        if action_dimen != self._ssm.num_actions:
-            raise ValueError(f'Wanted action_dimen {self._ssm.num_actions}, got {action_dimen}')
+        from .safempc import B200SafeDynamics, can_fold, fold_constraints  # local import: safempc imports this module
         if record not in ('full', 'costs', 'none'):
             raise ValueError(f'record must be full|costs|none, got {record}')
         if num_rollouts % world_size != 0:
@@ -129,10 +207,30 @@ class B200ConstrainedCemMpc:
         self._num_rollouts = num_rollouts
         self._num_elites = num_elites
         self._num_iterations = num_iterations
-        self._constraints = list(constraints)
-        self._rollout_function = self  # safempc_cem.py:270 reads mpc._rollout_function._constraints
-        self._problem: SafeProblem = fold_constraints(dynamics_func.problem, self._constraints)
+        self._constraints = list(constraints) if constraints is not None else []
         self.seed = int(seed)
+        self.fused = (rollout_function is None and isinstance(dynamics_func, B200SafeDynamics) and
+                      dynamics_func.fusable and all(can_fold(c) for c in self._constraints))
+        self._dyn = dynamics_func
+        if self.fused:
+            self._ssm: B200GpCemSSM = dynamics_func.ssm
+            n_s = self._ssm.num_states
+            if state_dimen != n_s + n_s * n_s:
+                raise ValueError(f'Wanted state_dimen {n_s + n_s * n_s}, got {state_dimen}')
+            if action_dimen != self._ssm.num_actions:
+                raise ValueError(f'Wanted action_dimen {self._ssm.num_actions}, got {action_dimen}')
+            self._rollout_function = self  # safempc_cem.py:270 reads mpc._rollout_function._constraints
+            self._problem: SafeProblem = fold_constraints(dynamics_func.problem, self._constraints)
+        else:
+            if num_instances != 1 or world_size != 1:
+                raise TypeError('batched instances and population sharding need the fused path (B200SafeDynamics on a '
+                                'B200GpCemSSM with built-in objective and constraints)')
+            self._ssm = getattr(dynamics_func, 'ssm', None)
+            if rollout_function is None:
+                rollout_function = RolloutFunction(dynamics_func, self._constraints, state_dimen, action_dimen,
+                                                   time_horizon, num_rollouts, seed=self.seed)
+            self._rollout_function = rollout_function
+            self._problem = None
         self.pick_best = bool(pick_best)
         self.record = record
         self.num_instances = int(num_instances)
@@ -157,16 +255,33 @@ class B200ConstrainedCemMpc:
         except Exception:
             pass
 
+    def set_objective(self, objective: int, objective_theta: float = 0.0) -> None:
+        """Change the built-in objective selector / its target (the InvertedPendulum advances its target angle during
+        an episode, environments.py:488-515); the device-side problem is rebuilt on the next solve."""
+        if not self.fused:
+            raise _lib.SecemError('set_objective applies to the fused path')
+        if (int(objective), float(objective_theta)) != (self._problem.objective, self._problem.objective_theta):
+            self._problem = self._problem.with_(objective=int(objective), objective_theta=float(objective_theta))
+            self._dyn.problem = self._dyn.problem.with_(objective=int(objective), objective_theta=float(objective_theta))
+            self._destroy()
+
     def set_comm(self, nccl_comm: Optional[int], rank: int, world_size: int) -> None:
         """Attach an NCCL communicator made by `dist.create_nccl_comm` (population sharding)."""
+        if not self.fused and world_size != 1:
+            raise TypeError('population sharding needs the fused path')
         if self._num_rollouts % world_size != 0:
             raise ValueError(f'num_rollouts {self._num_rollouts} must be divisible by world_size {world_size}')
         self._comm, self.rank, self.world_size = nccl_comm, int(rank), int(world_size)
         self._destroy()
 
     def _ensure_handle(self):
+        if not self.fused:
+            raise _lib.SecemError('this solver runs the interface path (Python dynamics / constraints): it has no '
+                                  'device-side CEM handle; use get_actions / optimize_trajectories')
         gp_handle = self._ssm.handle
-        key = (gp_handle.value, self.num_instances, self.pick_best, self.rank, self.world_size)
+        # never key on the handle's address: update_model destroys and re-creates the model and the allocator readily
+        # returns the same address (the library checks the generation too and refuses a stale GP handle)
+        key = (self._ssm.generation, self.num_instances, self.pick_best, self.rank, self.world_size)
         if self._handle and self._handle_key == key:
             return
         self._destroy()
@@ -249,8 +364,19 @@ class B200ConstrainedCemMpc:
             _lib.check(self._lib.se_cem_solve(self._handle, _lib.ptr(p0), _lib.ptr(noise), C.c_uint64(int(seed)),
                                               C.byref(out), _lib.stream_ptr(dev)))
         if sync:
-            check_flags(res['flags'].cpu(), 'CEM rollouts')
+            check_flags(self._collective_flags(res['flags']), 'CEM rollouts')
         return res
+
+    def _collective_flags(self, flags: Tensor) -> Tensor:
+        """Host copy of the numeric flags.  Sharded: the element-wise maximum over the ranks, so that every rank raises
+        (or warns) together instead of one rank leaving the others blocked in the next all-gather."""
+        if self.world_size > 1:
+            import torch.distributed as dist
+            if dist.is_available() and dist.is_initialized():
+                f = flags.clone() if dist.get_backend() == 'nccl' else flags.cpu()
+                dist.all_reduce(f, op=dist.ReduceOp.MAX)
+                return f.cpu()
+        return flags.cpu()
 
     def get_actions_point(self, state) -> Optional['np.ndarray']:
         """What CemSafeMPC.get_action needs from get_actions (safempc_cem.py:236-241) for a POINT state given on the
@@ -259,6 +385,14 @@ class B200ConstrainedCemMpc:
         synchronisation; no per-iteration records are exposed (use get_actions for those)."""
         import numpy as np
         ssm = self._ssm
+        if not self.fused:
+            n_s = len(np.asarray(state).reshape(-1))
+            dt = getattr(ssm, 'dtype', torch.float64)
+            dev = getattr(ssm, 'device', torch.device('cuda:0'))
+            flat = torch.zeros(self._state_dimen, dtype=dt, device=dev)
+            flat[:n_s] = torch.as_tensor(np.asarray(state, dtype=np.float64).reshape(-1), dtype=dt)
+            actions, _ = self.get_actions(flat)
+            return None if actions is None else actions.detach().cpu().numpy()
         n_s, T, n_u = ssm.num_states, self._time_horizon, ssm.num_actions
         dev, dt = ssm.device, ssm.dtype
         n_local = self._num_rollouts // self.world_size
@@ -305,8 +439,35 @@ class B200ConstrainedCemMpc:
                                 res['constraint'][i, inst] if 'constraint' in res else None))
         return out
 
+    def _optimize_interface(self, initial_state: Tensor, noise: Optional[Tensor]) -> List[Rollouts]:
+        """optimize_trajectories (constrained_cem_mpc.py:222-239) on the interface path: Python callbacks for dynamics /
+        constraints, library kernels for sampling, elite selection (+ index tie-break) and the refit."""
+        _lib.require_cuda(initial_state, 'initial_state')
+        rf = self._rollout_function
+        dev = initial_state.device
+        dt = initial_state.dtype if initial_state.is_floating_point() else torch.get_default_dtype()
+        means = torch.zeros((self._time_horizon, self._action_dimen), dtype=dt, device=dev)
+        stds = torch.ones((self._time_horizon, self._action_dimen), dtype=dt, device=dev)
+        seed = self.seed
+        self.seed += 1
+        rollouts_by_time = []
+        self.last_info = dict(means=[], stds=[], elite_ids=[])
+        for i in range(self._num_iterations):
+            if isinstance(rf, RolloutFunction):
+                rf.seed, rf.iteration = seed, i
+                rf.noise = None if noise is None else noise[i]
+            rollouts = rf.perform_rollouts((initial_state, means, stds))
+            ids, means, stds = select_elites_refit(rollouts.objective_costs, rollouts.constraint_costs,
+                                                   rollouts.actions, self._num_elites)
+            rollouts_by_time.append(rollouts)
+            self.last_info['means'].append(means), self.last_info['stds'].append(stds)
+            self.last_info['elite_ids'].append(ids)
+        return rollouts_by_time
+
     def optimize_trajectories(self, initial_state: Tensor, noise: Optional[Tensor] = None) -> List[Rollouts]:
         """constrained_cem_mpc.py:222-239 -> rollouts of every iteration (final one last)."""
+        if not self.fused:
+            return self._optimize_interface(initial_state, noise)
         res = self.solve(self._flat_state_to_p0(initial_state), None if noise is None else noise.unsqueeze(1))
         self.last_info = res
         return self._rollouts_of(res)
@@ -315,6 +476,13 @@ class B200ConstrainedCemMpc:
                     ) -> Tuple[Union[Tensor, None], List[Rollouts]]:
         """constrained_cem_mpc.py:259-280: (actions [T, n_u] of a feasible rollout of the last iteration | None,
         rollouts by iteration).  `noise` [I, N, T, n_u] fixes the candidates (parity tests)."""
+        if not self.fused:
+            _lib.require_cuda(state, 'state')
+            rollouts_by_time = self._optimize_interface(state, noise)
+            last = rollouts_by_time[-1]
+            best = pick_rollout(last.objective_costs, last.constraint_costs, self.pick_best)
+            self.last_info['best_id'] = best
+            return (last.actions[best] if best >= 0 else None), rollouts_by_time
         res = self.solve(self._flat_state_to_p0(state), None if noise is None else noise.unsqueeze(1),
                          reuse_outputs=reuse_outputs)
         self.last_info = res
@@ -336,10 +504,12 @@ def select_elites_refit(objective_costs: Tensor, constraint_costs: Tensor, actio
     lib = _lib.load()
     N, T, n_u = actions.shape
     dt, dev = actions.dtype, actions.device
+    if dt not in (torch.float32, torch.float64):
+        dt = torch.float64
     code = _lib.dtype_code(dt)
     obj = objective_costs.detach().to(dt).contiguous()
     con = constraint_costs.detach().to(dt).contiguous()
-    act = actions.detach().contiguous()
+    act = actions.detach().to(dt).contiguous()
     ids = torch.empty((num_elites,), dtype=torch.int32, device=dev)
     mean = torch.empty((T, n_u), dtype=dt, device=dev)
     std = torch.empty((T, n_u), dtype=dt, device=dev)
@@ -347,6 +517,21 @@ def select_elites_refit(objective_costs: Tensor, constraint_costs: Tensor, actio
         _lib.check(lib.se_cem_select_refit(code, _lib.ptr(obj), _lib.ptr(con), _lib.ptr(act), N, T, n_u, num_elites,
                                            _lib.ptr(ids), _lib.ptr(mean), _lib.ptr(std), _lib.stream_ptr(dev)))
     return ids, mean, std
+
+
+def pick_rollout(objective_costs: Tensor, constraint_costs: Tensor, pick_best: bool = False) -> int:
+    """The rollout `get_actions` returns (constrained_cem_mpc.py:272-280) on given costs, by the device kernel the solver
+    uses (`se_cem_pick`): the first feasible one (quirk Q3), or the arg-min objective feasible one; -1 if none."""
+    _lib.require_cuda(constraint_costs, 'constraint_costs')
+    lib = _lib.load()
+    dt = objective_costs.dtype if objective_costs.is_floating_point() else torch.float64
+    obj = objective_costs.detach().to(dt).contiguous()
+    con = constraint_costs.detach().to(dt).contiguous()
+    best = torch.empty((1,), dtype=torch.int32, device=con.device)
+    with torch.cuda.device(con.device):
+        _lib.check(lib.se_cem_pick(_lib.dtype_code(dt), _lib.ptr(obj), _lib.ptr(con), con.numel(),
+                                   1 if pick_best else 0, _lib.ptr(best), _lib.stream_ptr(con.device)))
+    return int(best.item())
 
 
 def sample_noise(seed: int, iteration: int, num_instances: int, num_rollouts: int, first: int, count: int, T: int,

@@ -8,6 +8,9 @@
 #include <cstdarg>
 #include <cstdio>
 #include <cstring>
+#include <map>
+#include <mutex>
+#include <utility>
 
 #include "../../include/secem.h"
 
@@ -56,6 +59,23 @@ inline int fail(const char* fmt, ...) {
       return ::se::fail("%s:%d: launch %s -> %s", __FILE__, __LINE__, #kernel, cudaGetErrorString(_e)); \
   } while (0)
 
+// Opt a kernel in to `bytes` of dynamic shared memory (> 48 KB needs it).  The attribute is per DEVICE, so it is
+// tracked per (kernel, device): a process may drive several GPUs.
+template <typename F>
+inline int set_max_dyn_smem(F* func, int bytes) {
+  static std::mutex mu;
+  static std::map<std::pair<const void*, int>, int> have;
+  int dev = 0;
+  SE_CUDA(cudaGetDevice(&dev));
+  std::lock_guard<std::mutex> lock(mu);
+  int& cur = have[std::make_pair(reinterpret_cast<const void*>(func), dev)];
+  if (bytes > cur) {
+    SE_CUDA(cudaFuncSetAttribute(func, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes));
+    cur = bytes;
+  }
+  return 0;
+}
+
 inline int64_t round_up(int64_t x, int64_t m) { return (x + m - 1) / m * m; }
 inline int64_t ceil_div(int64_t x, int64_t m) { return (x + m - 1) / m; }
 
@@ -78,6 +98,7 @@ struct GpDev {
 template <typename T>
 struct ProbDev {
   int ns, nu, m_safe, m_act, objective, all_states, m_obs;
+  int clamp_nonpos;  // se_problem.clamp_nonpositive: every variance <= 0 becomes 1e-5 (and is counted)
   T k_fb[SE_MAX_NU][SE_MAX_NS];
   T a[SE_MAX_NS][SE_MAX_NS];
   T b[SE_MAX_NS][SE_MAX_NU];

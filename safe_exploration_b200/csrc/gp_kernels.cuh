@@ -418,7 +418,7 @@ __global__ void gp_var_kernel(GpDev<T> gp, const T* __restrict__ partial, int nb
   const int64_t r = idx / gp.ns;
   T s = T(0);
   for (int ib = 0; ib < nb; ++ib) s += partial[((int64_t)o * nb + ib) * rows_pad + r];
-  var[(row0 + r) * gp.ns + o] = gp.outputscale[o] - s + gp.noise[o];
+  T v = gp.outputscale[o] - s + gp.noise[o];
   if (nseg > 0) {
     const int w = 1 + gp.d;
     const T* src = kpart + (r * gp.ns + o) * w;
@@ -433,6 +433,12 @@ __global__ void gp_var_kernel(GpDev<T> gp, const T* __restrict__ partial, int nb
         jac[((row0 + r) * gp.ns + o) * gp.d + dd] = -g * gp.inv_l2[o][dd];
       }
   }
+  // A non-finite input poisons the row's mean (the digit planes of the tensor-core path cannot carry a NaN); the
+  // reference's GP returns NaN for mean AND variance there, which is what _fix_zeros_nans looks at
+  // (gp_reachability_pytorch.py:234-243).
+  const T m_final = mean[(row0 + r) * gp.ns + o];
+  if (m_final != m_final) v = m_final;
+  var[(row0 + r) * gp.ns + o] = v;
 }
 
 }  // namespace se

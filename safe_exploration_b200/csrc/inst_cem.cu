@@ -29,11 +29,7 @@ int launch_cem_select_refit(const SelectArgs<T>& a, int num_inst, cudaStream_t s
   // selected keys + indices, and (populations of 4097 .. 16384) a cache of every key
   const int cache_n = a.n_global > kSortAllMax && a.n_global <= 16384 ? a.n_global : 0;
   const int smem = kMaxElites * 12 + cache_n * 8;
-  static int attr_smem = 0;
-  if (smem > attr_smem) {
-    SE_CUDA(cudaFuncSetAttribute(cem_select_refit_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-    attr_smem = smem;
-  }
+  SE_TRY(set_max_dyn_smem(cem_select_refit_kernel<T>, smem));
   SE_LAUNCH((cem_select_refit_kernel<T>), num_inst, kSelThreads, smem, stream, a, cache_n);
   return 0;
 }

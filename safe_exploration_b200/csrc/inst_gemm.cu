@@ -50,12 +50,7 @@ int launch_trisumsq<double>(se_gemm_impl impl, const double* kst, const double* 
   *nb_out = od.nb;
 #define SE_DMMA_LAUNCH(CFG, SKIP)                                                                                  \
   do {                                                                                                             \
-    static bool attr_set = false;                                                                                  \
-    if (!attr_set) {                                                                                               \
-      SE_CUDA(cudaFuncSetAttribute((gp_trisumsq_dmma_kernel<CFG, SKIP>), cudaFuncAttributeMaxDynamicSharedMemorySize, \
-                                   CFG::SMEM_BYTES));                                                              \
-      attr_set = true;                                                                                             \
-    }                                                                                                              \
+    SE_TRY(set_max_dyn_smem((gp_trisumsq_dmma_kernel<CFG, SKIP>), CFG::SMEM_BYTES));                               \
     SE_LAUNCH((gp_trisumsq_dmma_kernel<CFG, SKIP>), grid, CFG::THREADS, CFG::SMEM_BYTES, stream, kst, w, n_pad,    \
               rows_pad, od, partial, counter);                                                                     \
     return 0;                                                                                                      \

@@ -93,12 +93,7 @@ template <int S, int MODE>
 static int launch_oz_gemm_s(const int8_t* a_img, const int8_t* b_img, const double* scale_b, int n, int n_pad,
                             int rows_pad, const TriOrder& od, int grid, double* partial, cudaStream_t stream) {
   using C = oz::Cfg<S>;
-  static bool attr_set = false;
-  if (!attr_set) {
-    SE_CUDA(cudaFuncSetAttribute((oz::gp_trisumsq_ozaki_kernel<S, MODE>), cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                 C::SMEM_BYTES));
-    attr_set = true;
-  }
+  SE_TRY(set_max_dyn_smem((oz::gp_trisumsq_ozaki_kernel<S, MODE>), C::SMEM_BYTES));
   static const int dbg = getenv("SE_OZ_DBG") ? atoi(getenv("SE_OZ_DBG")) : 0;  // measurement knobs, see the kernel
   SE_LAUNCH((oz::gp_trisumsq_ozaki_kernel<S, MODE>), grid, oz::THREADS, C::SMEM_BYTES, stream, a_img, b_img, scale_b, n,
             n_pad, rows_pad, od, partial, dbg);

@@ -20,6 +20,14 @@ int launch_reach_step<SE_T>(const ProbDev<SE_T>& pr, const StepIO<SE_T>& io, int
 }
 
 template <>
+int launch_var_zero_scan<SE_T>(const SE_T* var, int64_t count, int32_t* flags, cudaStream_t stream) {
+  if (count <= 0) return 0;
+  SE_CUDA(cudaMemsetAsync(flags + 2, 0, sizeof(int32_t), stream));
+  SE_LAUNCH(var_zero_scan_kernel<SE_T>, (int)ceil_div(count, 256), 256, 0, stream, var, count, flags);
+  return 0;
+}
+
+template <>
 int launch_safety_distance<SE_T>(const ProbDev<SE_T>& pr, const SE_T* p, const SE_T* q, int64_t N, SE_T* d,
                                  uint8_t* inside, cudaStream_t stream) {
   if (N <= 0) return 0;

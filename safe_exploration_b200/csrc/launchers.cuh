@@ -31,6 +31,8 @@ int launch_var(const GpDev<T>& gp, const T* partial, int nb, int rows_pad, int64
 template <typename T>
 int launch_reach_step(const ProbDev<T>& pr, const StepIO<T>& io, int64_t N, cudaStream_t stream);
 template <typename T>
+int launch_var_zero_scan(const T* var, int64_t count, int32_t* flags, cudaStream_t stream);
+template <typename T>
 struct RolloutIO;
 template <typename T>
 int launch_transpose_w(const T* w, int n_pad, int ns, T* wt, cudaStream_t stream);

@@ -93,20 +93,31 @@ __device__ __forceinline__ T remainder_r_sqr(const T (&q)[NS][NS], const ProbDev
   return sym_lambda_max<T, NS>(m);
 }
 
-// _fix_zeros_nans (gp_reachability_pytorch.py:234-243), per element: NaN is counted in flags[0]; an exact zero is
-// counted in flags[1] and replaced by 1e-5.  (The reference additionally clamps *negative* entries, but only when the
-// batch also holds an exact zero; a negative value here turns into NaN at the next sqrt and is reported there.)
+// _fix_zeros_nans (gp_reachability_pytorch.py:234-243): NaN is counted in flags[0] (the caller raises); an exact zero
+// is counted in flags[1] and replaced by 1e-5.  The reference's rule is batch-wide: when the batch holds an exact zero
+// it sets EVERY x <= 0 to 1e-5, so negative entries are clamped too -- `clamp_neg` says whether that applies (the
+// se_reach_* entry points scan the batch first, var_zero_scan_kernel; se_cem_solve takes it from
+// se_problem.clamp_nonpositive).  Without it a negative value turns into NaN at the next sqrt and is reported there,
+// which is what the reference does when no exact zero is present.
 template <typename T>
-__device__ __forceinline__ T fix_zero_nan(T x, int32_t* flags) {
+__device__ __forceinline__ T fix_zero_nan(T x, int32_t* flags, bool clamp_neg = false) {
   if (x != x) {
     if (flags) atomicAdd(&flags[0], 1);
     return x;
   }
-  if (x == T(0)) {
+  if (x == T(0) || (clamp_neg && x < T(0))) {
     if (flags) atomicAdd(&flags[1], 1);
     return T(1e-5);
   }
   return x;
+}
+
+// flags[2] |= 1 when var[0 .. count) holds an exact zero (the batch-wide condition of _fix_zeros_nans)
+template <typename T>
+__global__ void var_zero_scan_kernel(const T* __restrict__ var, int64_t count, int32_t* __restrict__ flags) {
+  const int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  const bool z = i < count && var[i] == T(0);
+  if (__any_sync(0xffffffffu, z) && (threadIdx.x & 31) == 0) atomicOr(&flags[2], 1);
 }
 
 // support-function distance of the ellipsoid (p, q) to every face; returns true iff all d < 0
@@ -164,6 +175,7 @@ struct StepIO {
   T* q_all;        // [N, T, NS, NS]
   T* sigma_all;    // [N, T, NS]
   int32_t* flags;
+  int batch_zero_scan;  // 1: flags[2] holds "this batch has an exact-zero variance" (set by var_zero_scan_kernel)
   int64_t first;   // first candidate of this launch (all arrays are indexed by the absolute candidate id)
   // Fused variance reduction (se_cem_solve): when `partial` is set, the kernel forms var = s + noise - sum_ib partial
   // itself (what gp_var_kernel does, same order) instead of reading `var`, and, when the kernel-row launch was split
@@ -182,9 +194,11 @@ template <typename T, int NS, int NU>
 __device__ __forceinline__ void ellipsoid_step_core(const ProbDev<T>& pr, const T (&p)[NS], const T (&q)[NS][NS],
                                                     bool point, const T (&u)[NU], const T (&mu)[NS],
                                                     const T (&var)[NS], const T (&jac)[NS][NS + NU], int32_t* flags,
-                                                    T (&p1)[NS], T (&q1)[NS][NS], T (&sg)[NS]) {
+                                                    T (&p1)[NS], T (&q1)[NS][NS], T (&sg)[NS],
+                                                    bool clamp_neg = false) {
+  clamp_neg = clamp_neg || pr.clamp_nonpos != 0;
 #pragma unroll
-  for (int i = 0; i < NS; ++i) sg[i] = fix_zero_nan<T>(var[i], flags);  // sigm_0 (:76, :117)
+  for (int i = 0; i < NS; ++i) sg[i] = fix_zero_nan<T>(var[i], flags, clamp_neg);  // sigm_0 (:76, :117)
 
   // p_0 = mu_0 + a p + b u   (:93-94, :132)
 #pragma unroll
@@ -402,8 +416,14 @@ __device__ __forceinline__ void reach_step_body(const ProbDev<T>& pr, const Step
   }
 #pragma unroll
   for (int j = 0; j < NU; ++j) u[j] = io.u[c * io.u_stride + j];
+  // non-finite inputs poison the mean (kernel-row kernels); the reference's GP returns NaN variances there as well
+#pragma unroll
+  for (int i = 0; i < NS; ++i)
+    if (mu[i] != mu[i]) var[i] = mu[i];
   T q1[NS][NS];
-  ellipsoid_step_core<T, NS, NU>(pr, p, q, io.point != 0, u, mu, var, jac, writer ? io.flags : nullptr, p1, q1, sg);
+  const bool clamp_neg = io.batch_zero_scan && io.flags && io.flags[2] != 0;
+  ellipsoid_step_core<T, NS, NU>(pr, p, q, io.point != 0, u, mu, var, jac, writer ? io.flags : nullptr, p1, q1, sg,
+                                 clamp_neg);
   if (!writer) return;
 
   // ---- write the new ellipsoid ----

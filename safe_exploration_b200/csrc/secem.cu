@@ -3,6 +3,8 @@
 
 #include <cmath>
 #include <cstdlib>
+#include <mutex>
+#include <unordered_map>
 #include <vector>
 
 #include "cem_kernels.cuh"
@@ -24,6 +26,7 @@ using namespace se;
 constexpr int64_t kSplitRows = 4096;  // below this a kernel-row launch splits the training set over CTAs
 
 struct se_gp_s {
+  uint64_t generation = 0;  // unique per se_gp_create (never reused, unlike the handle's address)
   se_dtype dtype = SE_F64;
   int ns = 0, nu = 0, d = 0, n = 0, n_pad = 0;
   size_t esz = 8;
@@ -65,6 +68,20 @@ struct se_gp_s {
   bool timing = false;
   std::vector<cudaEvent_t> ev_gemm, ev_kstar;  // (start, stop) pairs
 };
+
+// Live GP handles and their generation.  A CEM handle keeps a raw pointer to its GP; the allocator readily hands the
+// address of a destroyed se_gp_s to the next se_gp_create (update_model destroys and re-creates the model), so a
+// pointer comparison cannot tell "same model" from "new model at the old address".  se_cem_solve looks the pointer up
+// here and compares generations instead, and the generation is part of the CUDA-graph key.
+static std::mutex g_gp_mutex;
+static std::unordered_map<const se_gp_s*, uint64_t> g_live_gp;
+static uint64_t g_gp_generation = 0;
+
+static uint64_t gp_live_generation(const se_gp_s* g) {  // 0 = not a live handle
+  std::lock_guard<std::mutex> lock(g_gp_mutex);
+  auto it = g_live_gp.find(g);
+  return it == g_live_gp.end() ? 0 : it->second;
+}
 
 template <typename T>
 static GpDev<T> gp_dev(const se_gp_s* g) {
@@ -169,12 +186,21 @@ extern "C" int se_gp_create(se_gp_t* out, int n_s, int n_u, int n, se_dtype dtyp
                                   g->n_pad, (float*)g->xt, (float*)g->alpha, (float*)g->w, st);
   if (rc != 0) return cleanup_fail();
   g->impl = resolve_impl(g, SE_GEMM_AUTO);
+  {
+    std::lock_guard<std::mutex> lock(g_gp_mutex);
+    g->generation = ++g_gp_generation;
+    g_live_gp[g] = g->generation;
+  }
   *out = g;
   return 0;
 }
 
 extern "C" int se_gp_destroy(se_gp_t g) {
   if (!g) return 0;
+  {
+    std::lock_guard<std::mutex> lock(g_gp_mutex);
+    g_live_gp.erase(g);
+  }
   for (void* p : {g->xt, g->alpha, g->w, g->kst, g->partial, g->kpart, g->post_mean, g->post_var, g->post_jac, (void*)g->counter,
                   (void*)g->b_img, (void*)g->exp_ab, (void*)g->scale_b, g->wt})
     if (p) cudaFree(p);
@@ -476,6 +502,7 @@ static int make_prob(const se_problem* pr, const double* k_fb_override, ProbDev<
   memset(&o, 0, sizeof(o));
   o.ns = ns, o.nu = nu, o.m_safe = pr->m_safe, o.m_act = pr->m_act;
   o.objective = pr->objective, o.all_states = pr->all_states_constraint;
+  o.clamp_nonpos = pr->clamp_nonpositive;
   const double* kf = k_fb_override ? k_fb_override : pr->k_fb;
   double kfb[SE_MAX_NU][SE_MAX_NS] = {};
   for (int k = 0; k < nu; ++k)
@@ -556,7 +583,52 @@ static int reach_onestep_t(se_gp_s* g, const se_problem* prob, const T* p, const
   io.point = q ? 0 : 1;
   io.first_step = 1, io.last_step = 1, io.T_len = 1;
   io.flags = flags;
+  if (flags) {  // batch-wide rule of _fix_zeros_nans: does this batch hold an exact-zero variance?
+    SE_TRY(launch_var_zero_scan<T>(var, N * g->ns, flags, st));
+    io.batch_zero_scan = 1;
+  }
   return launch_reach_step<T>(pr, io, N, st);
+}
+
+template <typename T>
+static int reach_step_t(const se_problem* prob, const T* p, const T* q, const T* u, const T* mean, const T* var,
+                        const T* jac, int64_t N, T* p1, T* q1, T* sigma, int32_t* flags, cudaStream_t st) {
+  ProbDev<T> pr;
+  SE_TRY(make_prob<T>(prob, nullptr, &pr));
+  SE_REQUIRE(q == nullptr || (prob->k_fb != nullptr && jac != nullptr),
+             "se_reach_step: k_fb and the mean Jacobian are required for ellipsoid states");
+  StepIO<T> io;
+  memset(&io, 0, sizeof(io));
+  io.p_in = p, io.q_in = q, io.p_out = p1, io.q_out = q1;
+  io.u = u, io.u_stride = pr.nu;
+  io.mean = mean, io.var = var, io.jac = q ? jac : nullptr;
+  io.sigma_out = sigma;
+  io.point = q ? 0 : 1;
+  io.first_step = 1, io.last_step = 1, io.T_len = 1;
+  io.flags = flags;
+  if (flags) {
+    SE_TRY(launch_var_zero_scan<T>(var, N * pr.ns, flags, st));
+    io.batch_zero_scan = 1;
+  }
+  return launch_reach_step<T>(pr, io, N, st);
+}
+
+extern "C" int se_reach_step(se_dtype dtype, const se_problem* prob, const void* dev_p, const void* dev_q,
+                             const void* dev_u, const void* dev_mean, const void* dev_var, const void* dev_jac,
+                             int64_t N, void* dev_p1, void* dev_q1, void* dev_sigma, int32_t* dev_flags,
+                             void* stream) {
+  SE_REQUIRE(prob && dev_p && dev_u && dev_mean && dev_var && dev_p1 && dev_q1, "se_reach_step: NULL argument");
+  SE_REQUIRE(dtype == SE_F32 || dtype == SE_F64, "se_reach_step: bad dtype");
+  SE_REQUIRE(N >= 0, "se_reach_step: N < 0");
+  if (N == 0) return 0;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (dtype == SE_F64)
+    return reach_step_t<double>(prob, (const double*)dev_p, (const double*)dev_q, (const double*)dev_u,
+                                (const double*)dev_mean, (const double*)dev_var, (const double*)dev_jac, N,
+                                (double*)dev_p1, (double*)dev_q1, (double*)dev_sigma, dev_flags, st);
+  return reach_step_t<float>(prob, (const float*)dev_p, (const float*)dev_q, (const float*)dev_u,
+                             (const float*)dev_mean, (const float*)dev_var, (const float*)dev_jac, N, (float*)dev_p1,
+                             (float*)dev_q1, (float*)dev_sigma, dev_flags, st);
 }
 
 extern "C" int se_reach_onestep(se_gp_t g, const se_problem* prob, const void* dev_p, const void* dev_q,
@@ -602,6 +674,10 @@ static int reach_multistep_t(se_gp_s* g, const se_problem* prob, const T* p0, co
     io.first_step = t == 0, io.last_step = t == T_len - 1, io.T_len = T_len, io.t_index = t;
     io.p_all = p_all, io.q_all = q_all, io.sigma_all = sigma_all;
     io.flags = flags;
+    if (flags) {
+      SE_TRY(launch_var_zero_scan<T>(var, N * g->ns, flags, st));
+      io.batch_zero_scan = 1;
+    }
     SE_TRY(launch_reach_step<T>(pr, io, N, st));
   }
   return 0;
@@ -720,6 +796,7 @@ struct GraphEntry {
 
 struct se_cem_s {
   se_gp_s* gp = nullptr;
+  uint64_t gp_generation = 0;  // generation of *gp when this handle was created
   se_cem_config cfg{};
   ProbDev<float> pf;
   ProbDev<double> pd;
@@ -768,8 +845,10 @@ extern "C" int se_cem_create(se_cem_t* out, se_gp_t gp, const se_problem* prob, 
   SE_REQUIRE((int64_t)cfg->num_instances * cfg->num_rollouts < (1ll << 31), "se_cem_create: population too large");
   SE_REQUIRE(prob->n_s == gp->ns && prob->n_u == gp->nu, "se_cem_create: problem / GP dimension mismatch");
   SE_REQUIRE(prob->k_fb && prob->a && prob->b, "se_cem_create: k_fb, a, b are required");
+  SE_REQUIRE(gp_live_generation(gp) != 0, "se_cem_create: the GP handle is not live (destroyed?)");
   se_cem_s* c = new se_cem_s();
   c->gp = gp;
+  c->gp_generation = gp->generation;
   c->cfg = *cfg;
   if (make_prob<float>(prob, nullptr, &c->pf) != 0 || make_prob<double>(prob, nullptr, &c->pd) != 0) {
     delete c;
@@ -868,6 +947,7 @@ static int cem_solve_t(se_cem_s* c, const ProbDev<T>& pr, const T* p0, const T* 
       SE_TRY(launch_transpose_w<T>((const T*)g->w, g->n_pad, ns, (T*)g->wt, st));
     }
     if (!fused) SE_TRY(gp_reserve(g, pipelined ? two_part_rows : cand));
+    if (!fused) SE_TRY(gp_reserve_posterior(g, cand));
     if (!fused && g->impl == SE_GEMM_TC) SE_TRY(tc_prepare(g, st));
     if (pipelined && !g->side) {
       SE_CUDA(cudaStreamCreateWithFlags(&g->side, cudaStreamNonBlocking));
@@ -1054,6 +1134,8 @@ static GraphKey graph_key(const se_cem_s* c, const void* p0, const void* noise, 
   k.val[4] = (getenv("SE_ROLLOUT_FUSED") ? atoi(getenv("SE_ROLLOUT_FUSED")) : 1) +
              2 * (getenv("SE_STEP_FUSED") ? atoi(getenv("SE_STEP_FUSED")) : 1);
   k.val[5] = g->n_pad;
+  k.val[6] = (int64_t)g->generation;  // kernels take GpDev (n, hyper-parameters) by value: a new model is a new graph
+  k.val[7] = g->n;
   return k;
 }
 
@@ -1069,6 +1151,9 @@ static void graph_cache_clear(se_cem_s* c) {
 extern "C" int se_cem_solve(se_cem_t c, const void* dev_p0, const void* dev_noise, uint64_t seed,
                             const se_cem_outputs* out, void* stream) {
   SE_REQUIRE(c && dev_p0 && out, "se_cem_solve: NULL argument");
+  SE_REQUIRE(gp_live_generation(c->gp) == c->gp_generation,
+             "se_cem_solve: the GP handle this CEM handle was created on has been destroyed or replaced "
+             "(update_model); create a new CEM handle with se_cem_create");
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   const int graph_env = getenv("SE_CEM_GRAPH") ? atoi(getenv("SE_CEM_GRAPH")) : 1;
   const int pipe_env = getenv("SE_PIPELINE") ? atoi(getenv("SE_PIPELINE")) : 0;
@@ -1143,6 +1228,35 @@ extern "C" int se_cem_noise(se_dtype dtype, uint64_t seed, int iteration, int nu
                                     (double*)dev_noise_out, st);
   return launch_cem_noise<float>(seed, iteration, num_instances, num_rollouts_global, first_rollout, count, T * n_u,
                                  (float*)dev_noise_out, st);
+}
+
+template <typename T>
+static int cem_pick_t(const T* objective, const T* constraint, int N, int pick_best, int32_t* best_id, cudaStream_t st) {
+  T* pack = nullptr;
+  T* act = nullptr;
+  int32_t* found = nullptr;
+  SE_CUDA(cudaMalloc(&pack, (size_t)2 * N * sizeof(T)));
+  SE_CUDA(cudaMalloc(&act, sizeof(T)));
+  SE_CUDA(cudaMalloc(&found, sizeof(int32_t)));
+  int rc = launch_cem_pack_costs<T>(objective, constraint, N, pack, nullptr, nullptr, st);
+  ActionSrc<T> src;
+  memset(&src, 0, sizeof(src));
+  src.mode = 2, src.n_global = N, src.tnu = 0;  // no action sequence to copy out: the caller indexes its own tensor
+  if (rc == 0) rc = launch_cem_pick<T>(CostView<T>{pack, 1, N}, N, pick_best, src, 1, act, found, best_id, st);
+  cudaStreamSynchronize(st);
+  cudaFree(pack);
+  cudaFree(act);
+  cudaFree(found);
+  return rc;
+}
+
+extern "C" int se_cem_pick(se_dtype dtype, const void* dev_objective, const void* dev_constraint, int N, int pick_best,
+                           int32_t* dev_best_id, void* stream) {
+  SE_REQUIRE(dev_objective && dev_constraint && dev_best_id && N >= 1, "se_cem_pick: bad arguments");
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (dtype == SE_F64)
+    return cem_pick_t<double>((const double*)dev_objective, (const double*)dev_constraint, N, pick_best, dev_best_id, st);
+  return cem_pick_t<float>((const float*)dev_objective, (const float*)dev_constraint, N, pick_best, dev_best_id, st);
 }
 
 template <typename T>

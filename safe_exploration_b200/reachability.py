@@ -22,7 +22,7 @@ class SafeProblem:
                  h_mat=None, h_vec=None, act_a=None, act_b=None, act_penalty: float = 3.0,
                  state_penalty: float = 10.0, objective: int = _lib.SE_OBJ_NEG_VARIANCE,
                  objective_theta: float = 0.0, all_states_constraint: bool = False, h_mat_obs=None,
-                 h_vec_obs=None):
+                 h_vec_obs=None, clamp_nonpositive: bool = False):
         def arr(x, shape):
             if x is None:
                 return None
@@ -53,6 +53,9 @@ class SafeProblem:
         # obstacle polytope of the intermediate ellipsoids (safempc_simple.py:373-383); None = reference CEM behaviour
         self.h_mat_obs = arr(h_mat_obs, (-1, n_s))
         self.h_vec_obs = None if h_vec_obs is None else arr(h_vec_obs, (self.h_mat_obs.shape[0],))
+        # _fix_zeros_nans inside se_cem_solve: False = only exact zeros become 1e-5 (a negative variance is reported as
+        # NaN, the reference's behaviour for a batch without an exact zero); True = every variance <= 0 becomes 1e-5
+        self.clamp_nonpositive = bool(clamp_nonpositive)
 
     def with_(self, **kw) -> 'SafeProblem':
         cur = dict(n_s=self.n_s, n_u=self.n_u, l_mu=self.l_mu, l_sigma=self.l_sigma, k_fb=self.k_fb, a=self.a,
@@ -60,7 +63,7 @@ class SafeProblem:
                    act_b=self.act_b, act_penalty=self.act_penalty, state_penalty=self.state_penalty,
                    objective=self.objective, objective_theta=self.objective_theta,
                    all_states_constraint=self.all_states_constraint, h_mat_obs=self.h_mat_obs,
-                   h_vec_obs=self.h_vec_obs)
+                   h_vec_obs=self.h_vec_obs, clamp_nonpositive=self.clamp_nonpositive)
         cur.update(kw)
         return SafeProblem(**cur)
 
@@ -80,6 +83,7 @@ class SafeProblem:
         s.all_states_constraint = 1 if self.all_states_constraint else 0
         s.m_obs = 0 if self.h_mat_obs is None else self.h_mat_obs.shape[0]
         s.h_mat_obs, s.h_vec_obs = dp(self.h_mat_obs), dp(self.h_vec_obs)
+        s.clamp_nonpositive = 1 if self.clamp_nonpositive else 0
         return s  # the numpy arrays it points into are owned by `self`
 
 
@@ -99,9 +103,44 @@ def check_flags(flags: Tensor, where: str) -> None:
 
 def _gp_of(ssm) -> B200GpCemSSM:
     if not isinstance(ssm, B200GpCemSSM):
-        raise TypeError('the B200 reachability kernels need a B200GpCemSSM; other CemSSMs (e.g. MC-dropout) go '
-                        'through the Python DynamicsFunc interface of B200ConstrainedCemMpc')
+        raise TypeError(f'{type(ssm).__name__} is not a B200GpCemSSM: this entry point evaluates the GP inside the '
+                        f'kernels.  onestep_reachability accepts any CemSSM (it calls the model\'s predict_* methods '
+                        f'and runs the ellipsoid algebra of the step on the device: se_reach_step)')
     return ssm
+
+
+def _onestep_generic_ssm(p_center, ssm, k_ff, prob: SafeProblem, q_shape):
+    """Interface fallback for a CemSSM that is not the B200 GP, e.g. the MC-dropout models of
+    ssm_cem/dropout_ssm_cem.py: the model's own predict_with(out)_jacobians runs on the caller's device tensors
+    (gp_reachability_pytorch.py:73, 114), the ellipsoid algebra of the step runs in libsecem.so (`se_reach_step`)."""
+    _lib.require_cuda(p_center, 'p_center')
+    lib = _lib.load()
+    N = p_center.shape[0]
+    n_s = prob.n_s
+    dt, dev = p_center.dtype, p_center.device
+    code = _lib.dtype_code(dt)
+    if q_shape is None:
+        mean, var = ssm.predict_without_jacobians(p_center, k_ff)
+        jac = None
+    else:
+        mean, var, jac = ssm.predict_with_jacobians(p_center, k_ff)
+    prep = lambda t: None if t is None else t.detach().to(device=dev, dtype=dt).contiguous()
+    p, u, q, mean, var, jac = (prep(t) for t in (p_center, k_ff, q_shape, mean, var, jac))
+    assert_shape(mean, (N, n_s))
+    assert_shape(var, (N, n_s))
+    assert_shape(jac, (N, n_s, n_s + prob.n_u), ignore_if_none=True)
+    p1 = torch.empty((N, n_s), dtype=dt, device=dev)
+    q1 = torch.empty((N, n_s, n_s), dtype=dt, device=dev)
+    sig = torch.empty((N, n_s), dtype=dt, device=dev)
+    flags = torch.zeros(4, dtype=torch.int32, device=dev)
+    if N > 0:
+        cs = prob.c_struct()
+        with torch.cuda.device(dev):
+            _lib.check(lib.se_reach_step(code, C.byref(cs), _lib.ptr(p), _lib.ptr(q), _lib.ptr(u), _lib.ptr(mean),
+                                         _lib.ptr(var), _lib.ptr(jac), N, _lib.ptr(p1), _lib.ptr(q1), _lib.ptr(sig),
+                                         _lib.ptr(flags), _lib.stream_ptr(dev)))
+        check_flags(flags.cpu(), 'onestep_reachability')
+    return p1, q1, sig
 
 
 def onestep_reachability(p_center: Tensor, ssm: CemSSM, k_ff: Tensor, l_mu: Tensor, l_sigma: Tensor,
@@ -109,8 +148,9 @@ def onestep_reachability(p_center: Tensor, ssm: CemSSM, k_ff: Tensor, l_mu: Tens
                          verbose: int = 1, a: Optional[Tensor] = None, b: Optional[Tensor] = None
                          ) -> Tuple[Tensor, Tensor, Tensor]:
     """Drop-in for gp_reachability_pytorch.onestep_reachability (:18-181): same arguments, same returns
-    (p_1 [N, n_s], q_1 [N, n_s, n_s], sigma [N, n_s]); `verbose` is accepted and ignored."""
-    gp = _gp_of(ssm)
+    (p_1 [N, n_s], q_1 [N, n_s, n_s], sigma [N, n_s]); `verbose` is accepted and ignored.  `ssm` may be any CemSSM:
+    a B200GpCemSSM is evaluated inside the kernels, any other model through its own predict_* methods."""
+    gp = ssm
     N = p_center.shape[0]
     n_s, n_u = gp.num_states, gp.num_actions
     assert_shape(p_center, (N, n_s))
@@ -122,6 +162,8 @@ def onestep_reachability(p_center: Tensor, ssm: CemSSM, k_ff: Tensor, l_mu: Tens
     assert_shape(a, (n_s, n_s), ignore_if_none=True)
     assert_shape(b, (n_s, n_u), ignore_if_none=True)
     prob = SafeProblem(n_s, n_u, l_mu, l_sigma, k_fb=k_fb, a=a, b=b if a is not None else None, c_safety=c_safety)
+    if not isinstance(ssm, B200GpCemSSM):
+        return _onestep_generic_ssm(p_center, ssm, k_ff, prob, q_shape)
     dev, dt = p_center.device, gp.dtype
     p = gp._prep(p_center, 'p_center')
     u = gp._prep(k_ff, 'k_ff')

@@ -15,8 +15,8 @@ from torch import Tensor
 
 from . import _lib
 from .cem import ActionConstraint, B200ConstrainedCemMpc, Constraint, DynamicsFunc, TorchPolytope, box2torchpoly
-from .reachability import SafeProblem, is_ellipsoid_inside_polytope, onestep_reachability
-from .ssm import B200GpCemSSM, assert_shape
+from .reachability import SafeProblem, is_ellipsoid_inside_polytope, multistep_reachability, onestep_reachability
+from .ssm import B200GpCemSSM, CemSSM, assert_shape
 
 
 class MpcResult(Enum):
@@ -96,6 +96,11 @@ class EllipsoidStateConstraint(Constraint):
         inside = is_ellipsoid_inside_polytope(p, q, self._polytope_a.to(p), self._polytope_b.to(p))
         return (inside.size(0) - inside.sum()) * 10
 
+    def batch_call(self, trajectories: Tensor, actions: Tensor) -> Tensor:
+        """All rollouts at once (interface path of B200ConstrainedCemMpc): trajectories [N, T+1, S] -> costs [N]."""
+        return _batch_inside_cost(self._pq_flattener, trajectories[:, 1:] if self.all_states else trajectories[:, -1:],
+                                  self._polytope_a, self._polytope_b)
+
 
 class EllipsoidTerminalConstraint(Constraint):
     """safempc_cem.py:102-113."""
@@ -107,6 +112,9 @@ class EllipsoidTerminalConstraint(Constraint):
 
     def __call__(self, trajectory, actions) -> float:
         return self._constraint(trajectory[-1:, :], actions[-1:, :])
+
+    def batch_call(self, trajectories: Tensor, actions: Tensor) -> Tensor:
+        return self._constraint.batch_call(trajectories, actions)
 
 
 class EllipsoidObstacleConstraint(Constraint):
@@ -130,6 +138,22 @@ class EllipsoidObstacleConstraint(Constraint):
         inside = is_ellipsoid_inside_polytope(p, q, self._polytope_a.to(p), self._polytope_b.to(p))
         return (inside.size(0) - inside.sum()) * 10
 
+    def batch_call(self, trajectories: Tensor, actions: Tensor) -> Tensor:
+        if trajectories.shape[1] <= 2:
+            return torch.zeros((trajectories.shape[0],), dtype=trajectories.dtype, device=trajectories.device)
+        return _batch_inside_cost(self._pq_flattener, trajectories[:, 1:-1], self._polytope_a, self._polytope_b)
+
+
+def _batch_inside_cost(flattener: PQFlattener, states: Tensor, polytope_a: Tensor, polytope_b: Tensor) -> Tensor:
+    """10 x #{ellipsoids of each rollout not strictly inside the polytope}: states [N, K, S] -> [N]."""
+    N, K, S = states.shape
+    n_s = flattener._state_dimen
+    flat = states.reshape(N * K, S)
+    p = flat[:, :n_s].contiguous()
+    q = flat[:, n_s:].reshape(N * K, n_s, n_s).contiguous()
+    inside = is_ellipsoid_inside_polytope(p, q, polytope_a.to(p), polytope_b.to(p)).reshape(N, K)
+    return 10.0 * (K - inside.sum(dim=1)).to(states.dtype)
+
 
 def construct_constraints(conf, env) -> List[Constraint]:
     """safempc_cem.py:135-146: [ActionConstraint(normalised action box), Ellipsoid{State|Terminal}Constraint]."""
@@ -152,10 +176,32 @@ class B200SafeDynamics(DynamicsFunc):
     the GP and the constants of one ellipsoid step.  Calling it performs one batched step on the device, so it also
     works as a plain `DynamicsFunc`."""
 
-    def __init__(self, ssm: B200GpCemSSM, problem: SafeProblem):
+    def __init__(self, ssm: CemSSM, problem: SafeProblem, objective_fn: Optional[Callable] = None):
+        """:param ssm: a B200GpCemSSM (evaluated inside the kernels) or any other CemSSM (its predict_* methods are
+                       called per step and the ellipsoid algebra runs on the device: the interface path)
+        :param objective_fn: optional `env.objective_cost_function` (safempc_cem.py:304-312): called per step with the
+                       new centres [N, n_s]; a `None` return selects the default -sum(variance)"""
         self.ssm = ssm
         self.problem = problem
+        self.objective_fn = objective_fn
         self._pq = PQFlattener(ssm.num_states)
+
+    @property
+    def fusable(self) -> bool:
+        """Can the whole rollout run inside se_cem_solve?  Needs the B200 GP and a built-in objective selector."""
+        return isinstance(self.ssm, B200GpCemSSM) and self.objective_fn is None
+
+    def _objective_cost(self, p_next: Tensor, sigma: Tensor) -> Tensor:
+        """safempc_cem.py:304-312."""
+        pr = self.problem
+        if self.objective_fn is not None:
+            cost = self.objective_fn(p_next)
+            return -torch.sum(sigma, dim=1) if cost is None else cost
+        if pr.objective == _lib.SE_OBJ_NEG_VARIANCE:
+            return -torch.sum(sigma, dim=1)
+        if pr.objective == _lib.SE_OBJ_ABS_STATE1:
+            return torch.abs(pr.objective_theta - p_next[:, 1])
+        return -p_next[:, -1]
 
     def __call__(self, states: Tensor, actions: Tensor) -> Tuple[Tensor, Tensor]:
         pr = self.problem
@@ -165,13 +211,79 @@ class B200SafeDynamics(DynamicsFunc):
         p_next, q_next, sigma = onestep_reachability(ps.contiguous(), self.ssm, actions, t(pr.l_mu), t(pr.l_sigma), qs,
                                                      k_fb=t(pr.k_fb), a=t(pr.a), b=t(pr.b), verbose=0,
                                                      c_safety=pr.c_safety)
-        if pr.objective == _lib.SE_OBJ_NEG_VARIANCE:
-            cost = -torch.sum(sigma, dim=1)
-        elif pr.objective == _lib.SE_OBJ_ABS_STATE1:
-            cost = torch.abs(pr.objective_theta - p_next[:, 1])
-        else:
-            cost = -p_next[:, -1]
-        return self._pq.flatten(p_next, q_next), cost
+        return self._pq.flatten(p_next, q_next), self._objective_cost(p_next, sigma)
+
+    def rollout_batch(self, initial_states: Tensor, actions: Tensor):
+        """All T steps of N rollouts in ONE device call (`se_reach_multistep`) when the model is the B200 GP and the
+        rollouts start from point states -- the case of a callable `env.objective_cost_function`: the objective is then
+        evaluated per step on the recorded centres.  -> (trajectories [N, T+1, S], objective_costs [N]), or None when
+        the per-step `__call__` has to be used."""
+        if not isinstance(self.ssm, B200GpCemSSM):
+            return None
+        ps, qs = self._pq.unflatten(initial_states)
+        if qs is not None:
+            return None
+        pr = self.problem
+        N, T = actions.shape[0], actions.shape[1]
+        _, _, p_all, q_all, s_all = multistep_reachability(ps.contiguous(), self.ssm, pr.k_fb, actions, pr.l_mu,
+                                                           pr.l_sigma, None, c_safety=pr.c_safety, a=pr.a, b=pr.b)
+        n_s = self.ssm.num_states
+        traj = torch.empty((N, T + 1, n_s + n_s * n_s), dtype=p_all.dtype, device=p_all.device)
+        traj[:, 0] = self._pq.flatten(ps.to(p_all.dtype), None)
+        traj[:, 1:, :n_s] = p_all
+        traj[:, 1:, n_s:] = q_all.reshape(N, T, n_s * n_s)
+        cost = torch.zeros((N,), dtype=p_all.dtype, device=p_all.device)
+        for t in range(T):
+            cost += self._objective_cost(p_all[:, t], s_all[:, t]).to(cost)
+        return traj, cost
+
+
+def can_fold(constraint) -> bool:
+    """Is this one of the constraint classes the fused kernels evaluate themselves?"""
+    return isinstance(constraint, (ActionConstraint, EllipsoidTerminalConstraint, EllipsoidStateConstraint,
+                                   EllipsoidObstacleConstraint))
+
+
+_OBJ_CALLABLE = -1  # not a built-in selector: env.objective_cost_function is called on the recorded centres
+
+
+def classify_objective(env) -> Tuple[int, float, Optional[Callable]]:
+    """Which objective does `env` ask for (safempc_cem.py:304-312)?  -> (selector, theta, callable | None).
+
+    An explicit `env.objective_spec = (kind, theta)` wins.  Otherwise `env.objective_cost_function` is probed on a few
+    fixed centres: `None` selects the default -sum(variance); a function that reproduces one of the reference's two
+    environment objectives exactly -- |theta - p[:, 1]| (InvertedPendulum, environments.py:505-510) or -p[:, -1]
+    (LunarLander, lunarlander.py:111-113) -- selects the kernel's built-in form of it (theta is read off the probe,
+    and re-read before every solve, so an advancing target is followed); anything else stays a Python callable and
+    the solver evaluates it per step on the recorded centres (interface path)."""
+    names = {'neg_variance': _lib.SE_OBJ_NEG_VARIANCE, 'abs_state1': _lib.SE_OBJ_ABS_STATE1,
+             'neg_last_state': _lib.SE_OBJ_NEG_LAST_STATE}
+    spec = getattr(env, 'objective_spec', None)
+    if spec is not None:
+        kind, theta = spec
+        return names[kind], float(theta), None
+    fn = getattr(env, 'objective_cost_function', None)
+    if fn is None:
+        return _lib.SE_OBJ_NEG_VARIANCE, 0.0, None
+    n_s = env.n_s
+    gen = torch.Generator().manual_seed(20240229)
+    probe = torch.randn((6, n_s), generator=gen, dtype=torch.float64)
+    probe[0] = 0.0
+    try:
+        out = fn(probe)
+    except Exception:  # e.g. a function that insists on its own device: treat it as opaque
+        return _OBJ_CALLABLE, 0.0, fn
+    if out is None:
+        return _lib.SE_OBJ_NEG_VARIANCE, 0.0, None
+    out = torch.as_tensor(out, dtype=torch.float64).reshape(-1)
+    if out.shape[0] == probe.shape[0]:
+        if torch.equal(out, -probe[:, -1]):
+            return _lib.SE_OBJ_NEG_LAST_STATE, 0.0, None
+        if n_s >= 2:
+            for theta in (float(out[0]), -float(out[0])):  # probe[0, 1] = 0, so out[0] = |theta|
+                if torch.equal(out, torch.abs(theta - probe[:, 1])):
+                    return _lib.SE_OBJ_ABS_STATE1, theta, None
+    return _OBJ_CALLABLE, 0.0, fn
 
 
 def fold_constraints(problem: SafeProblem, constraints: Sequence[Constraint]) -> SafeProblem:
@@ -225,11 +337,14 @@ class B200CemSafeMPC(SafeMPC):
     `env` needs n_s, n_u, l_mu, l_sigm, objective_cost_function (and optionally `objective_spec`), `conf` needs
     mpc_time_horizon, cem_num_rollouts, cem_num_elites, cem_num_iterations, use_prior_model."""
 
-    def __init__(self, ssm: B200GpCemSSM, constraints: Sequence[Constraint], env, conf, opt_env, wx_feedback_cost,
+    def __init__(self, ssm: CemSSM, constraints: Sequence[Constraint], env, conf, opt_env, wx_feedback_cost,
                  wu_feedback_cost, beta_safety: float, safe_policy: Callable[[ndarray], ndarray],
                  lqr: Optional[LqrFeedbackController] = None, mpc: Optional[B200ConstrainedCemMpc] = None,
                  verbose: bool = True) -> None:
         super().__init__()
+        self._env = env
+        self._conf = conf
+        self._constraints = list(constraints)
         self._state_dimen = env.n_s
         self._action_dimen = env.n_u
         self._pq_flattener = PQFlattener(env.n_s)
@@ -250,36 +365,44 @@ class B200CemSafeMPC(SafeMPC):
         # safempc_cem.py:291-296: zeros (not identity) when the prior is disabled (quirk Q9)
         a = self._linearized_model_a if self._use_prior_model else np.zeros_like(self._linearized_model_a)
         b = self._linearized_model_b if self._use_prior_model else np.zeros_like(self._linearized_model_b)
-        objective, theta = self._objective_of(env)
         k_fb = lqr.get_control_matrix_pytorch() if hasattr(lqr, 'get_control_matrix_pytorch') else lqr
-        problem = SafeProblem(env.n_s, env.n_u, env.l_mu, env.l_sigm, k_fb=k_fb, a=a, b=b, c_safety=beta_safety,
-                              objective=objective, objective_theta=theta)
-        self._dynamics = B200SafeDynamics(ssm, problem)
-        if mpc is None:
-            mpc = B200ConstrainedCemMpc(self._dynamics, constraints=constraints,
-                                        state_dimen=self._pq_flattener.get_flat_state_dimen(), action_dimen=env.n_u,
-                                        time_horizon=self._mpc_time_horizon, num_rollouts=conf.cem_num_rollouts,
-                                        num_elites=conf.cem_num_elites, num_iterations=conf.cem_num_iterations,
-                                        record=getattr(conf, 'cem_record', 'costs'))
+        self._base_problem = SafeProblem(env.n_s, env.n_u, env.l_mu, env.l_sigm, k_fb=k_fb, a=a, b=b,
+                                         c_safety=beta_safety,
+                                         clamp_nonpositive=bool(getattr(conf, 'cem_clamp_nonpositive_variance', False)))
+        self._objective_class = None
+        self._mpc_injected = mpc is not None
         self._mpc = mpc
+        self._dynamics = None
+        self._refresh_objective()
         self._last_mpc_actions = np.empty((0, self.action_dimen))
         self._mpc_actions_executed = 0
 
-    @staticmethod
-    def _objective_of(env) -> Tuple[int, float]:
-        """safempc_cem.py:304-312: the env's objective if it has one, else -sum(variance).  Environments describe
-        theirs declaratively through `objective_spec = (kind, theta)` so it can run inside the kernel."""
-        spec = getattr(env, 'objective_spec', None)
-        if spec is None:
-            probe = env.objective_cost_function(torch.zeros((1, env.n_s), dtype=torch.float64)) \
-                if hasattr(env, 'objective_cost_function') else None
-            if probe is not None:
-                raise TypeError('env.objective_cost_function is an arbitrary Python function; give the environment an '
-                                '`objective_spec` = ("abs_state1", theta) | ("neg_last_state", 0) | None instead')
-            return _lib.SE_OBJ_NEG_VARIANCE, 0.0
-        kind, theta = spec
-        return {'neg_variance': _lib.SE_OBJ_NEG_VARIANCE, 'abs_state1': _lib.SE_OBJ_ABS_STATE1,
-                'neg_last_state': _lib.SE_OBJ_NEG_LAST_STATE}[kind], float(theta)
+    def _refresh_objective(self) -> None:
+        """safempc_cem.py:304-312 reads `env.objective_cost_function` on every step; here the objective is classified
+        (classify_objective) before every solve, so a target that advances during an episode
+        (environments.py:488-515) is followed: a new theta updates the device-side problem, a change of class
+        (built-in <-> callable) rebuilds the optimiser."""
+        kind, theta, fn = classify_objective(self._env)
+        cls = (kind, fn is not None)
+        if cls == self._objective_class:
+            if fn is None and self._mpc is not None and getattr(self._mpc, 'fused', False):
+                self._mpc.set_objective(kind, theta)
+            elif self._dynamics is not None:
+                self._dynamics.objective_fn = fn
+            return
+        self._objective_class = cls
+        problem = self._base_problem.with_(objective=max(kind, 0), objective_theta=theta)
+        self._dynamics = B200SafeDynamics(self._ssm, problem, objective_fn=fn)
+        if self._mpc_injected:
+            return
+        conf, env = self._conf, self._env
+        if self._mpc is not None and hasattr(self._mpc, '_destroy'):
+            self._mpc._destroy()
+        self._mpc = B200ConstrainedCemMpc(self._dynamics, constraints=self._constraints,
+                                          state_dimen=self._pq_flattener.get_flat_state_dimen(), action_dimen=env.n_u,
+                                          time_horizon=self._mpc_time_horizon, num_rollouts=conf.cem_num_rollouts,
+                                          num_elites=conf.cem_num_elites, num_iterations=conf.cem_num_iterations,
+                                          record=getattr(conf, 'cem_record', 'costs'))
 
     @property
     def state_dimen(self) -> int:
@@ -310,12 +433,14 @@ class B200CemSafeMPC(SafeMPC):
     def get_action(self, state: ndarray) -> Tuple[ndarray, MpcResult]:
         """safempc_cem.py:231-263."""
         assert_shape(state, (self._state_dimen,))
+        self._refresh_objective()
         if hasattr(self._mpc, 'get_actions_point'):
             # point state in, plan out: one small copy each way (the solver reuses its buffers, so the library replays
             # its CUDA graph of the solve)
             mpc_actions = self._mpc.get_actions_point(state)
         else:
-            state_batch = torch.tensor(state, dtype=self._ssm.dtype, device=self._ssm.device).unsqueeze(0)
+            state_batch = torch.tensor(state, dtype=getattr(self._ssm, 'dtype', torch.float64),
+                                       device=getattr(self._ssm, 'device', 'cuda:0')).unsqueeze(0)
             mpc_actions, _ = self._mpc.get_actions(self._pq_flattener.flatten(state_batch, None), reuse_outputs=True)
             mpc_actions = mpc_actions.detach().cpu().numpy() if mpc_actions is not None else mpc_actions
         if mpc_actions is not None:
@@ -350,9 +475,18 @@ class B200CemSafeMPC(SafeMPC):
         if getattr(self, '_batch_plans', None) is None or len(self._batch_plans) != m:
             self._batch_plans = [np.empty((0, self.action_dimen)) for _ in range(m)]
             self._batch_executed = [0] * m
-        dev_states = torch.as_tensor(states, dtype=self._ssm.dtype, device=self._ssm.device)
-        plans, found = self._mpc.get_actions_batch(dev_states, reuse_outputs=True)
-        plans, found = plans.detach().cpu().numpy(), found.cpu().numpy()
+        self._refresh_objective()
+        if getattr(self._mpc, 'fused', True):
+            dev_states = torch.as_tensor(states, dtype=self._ssm.dtype, device=self._ssm.device)
+            plans, found = self._mpc.get_actions_batch(dev_states, reuse_outputs=True)
+            plans, found = plans.detach().cpu().numpy(), found.cpu().numpy()
+        else:  # interface path (Python callbacks): one optimisation per scenario, like the reference's loop
+            plans = np.zeros((m, self._mpc_time_horizon, self.action_dimen))
+            found = np.zeros((m,), dtype=bool)
+            for i in range(m):
+                plan = self._mpc.get_actions_point(states[i])
+                if plan is not None:
+                    plans[i], found[i] = plan, True
         actions = np.empty((m, self.action_dimen))
         results = []
         for i in range(m):
@@ -381,14 +515,14 @@ class B200CemSafeMPC(SafeMPC):
         x_s = x[:, :self.state_dimen]
         x_u = x[:, self.state_dimen:]
         y_error = y - self.eval_prior(x_s, x_u) if self._use_prior_model else y
-        dev = self._ssm.device
+        dev = getattr(self._ssm, 'device', 'cuda:0')
         self._ssm.update_model(torch.tensor(x, device=dev), torch.tensor(y_error, device=dev), opt_hyp, replace_old)
 
     def information_gain(self) -> Union[ndarray, List[None]]:
         return [None] * self.state_dimen
 
     def ssm_predict(self, z: ndarray) -> Tuple[ndarray, ndarray]:
-        mean, sigma = self._ssm.predict_raw(torch.tensor(z, device=self._ssm.device))
+        mean, sigma = self._ssm.predict_raw(torch.tensor(z, device=getattr(self._ssm, 'device', 'cuda:0')))
         return mean.detach().cpu().numpy(), sigma.detach().cpu().numpy()
 
     def eval_prior(self, states: ndarray, actions: ndarray):

@@ -151,6 +151,7 @@ class B200GpCemSSM(CemSSM):
         self._tc_digits = tc_digits
         self._workspace_bytes = workspace_bytes
         self._handle = C.c_void_p(None)
+        self.generation = 0  # bumped by every _update_model: dependents (CEM handles) key on it, never on the address
         self._last_training_losses = []
 
     # ---- handle management -------------------------------------------------------------------------------------
@@ -226,6 +227,7 @@ class B200GpCemSSM(CemSSM):
                                               _lib.stream_ptr(self.device)))
             torch.cuda.current_stream(self.device).synchronize()  # xs / al / li may be freed after this
         self._handle = handle
+        self.generation += 1
         if self._gemm_impl != _lib.SE_GEMM_AUTO:
             _lib.check(self._lib.se_gp_set_gemm_impl(handle, self._gemm_impl))
         if self._tc_digits:

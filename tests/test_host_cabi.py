@@ -52,7 +52,7 @@ def test_struct_layouts_match_header(tmp_path):
         assert int(got[cname]) == ctypes.sizeof(cls), cname
         for field, _ in cls._fields_:
             assert int(got[f'{cname}.{field}']) == getattr(cls, field).offset, f'{cname}.{field}'
-    assert ctypes.sizeof(_lib.SeProblem) == 160  # 144 before the obstacle polytope (m_obs, h_mat_obs, h_vec_obs)
+    assert ctypes.sizeof(_lib.SeProblem) == 168  # 160 before clamp_nonpositive, 144 before the obstacle polytope
 
 
 def test_argument_errors_are_reported_without_a_gpu():
@@ -160,8 +160,14 @@ def test_cem_constructor_contract():
     assert mpc._num_iterations == 3 and mpc._rollout_function._constraints[1] is cons[1]  # safempc_cem.py:270, 280
     with pytest.raises(ValueError):
         se.B200ConstrainedCemMpc(dyn, cons, 5, 1, 5, 64, 8, 3)
-    with pytest.raises(TypeError):
-        se.B200ConstrainedCemMpc(lambda s, a: (s, a), cons, 6, 1, 5, 64, 8, 3)
+    # an arbitrary DynamicsFunc selects the interface path (reference-shaped loop on device tensors) ...
+    generic = se.B200ConstrainedCemMpc(lambda s, a: (s, a), cons, 6, 1, 5, 64, 8, 3)
+    assert not generic.fused and mpc.fused
+    assert generic._rollout_function._constraints[1] is cons[1]
+    with pytest.raises(_lib.SecemError):  # ... which is not a CPU fallback: host tensors are refused
+        generic.get_actions(torch.zeros(6))
+    with pytest.raises(TypeError):  # batching / sharding exist on the fused path only
+        se.B200ConstrainedCemMpc(lambda s, a: (s, a), cons, 6, 1, 5, 64, 8, 3, num_instances=4)
     with pytest.raises(_lib.SecemError):
         mpc.get_actions(torch.zeros(1, 6))  # no training data -> loud failure, no fallback
 
