@@ -219,6 +219,10 @@ typedef struct {
      world_size == 1: first_rollout = 0, local_rollouts = num_rollouts */
   int first_rollout;
   int local_rollouts;
+  /* instance sharding (BASELINE config "batched independent MPC solves"): global index of this handle's instance 0.
+     The candidate RNG is keyed by (seed, iteration, GLOBAL instance id, rollout id), so a batch of instances dealt out
+     to several GPUs draws exactly the candidates of the same batch solved on one.  0 for a single handle. */
+  int first_instance;
 } se_cem_config;
 
 typedef struct {

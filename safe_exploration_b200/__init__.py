@@ -9,6 +9,7 @@ Drop-in for the hot path of oscarkey/safe-exploration behind the reference's own
     constrained_cem_mpc.ConstrainedCemMpc                cem.B200ConstrainedCemMpc
     safempc_cem.CemSafeMPC (SafeMPC)                     safempc.B200CemSafeMPC
     utils_config.create_solver (safempc_cem branch)      utils_config.create_solver
+    episode_runner.do_rollout                            runner.do_rollout, runner.do_rollout_batch
 
 All numerics run in libsecem.so (csrc/, C ABI in include/secem.h); there is no CPU fallback.
 """
@@ -22,6 +23,7 @@ from .safempc import (B200CemSafeMPC, B200SafeDynamics, EllipsoidObstacleConstra
                       EllipsoidTerminalConstraint,
                       LqrFeedbackController, MpcResult, PQFlattener, SafeMPC, classify_objective,
                       construct_constraints, dlqr)
+from .runner import do_rollout, do_rollout_batch
 from .ssm import B200GpCemSSM, CemSSM, assert_shape
 from .utils_config import create_cem_ssm, create_solver
 

@@ -35,7 +35,7 @@ class SeProblem(C.Structure):
 class SeCemConfig(C.Structure):
     _fields_ = [("num_instances", C.c_int), ("num_rollouts", C.c_int), ("time_horizon", C.c_int),
                 ("num_elites", C.c_int), ("num_iterations", C.c_int), ("pick_best", C.c_int),
-                ("first_rollout", C.c_int), ("local_rollouts", C.c_int)]
+                ("first_rollout", C.c_int), ("local_rollouts", C.c_int), ("first_instance", C.c_int)]
 
 
 class SeCemOutputs(C.Structure):

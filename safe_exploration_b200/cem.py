@@ -195,7 +195,7 @@ class B200ConstrainedCemMpc:
     def __init__(self, dynamics_func, constraints: Sequence[Constraint], state_dimen: int, action_dimen: int,
                  time_horizon: int, num_rollouts: int, num_elites: int, num_iterations: int, rollout_function=None,
                  seed: int = 0, pick_best: bool = False, record: str = 'full', num_instances: int = 1,
-                 rank: int = 0, world_size: int = 1):
+                 rank: int = 0, world_size: int = 1, first_instance: int = 0):
         from .safempc import B200SafeDynamics, can_fold, fold_constraints  # local import: safempc imports this module
         if record not in ('full', 'costs', 'none'):
             raise ValueError(f'record must be full|costs|none, got {record}')
@@ -234,6 +234,7 @@ class B200ConstrainedCemMpc:
         self.pick_best = bool(pick_best)
         self.record = record
         self.num_instances = int(num_instances)
+        self.first_instance = int(first_instance)  # instance sharding: global index of this solver's instance 0
         self.rank, self.world_size = int(rank), int(world_size)
         self._lib = _lib.load()
         self._handle = C.c_void_p(None)
@@ -281,13 +282,15 @@ class B200ConstrainedCemMpc:
         gp_handle = self._ssm.handle
         # never key on the handle's address: update_model destroys and re-creates the model and the allocator readily
         # returns the same address (the library checks the generation too and refuses a stale GP handle)
-        key = (self._ssm.generation, self.num_instances, self.pick_best, self.rank, self.world_size)
+        key = (self._ssm.generation, self.num_instances, self.pick_best, self.rank, self.world_size,
+               self.first_instance)
         if self._handle and self._handle_key == key:
             return
         self._destroy()
         n_local = self._num_rollouts // self.world_size
         cfg = _lib.SeCemConfig(self.num_instances, self._num_rollouts, self._time_horizon, self._num_elites,
-                               self._num_iterations, 1 if self.pick_best else 0, self.rank * n_local, n_local)
+                               self._num_iterations, 1 if self.pick_best else 0, self.rank * n_local, n_local,
+                               self.first_instance)
         cs = self._problem.c_struct()
         handle = C.c_void_p(None)
         with torch.cuda.device(self._ssm.device):

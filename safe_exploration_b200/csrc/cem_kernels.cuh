@@ -45,6 +45,7 @@ struct ActionSrc {
   const uint64_t* seed_dev;  // when set, the seed is read from device memory (a replayed CUDA graph gets a new one)
   int iteration;
   int n_global;      // rollouts per instance over all ranks
+  int inst_offset;   // global index of local instance 0 (instance sharding): the RNG is keyed by GLOBAL instance id
   int tnu;           // T * n_u
   const T* ext;      // mode 1: noise [M, N_global, T*n_u] of this iteration; mode 2: actions [M, N_global, T*n_u]
   const double* mean;  // [M, T*n_u] sampling distribution of this iteration
@@ -60,7 +61,8 @@ __device__ __forceinline__ T candidate_action(const ActionSrc<T>& s, int inst, i
     z = (double)s.ext[flat];
   } else {
     double z0, z1;
-    philox_normal_pair(s.seed_dev ? *s.seed_dev : s.seed, (uint32_t)s.iteration, (uint32_t)(inst * s.n_global + gid), (uint32_t)(e >> 1), z0, z1);
+    philox_normal_pair(s.seed_dev ? *s.seed_dev : s.seed, (uint32_t)s.iteration,
+                       (uint32_t)((inst + s.inst_offset) * s.n_global + gid), (uint32_t)(e >> 1), z0, z1);
     z = (e & 1) ? z1 : z0;
   }
   // actions = means + stds * eps  ==  Normal(means, stds).sample()   (constrained_cem_mpc.py:167)

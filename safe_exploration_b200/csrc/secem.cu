@@ -842,7 +842,9 @@ extern "C" int se_cem_create(se_cem_t* out, se_gp_t gp, const se_problem* prob, 
   SE_REQUIRE(cfg->local_rollouts >= 1 && cfg->first_rollout >= 0 &&
                  cfg->first_rollout + cfg->local_rollouts <= cfg->num_rollouts,
              "se_cem_create: bad shard [%d, +%d) of %d", cfg->first_rollout, cfg->local_rollouts, cfg->num_rollouts);
-  SE_REQUIRE((int64_t)cfg->num_instances * cfg->num_rollouts < (1ll << 31), "se_cem_create: population too large");
+  SE_REQUIRE(cfg->first_instance >= 0 &&
+                 ((int64_t)cfg->first_instance + cfg->num_instances) * cfg->num_rollouts < (1ll << 31),
+             "se_cem_create: population too large");
   SE_REQUIRE(prob->n_s == gp->ns && prob->n_u == gp->nu, "se_cem_create: problem / GP dimension mismatch");
   SE_REQUIRE(prob->k_fb && prob->a && prob->b, "se_cem_create: k_fb, a, b are required");
   SE_REQUIRE(gp_live_generation(gp) != 0, "se_cem_create: the GP handle is not live (destroyed?)");
@@ -965,6 +967,7 @@ static int cem_solve_t(se_cem_s* c, const ProbDev<T>& pr, const T* p0, const T* 
   ActionSrc<T> src;
   memset(&src, 0, sizeof(src));
   src.seed = seed, src.seed_dev = seed_dev, src.n_global = Ng, src.tnu = tnu;
+  src.inst_offset = cf.first_instance;
   CostView<T> costs{pack_all, M, Nl};
 
   for (int it = 0; it < cf.num_iterations; ++it) {

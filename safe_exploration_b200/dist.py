@@ -77,6 +77,45 @@ def attach_population_sharding(mpc, group: Optional[dist.ProcessGroup] = None) -
     return comm
 
 
+def solve_instances_sharded(mpc, p0_all: torch.Tensor, seed: Optional[int] = None,
+                            group: Optional[dist.ProcessGroup] = None):
+    """BASELINE config C4 -- M independent MPC problems dealt out to the ranks of `group` (`shard_instances`), no
+    communication on the data path, results gathered on every rank at the end: what the per-scenario loop of
+    episode_runner.py:206-231 does one solve at a time.
+
+    :param mpc: this rank's fused B200ConstrainedCemMpc; its `first_instance` / `num_instances` are set here
+    :param p0_all: [M, n_s] initial states of ALL instances (host or device; every rank passes the same tensor)
+    :returns: plans [M, T, n_u], found [M] (bool) for all instances, in global instance order.  Identical to one batched
+              solve of all M instances on one GPU with the same seed (the candidate RNG is keyed by global instance id)."""
+    rank, world = (dist.get_rank(group), dist.get_world_size(group)) if dist.is_initialized() else (0, 1)
+    M = p0_all.shape[0]
+    first, count = shard_instances(M, rank, world)
+    dev = mpc._ssm.device
+    T_len, n_u = mpc._time_horizon, mpc._action_dimen
+    base, rem = divmod(M, world)
+    cap = base + (1 if rem else 0)  # every rank contributes a slab of the same size to the gather
+    plans = torch.zeros((cap, T_len, n_u), dtype=mpc._ssm.dtype, device=dev)
+    found = torch.zeros((cap,), dtype=torch.int32, device=dev)
+    if count > 0:
+        mpc.first_instance = first
+        res = mpc.solve(p0_all[first:first + count].to(device=dev, dtype=mpc._ssm.dtype), seed=seed)
+        plans[:count], found[:count] = res['actions'], res['found']
+    if world == 1:
+        return plans[:M], found[:M].bool()
+    backend = dist.get_backend(group)
+    send_p, send_f = (plans, found) if backend == 'nccl' else (plans.cpu(), found.cpu())
+    all_p = [torch.empty_like(send_p) for _ in range(world)]
+    all_f = [torch.empty_like(send_f) for _ in range(world)]
+    dist.all_gather(all_p, send_p, group=group)
+    dist.all_gather(all_f, send_f, group=group)
+    out_p, out_f = [], []
+    for r in range(world):
+        _, c = shard_instances(M, r, world)
+        out_p.append(all_p[r][:c])
+        out_f.append(all_f[r][:c])
+    return torch.cat(out_p), torch.cat(out_f).bool()
+
+
 def pack_costs(objective: torch.Tensor, constraint: torch.Tensor) -> torch.Tensor:
     """Local costs [M, N_local] x2 -> the send buffer layout of the device path: [2, M, N_local]
     (plane 0 = objective, plane 1 = constraint; csrc/cem_kernels.cuh `cem_pack_costs_kernel`)."""

@@ -196,7 +196,7 @@ def reach_microbench_workload(n_train=1024, n_s=2, num_ellipsoids=1 << 20, time_
 
 
 def build_solver(w: Workload, dtype=None, device='cuda:0', record='costs', pick_best=False, seed=0,
-                 num_instances=1, gemm_impl=0, rank=0, world_size=1):
+                 num_instances=1, gemm_impl=0, rank=0, world_size=1, first_instance=0):
     """Workload -> (B200GpCemSSM, B200ConstrainedCemMpc) wired exactly like CemSafeMPC.__init__ does."""
     import torch
     from .cem import ActionConstraint, B200ConstrainedCemMpc, TorchPolytope
@@ -214,5 +214,5 @@ def build_solver(w: Workload, dtype=None, device='cuda:0', record='costs', pick_
     mpc = B200ConstrainedCemMpc(B200SafeDynamics(ssm, problem), constraints, w.n_s + w.n_s ** 2, w.n_u,
                                 w.time_horizon, w.num_rollouts, w.num_elites, w.num_iterations, seed=seed,
                                 pick_best=pick_best, record=record, num_instances=num_instances, rank=rank,
-                                world_size=world_size)
+                                world_size=world_size, first_instance=first_instance)
     return ssm, mpc

@@ -93,3 +93,46 @@ def test_population_sharding_world2_matches_single_process(tmp_path):
             assert torch.equal(h[it][0], ref['elite_ids'][it])
             assert torch.allclose(h[it][1], ref['means'][it], rtol=1e-12, atol=1e-15)
             assert torch.allclose(h[it][2], ref['stds'][it], rtol=1e-12, atol=1e-15)
+
+
+# ---- instance sharding (BASELINE config C4): split + gather, world_size 2 over gloo ---------------------------------------
+class _FakeSolver:
+    """Stands for a fused B200ConstrainedCemMpc in the host-side split / gather logic: its "plan" for an instance is a
+    function of the instance's state and GLOBAL index, so a wrong split, a wrong offset or a wrong gather order shows."""
+
+    class _Ssm:
+        device, dtype = torch.device('cpu'), torch.float64
+
+    def __init__(self):
+        self._ssm, self._time_horizon, self._action_dimen = self._Ssm(), 3, 1
+        self.first_instance = 0
+
+    def solve(self, p0, seed=None):
+        m = p0.shape[0]
+        gid = torch.arange(self.first_instance, self.first_instance + m, dtype=torch.float64)
+        plan = (p0.sum(dim=1) + 100.0 * gid + seed).view(m, 1, 1).expand(m, 3, 1).clone()
+        return dict(actions=plan, found=(gid.long() % 2 == 0).to(torch.int32))
+
+
+def _instance_worker(rank, world, port, out_dir):
+    torch.set_default_dtype(torch.double)
+    os.environ.update(MASTER_ADDR='127.0.0.1', MASTER_PORT=str(port))
+    dist.init_process_group('gloo', rank=rank, world_size=world)
+    try:
+        p0_all = torch.arange(10, dtype=torch.float64).view(5, 2)
+        plans, found = sedist.solve_instances_sharded(_FakeSolver(), p0_all, seed=7)
+        torch.save((plans, found), os.path.join(out_dir, f'inst{rank}.pt'))
+    finally:
+        dist.destroy_process_group()
+
+
+def test_instance_sharding_world2_split_and_gather(tmp_path):
+    with socket.socket() as s:
+        s.bind(('127.0.0.1', 0))
+        port = s.getsockname()[1]
+    mp.spawn(_instance_worker, args=(2, port, str(tmp_path)), nprocs=2, join=True)
+    p0_all = torch.arange(10, dtype=torch.float64).view(5, 2)
+    want = _FakeSolver().solve(p0_all, seed=7)  # all five instances on one "GPU"
+    for rank in range(2):  # 3 + 2 instances; every rank ends up with all results in global order
+        plans, found = torch.load(os.path.join(tmp_path, f'inst{rank}.pt'))
+        assert torch.equal(plans, want['actions']) and torch.equal(found, want['found'].bool())

@@ -52,6 +52,7 @@ def test_struct_layouts_match_header(tmp_path):
         assert int(got[cname]) == ctypes.sizeof(cls), cname
         for field, _ in cls._fields_:
             assert int(got[f'{cname}.{field}']) == getattr(cls, field).offset, f'{cname}.{field}'
+    assert ctypes.sizeof(_lib.SeCemConfig) == 36
     assert ctypes.sizeof(_lib.SeProblem) == 168  # 160 before clamp_nonpositive, 144 before the obstacle polytope
 
 
@@ -263,3 +264,63 @@ def test_create_solver_wires_the_b200_classes():
         solver_type = 'safempc'
     with pytest.raises(ValueError, match='Unknown solver type'):
         se.create_solver(Casadi(), _PendulumEnv())
+
+
+def test_runner_host_logic_with_a_scripted_solver():
+    """do_rollout / do_rollout_batch (episode_runner.py:165-324): stacks start with the reference's zero row, exit codes
+    follow the MpcResult, a finished scenario keeps its slot, metrics carry the reference's names."""
+    from safe_exploration_b200.runner import do_rollout, do_rollout_batch
+    from safe_exploration_b200.safempc import MpcResult
+
+    class Env:
+        n_s, n_u = 2, 1
+
+        def __init__(self, x0, fail_at=None):
+            self.x0, self.fail_at, self.t = np.asarray(x0, float), fail_at, 0
+
+        def reset(self, mean=None, std=None):
+            self.x, self.t = self.x0.copy(), 0
+            return self.x
+
+        def step(self, action):
+            self.x = self.x + float(np.asarray(action).reshape(-1)[0])
+            self.t += 1
+            return np.asarray(action).reshape(1), self.x.copy(), 2 * self.x, self.fail_at == self.t, 7
+
+    class Solver:
+        def __init__(self):
+            self.batch_shapes = []
+
+        def get_action(self, state):
+            return np.array([0.5]), MpcResult.FOUND_SOLUTION if state[0] < 1 else MpcResult.SAFE_CONTROLLER
+
+        def get_action_batch(self, states):
+            self.batch_shapes.append(states.shape)
+            out = [self.get_action(s) for s in states]
+            return np.stack([a for a, _ in out]), [r for _, r in out]
+
+        def collect_metrics(self):
+            return {'losses': []}
+
+    class Sink:
+        def __init__(self):
+            self.s, self.n = {}, []
+
+        def log_scalar(self, k, v, step):
+            self.s[k] = v
+
+        def log_non_scalars(self, d, step):
+            self.n.append(d)
+
+    sink = Sink()
+    xx, yy, cc, codes, failed = do_rollout(Env([0., 0.]), 4, metrics=sink, solver=Solver(), cost=lambda s: s[0])
+    assert xx.shape == (5, 3) and not xx[0].any() and np.array_equal(xx[1:, 0], [0., .5, 1., 1.5])
+    assert np.array_equal(yy[1:, 0], [1., 2., 3., 4.]) and cc == [.5, 1., 1.5, 2.] and not failed
+    assert codes[:, 0].tolist() == [0, 1, 1, 0, 0]
+    assert sink.s['episode_length'] == 4 and sink.s['mpc_found_solution_count'] == 2
+    assert sink.s['safe_controller_fallback_count'] == 2 and sink.s['env_result'] == 7 and sink.n == [{'losses': []}]
+    solver = Solver()
+    res = do_rollout_batch([Env([0., 0.]), Env([5., 5.], fail_at=2), Env([0., 0.])], 4, solver)
+    assert solver.batch_shapes == [(3, 2)] * 4  # the finished scenario keeps its slot
+    assert np.array_equal(res[0][0], xx) and np.array_equal(res[2][0], xx)
+    assert res[1][0].shape == (3, 3) and res[1][4] and res[1][3][:, 0].tolist() == [0, 0, 0]
