@@ -8,7 +8,11 @@ on synthetic data of the BASELINE config C2 (InvertedPendulum, GP on 2000 traini
     python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference] [--dtype f64|f32] [--config C2|C1|C3]
 
 N > 1 is launched by the driver under torch.distributed.run (one rank per GPU): the population is sharded over the
-ranks (weak scaling: 16384 candidates per GPU) with one NCCL all-gather of candidate costs per CEM iteration.
+ranks (weak scaling: 16384 candidates per GPU) with one NCCL all-gather of candidate costs per CEM iteration.  The N > 1
+line also carries two side records measured in the same process: `strong_scaling` (BASELINE config C3: CartPole, n_train
+5000, horizon 15, population 65536 split over the N ranks) and `c4` (BASELINE config C4: independent pendulum MPC
+instances x population 4096, instance-sharded, 128 instances per GPU, results gathered on rank 0).  The N = 1 line
+carries a `c1` record: BASELINE config C1 (the reference's own CPU-sized case) with the CPU path timed in full beside it.
 `--impl reference` times the reference's CPU path (the float64 oracle port, all host threads) on a bounded sample of the
 same workload and prints the same JSON line with "impl": "reference".
 """
@@ -43,6 +47,7 @@ def parse_args():
                     help='digit planes of the tcgen05 variance GEMM (0 = chosen from outputscale / noise)')
     ap.add_argument('--cpu-sample', type=int, default=2048, help='candidates in the CPU-baseline sample')
     ap.add_argument('--no-cpu-baseline', action='store_true')
+    ap.add_argument('--no-side-records', action='store_true', help='skip the c1 / strong_scaling / c4 records')
     return ap.parse_args()
 
 
@@ -102,7 +107,11 @@ def run_reference(args):
     value, sec, threads = cpu_reference_run(w, args.cpu_sample, max(1, args.steps), max(0, min(args.warmup, 1)))
     line = {
         'impl': 'reference', 'metric': METRIC, 'value': value, 'unit': UNIT, 'n_gpus': args.gpus, 'steps': args.steps,
-        'warmup': args.warmup, 'ms_per_step': sec * 1e3, 'higher_is_better': True, 'scaling': 'weak',
+        'warmup': args.warmup, 'ms_per_step': sec * 1e3, 'ms_per_sample': sec * 1e3,
+        'step_definition': f'one step of this arm = one bounded SAMPLE of the workload ({args.cpu_sample} candidates x '
+                           f'1 CEM iteration at full n_train and horizon), not a whole solve; value = candidate-steps '
+                           f'of the sample / its time',
+        'higher_is_better': True, 'scaling': 'weak',
         'vs_baseline': None, 'dtype': 'f64', 'data': 'synthetic', 'config': workload_desc(w, 1, 'f64'),
         'cpu_baseline': {'value': value, 'unit': UNIT, 'cores': threads, 'kind': 'port',
                          'sample': f'{args.cpu_sample} candidates x horizon {w.time_horizon} x 1 CEM iteration at full '
@@ -187,21 +196,21 @@ class ClockSampler:
                 'reasons': sorted(self.reasons), 'samples': len(self.samples)}
 
 
-def profiled_traffic(kernel_substr: str):
-    """DRAM bytes (read + write) per launch of the dominant kernel from the committed `ncu --set full` capture of this
-    workload (profiles/r01_ncu_full_tc_c2.csv), or None.  The capture is of the default C2 / tcgen05 configuration."""
-    import csv
-    path = os.path.join(ROOT, 'profiles', 'r01_ncu_full_tc_c2.csv')
+def profiled_traffic(kernel_name: str, workload: str):
+    """DRAM bytes (read + write) per launch of the dominant kernel from the committed `ncu --set full` capture
+    (profiles/ncu_traffic.json, written by tools/ncu_traffic.py from the capture's raw page together with the commit,
+    kernel name and workload it was taken on).  Returns (bytes | None, stamp): None when no capture matches the kernel
+    that ran -- a stale figure is worse than none."""
+    path = os.path.join(ROOT, 'profiles', 'ncu_traffic.json')
     try:
-        rows = list(csv.reader(open(path)))
-        head, units = rows[0], rows[1]
-        name, rd, wr = head.index('Kernel Name'), head.index('dram__bytes_read.sum'), head.index('dram__bytes_write.sum')
-        scale = {'byte': 1.0, 'Kbyte': 1e3, 'Mbyte': 1e6, 'Gbyte': 1e9}
-        vals = [float(r[rd]) * scale[units[rd]] + float(r[wr]) * scale[units[wr]]
-                for r in rows[2:] if kernel_substr in r[name]]
-        return sum(vals) / len(vals) if vals else None
+        with open(path) as f:
+            entries = json.load(f)
     except Exception:
-        return None
+        return None, None
+    for e in entries:
+        if e.get('kernel') == kernel_name and e.get('workload') == workload:
+            return e.get('dram_bytes_per_launch'), {k: e.get(k) for k in ('commit', 'kernel', 'workload', 'source')}
+    return None, {'note': f'no committed capture of {kernel_name} on {workload}'}
 
 
 def measured_peaks():
@@ -213,6 +222,146 @@ def measured_peaks():
 
 
 # ---- the B200 arm ----------------------------------------------------------------------------------------------------------
+def _timed_solves(lib, _lib, ssm, mpc, p0, steps, barrier, dev, instrument, seed=None):
+    """K solves between two CUDA events on the solve stream.  instrument=False: the production path (CUDA graphs, fused
+    steps); instrument=True: the library brackets every variance-GEMM / kernel-row launch with events
+    (se_gp_timing_enable), which switches graphs and step fusion off -- used only for the per-kernel split."""
+    import ctypes as C
+    if instrument:
+        _lib.check(lib.se_gp_timing_enable(ssm.handle, 1))
+    lib.se_launch_count_reset()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    ev0.record()
+    res = None
+    for _ in range(steps):
+        res = mpc.solve(p0, sync=False, seed=seed)
+    ev1.record()
+    barrier()
+    ms_total = ev0.elapsed_time(ev1)
+    out = dict(ms_total=ms_total, launches=int(lib.se_launch_count()), res=res)
+    if instrument:
+        gemm_ms, kstar_ms = C.c_double(0), C.c_double(0)
+        gemm_n, kstar_n = C.c_int64(0), C.c_int64(0)
+        _lib.check(lib.se_gp_timing_read(ssm.handle, C.byref(gemm_ms), C.byref(gemm_n), C.byref(kstar_ms),
+                                         C.byref(kstar_n), _lib.stream_ptr(dev)))
+        _lib.check(lib.se_gp_timing_enable(ssm.handle, 0))
+        out.update(gemm_ms=gemm_ms.value, gemm_n=int(gemm_n.value), kstar_ms=kstar_ms.value, kstar_n=int(kstar_n.value))
+    return out
+
+
+def _max_over_ranks(x, world, dev):
+    if world == 1:
+        return x
+    import torch.distributed as dist
+    t = torch.tensor([x], device=dev, dtype=torch.float64)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    return float(t.item())
+
+
+def _gemm_kernel_name(digits):
+    mode = int(os.environ.get('SE_OZ_REUSE', '2'))
+    return f'oz::gp_trisumsq_ozaki_kernel<{digits},{mode}>'
+
+
+def side_record_c1(lib, _lib, workloads, dev, dtype, barrier, with_cpu):
+    """BASELINE config C1 (the only config the reference runs on its own CPU path today): GPU solve time, and the CPU
+    path (oracle port with the reference's per-item loops, all host threads) timed IN FULL, median of 5 solves
+    (BASELINE.md section 2)."""
+    w = make_workload('C1', 1)
+    ssm, mpc = workloads.build_solver(w, dtype=dtype, device=dev, record='none', seed=77)
+    p0 = torch.as_tensor(w.p0, device=dev, dtype=dtype).unsqueeze(0)
+    for _ in range(5):
+        mpc.solve(p0, sync=False)
+    t = _timed_solves(lib, _lib, ssm, mpc, p0, 50, barrier, dev, False)
+    ms = t['ms_total'] / 50
+    cand_steps = w.num_rollouts * w.time_horizon * w.num_iterations
+    rec = {'workload': workload_desc(w, 1, 'f64')['workload'], 'ms_per_solve': ms, 'value': cand_steps / (ms * 1e-3),
+           'unit': UNIT, 'solves_timed': 50, 'gpu_launches_per_solve': t['launches'] / 50}
+    if with_cpu:
+        from oracle import oracle
+        threads = os.cpu_count() or 1
+        torch.set_num_threads(threads)
+        T = lambda x: torch.as_tensor(np.asarray(x, dtype=np.float64))
+        gp = oracle.OracleGpCemSSM(w.n_s, w.n_u, w.lengthscale, w.outputscale, w.noise)
+        gp.update_model(T(w.x_train), T(w.y_train), replace_old=True)
+        prob = oracle.SafeCemProblem(gp, w.l_mu, w.l_sigma, w.k_fb, w.a, w.b, w.beta_safety, w.h_mat, w.h_vec, w.act_a,
+                                     w.act_b)
+        times = []
+        for rep in range(6):
+            noise = T(np.stack([oracle.philox_normal_noise(rep, i, 0, w.num_rollouts, w.time_horizon, w.n_u)
+                                for i in range(w.num_iterations)]))
+            t0 = time.perf_counter()
+            oracle.cem_solve(prob, T(w.p0), noise, w.num_elites, loops=True)
+            if rep > 0:
+                times.append(time.perf_counter() - t0)
+        sec = float(np.median(times))
+        rec['cpu_baseline'] = {'value': cand_steps / sec, 'unit': UNIT, 'cores': threads, 'kind': 'port',
+                               'ms_per_solve': sec * 1e3,
+                               'sample': 'the whole C1 solve (500 candidates x horizon 5 x 8 iterations), median of 5, '
+                                         'float64 eager torch, reference per-item loops kept'}
+        rec['gpu_over_cpu'] = sec * 1e3 / ms
+    mpc._destroy()
+    return rec
+
+
+def side_record_strong_scaling(lib, _lib, workloads, sedist, dev, dtype, rank, world, barrier):
+    """BASELINE config C3 at its full size with the population split over the ranks (strong scaling): CartPole, n_train
+    5000, horizon 15, population 65536, 8 iterations; 3 timed solves + one instrumented solve for the kernel split."""
+    w = workloads.cartpole_workload(num_rollouts=65536)
+    ssm, mpc = workloads.build_solver(w, dtype=dtype, device=dev, record='none', seed=4321)
+    comm = sedist.attach_population_sharding(mpc) if world > 1 else 0
+    p0 = torch.as_tensor(w.p0, device=dev, dtype=dtype).unsqueeze(0)
+    mpc.solve(p0, sync=False)
+    t = _timed_solves(lib, _lib, ssm, mpc, p0, 3, barrier, dev, False)
+    ms = _max_over_ranks(t['ms_total'], world, dev) / 3
+    ti = _timed_solves(lib, _lib, ssm, mpc, p0, 1, barrier, dev, True)
+    cand_steps = w.num_rollouts * w.time_horizon * w.num_iterations
+    impl, digits = ssm.gemm_info()
+    rec = {'workload': workload_desc(w, world, 'f64')['workload'], 'scaling': 'strong', 'n_gpus': world,
+           'ms_per_solve': ms, 'value': cand_steps / (ms * 1e-3), 'unit': UNIT, 'solves_timed': 3,
+           'gemm_impl': impl, 'variance_digit_planes': digits,
+           'gemm_share_of_solve': ti['gemm_ms'] / ti['ms_total'], 'kstar_share_of_solve': ti['kstar_ms'] / ti['ms_total'],
+           'gemm_avg_launch_ms': ti['gemm_ms'] / max(1, ti['gemm_n']),
+           'found_solution': bool(int(t['res']['found'][0]))}
+    barrier()
+    mpc._destroy()
+    if world > 1:
+        sedist.destroy_nccl_comm(comm)
+    ssm._destroy()
+    return rec
+
+
+def side_record_c4(lib, _lib, workloads, sedist, dev, dtype, rank, world, barrier):
+    """BASELINE config C4: independent pendulum MPC instances x population 4096, instance-sharded (no communication on
+    the data path), 128 instances per GPU -- 1024 instances on 8 GPUs --, results gathered on every rank at the end."""
+    per_gpu = 128
+    M = per_gpu * world
+    w = workloads.pendulum_workload(num_rollouts=4096)
+    ssm, mpc = workloads.build_solver(w, dtype=dtype, device=dev, record='none', seed=99, num_instances=per_gpu)
+    p0_all = 0.05 * torch.randn((M, w.n_s), generator=torch.Generator().manual_seed(3), dtype=torch.float64)
+    sedist.solve_instances_sharded(mpc, p0_all, seed=10)  # warm-up (workspaces, digit image)
+    barrier()
+    t0 = time.perf_counter()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    ev0.record()
+    plans, found = sedist.solve_instances_sharded(mpc, p0_all, seed=11)
+    ev1.record()
+    barrier()
+    wall = time.perf_counter() - t0
+    ms = _max_over_ranks(ev0.elapsed_time(ev1), world, dev)
+    cand_steps = M * w.num_rollouts * w.time_horizon * w.num_iterations
+    rec = {'workload': f'C4: {M} independent InvertedPendulum MPC instances ({per_gpu}/GPU) x population 4096, exact GP '
+                       f'n_train={w.n_train}, horizon {w.time_horizon}, elites {w.num_elites}, iterations '
+                       f'{w.num_iterations}', 'scaling': 'weak (instance-sharded, no data-path collective)',
+           'n_gpus': world, 'instances': M, 'ms_per_batch_solve': ms, 'ms_per_instance': ms / per_gpu,
+           'value': cand_steps / (ms * 1e-3), 'unit': UNIT, 'wall_s_including_gather': wall,
+           'instances_with_a_feasible_plan': int(found.sum()), 'gathered_plans_shape': list(plans.shape)}
+    mpc._destroy()
+    ssm._destroy()
+    return rec
+
+
 def run_b200(args):
     import ctypes as C
     import torch.distributed as dist
@@ -248,39 +397,27 @@ def run_b200(args):
             torch.cuda.synchronize()
 
     # warm-up (also grows every workspace, so the timed region makes no allocation inside the library)
-    for _ in range(max(3, args.warmup)):
+    warm = max(3, args.warmup)
+    for _ in range(warm):
         mpc.solve(p0, sync=False)
     barrier()
 
-    # ---- device-resident timing: K solves between two events, max over ranks ----
-    # models of <= 128 training points run the fused rollout kernel (one launch per CEM iteration); the per-kernel
-    # event timing below would switch the library back to the four-kernel step, so it stays off for them
-    fused_small = w.n_train <= 128 and args.gemm == 'auto' and os.environ.get('SE_ROLLOUT_FUSED', '1') != '0'
-    if not fused_small:
-        _lib.check(lib.se_gp_timing_enable(ssm.handle, 1))
-    lib.se_launch_count_reset()
-    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    # ---- device-resident timing of the PRODUCTION path: K solves between two events, max over ranks ----
     with ClockSampler(local_rank) as clocks:
-        barrier()
-        ev0.record()
-        for _ in range(args.steps):
-            res = mpc.solve(p0, sync=False)
-        ev1.record()
-        barrier()
-    ms_total = ev0.elapsed_time(ev1)
-    launches = int(lib.se_launch_count())
-    gemm_ms, kstar_ms = C.c_double(0), C.c_double(0)
-    gemm_n, kstar_n = C.c_int64(0), C.c_int64(0)
-    _lib.check(lib.se_gp_timing_read(ssm.handle, C.byref(gemm_ms), C.byref(gemm_n), C.byref(kstar_ms),
-                                     C.byref(kstar_n), _lib.stream_ptr(dev)))
-    _lib.check(lib.se_gp_timing_enable(ssm.handle, 0))
-    if world > 1:
-        t = torch.tensor([ms_total], device=dev, dtype=torch.float64)
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        ms_total = float(t.item())
+        plain = _timed_solves(lib, _lib, ssm, mpc, p0, args.steps, barrier, dev, False)
+    ms_total = _max_over_ranks(plain['ms_total'], world, dev)
     ms_per_step = ms_total / args.steps
     value = cand_steps / (ms_per_step * 1e-3)
+    launches = plain['launches']
+    res = plain['res']
     flags = res['flags'].cpu().tolist()
+
+    # ---- second pass, instrumented: per-kernel split (models of <= 128 training points run one fused rollout kernel
+    # per CEM iteration, which has no separate variance GEMM to time) ----
+    fused_small = w.n_train <= 128 and args.gemm == 'auto' and os.environ.get('SE_ROLLOUT_FUSED', '1') != '0'
+    inst = None
+    if not fused_small:
+        inst = _timed_solves(lib, _lib, ssm, mpc, p0, args.steps, barrier, dev, True)
 
     # ---- end to end through the public API: host state in, host action out, every step ----
     class Env:
@@ -303,11 +440,7 @@ def run_b200(args):
     for _ in range(args.steps):
         action, result = solver.get_action(state_host)
     barrier()
-    e2e_sec = (time.perf_counter() - t0) / args.steps
-    if world > 1:
-        t = torch.tensor([e2e_sec], device=dev, dtype=torch.float64)
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        e2e_sec = float(t.item())
+    e2e_sec = _max_over_ranks((time.perf_counter() - t0) / args.steps, world, dev)
     esz = 8 if args.dtype == 'f64' else 4
     e2e = {'value': cand_steps / e2e_sec, 'unit': UNIT, 'ms_per_solve': e2e_sec * 1e3,
            'h2d_bytes_per_step': w.n_s * esz, 'd2h_bytes_per_step': w.time_horizon * w.n_u * esz + 8 + 16,
@@ -318,7 +451,6 @@ def run_b200(args):
     impl_name, digits = ssm.gemm_info()
     rows_local = w.num_rollouts // world
     fp64_flop_per_launch = w.n_s * float(rows_local) * float(w.n_train) ** 2  # n^2/2 FMA per (candidate, output)
-    gemm_avg_ms = gemm_ms.value / max(1, gemm_n.value)
 
     def pipe_peak(kinds):
         best, f = 0.0, C.c_double(0)
@@ -328,44 +460,65 @@ def run_b200(args):
         return best / 1e12
 
     fp64_peak = pipe_peak([1, 2]) if (rank == 0 and args.dtype == 'f64') else None
-    if impl_name == 'tcgen05-i8':
-        # every float64 FMA of the contraction is evaluated as S (S + 1) / 2 exact int8 digit-plane MACs
-        pairs = digits * (digits + 1) // 2
-        work_per_launch = pairs * fp64_flop_per_launch  # int8 OP (2 x MAC)
-        peak_burst = pipe_peak([3]) if rank == 0 else None
-        peak = pipe_peak([4]) if rank == 0 else None  # the GEMM runs inside a long step: sustained figure
-        pipe = f'int8 tensor (tcgen05.mma kind::i8, {digits} radix-256 digit planes, {pairs} MMAs per K step)'
-        unit = 'TOP/s'
-        peak_src_txt = ('int8 tcgen05 peak measured in this run with se_measure_peak(4): back-to-back 128x256x32 MMAs, '
-                        f'operands resident, sustained for 1.5 s under the power cap (burst: {peak_burst} TOP/s); '
-                        f'for scale: 2 x MEASURED_PEAKS.json ({peak_src}) bf16 burst = '
-                        f'{2 * peaks.get("bf16_tflops", 0):.0f}, sustained = {2 * peaks.get("bf16_tflops_sustained", 0):.0f}')
+    roofline = None
+    if inst is not None:
+        gemm_avg_ms = inst['gemm_ms'] / max(1, inst['gemm_n'])
+        extra = {}
+        if impl_name == 'tcgen05-i8':
+            # every float64 FMA of the contraction is evaluated as S (S + 1) / 2 exact int8 digit-plane MACs
+            pairs = digits * (digits + 1) // 2
+            work_per_launch = pairs * fp64_flop_per_launch  # int8 OP (2 x MAC)
+            peak_burst = pipe_peak([3]) if rank == 0 else None
+            peak = pipe_peak([4]) if rank == 0 else None  # the GEMM runs inside a long step: sustained figure
+            pipe = f'int8 tensor (tcgen05.mma kind::i8, {digits} radix-256 digit planes, {pairs} MMAs per K step)'
+            unit = 'TOP/s'
+            peak_src_txt = ('int8 tcgen05 peak measured in this run with se_measure_peak(4): back-to-back 128x256x32 MMAs, '
+                            'operands resident, sustained for 1.5 s under the power cap; the other denominators are in '
+                            '`frac_against`')
+            achieved = work_per_launch / (gemm_avg_ms * 1e-3) / 1e12 if gemm_avg_ms > 0 else None
+            if achieved and rank == 0:
+                extra['frac_against'] = {
+                    'int8_sustained_measured_in_run': achieved / peak if peak else None,
+                    'int8_burst_measured_in_run': achieved / peak_burst if peak_burst else None,
+                    f'2x_bf16_sustained_MEASURED_PEAKS_{peak_src}': achieved / (2 * peaks['bf16_tflops_sustained'])
+                    if peaks.get('bf16_tflops_sustained') else None,
+                    f'2x_bf16_burst_MEASURED_PEAKS_{peak_src}': achieved / (2 * peaks['bf16_tflops'])
+                    if peaks.get('bf16_tflops') else None,
+                    'int8_nominal_4500': achieved / 4500.0}
+                extra['peaks_top_s'] = {'int8_sustained_in_run': peak, 'int8_burst_in_run': peak_burst,
+                                        '2x_bf16_sustained': 2 * peaks.get('bf16_tflops_sustained', 0),
+                                        '2x_bf16_burst': 2 * peaks.get('bf16_tflops', 0), 'int8_nominal': 4500.0}
+        else:
+            work_per_launch = fp64_flop_per_launch
+            peak = (fp64_peak if args.dtype == 'f64' else pipe_peak([0])) if rank == 0 else None
+            pipe = 'FP64 (DMMA / DFMA)' if args.dtype == 'f64' else 'FP32 FFMA'
+            unit = 'TFLOP/s'
+            peak_src_txt = ('measured in this run with se_measure_peak (register-resident FMA / DMMA loop on every SM); '
+                            f'MEASURED_PEAKS.json ({peak_src}) holds only HBM and bf16 numbers')
+            achieved = work_per_launch / (gemm_avg_ms * 1e-3) / 1e12 if gemm_avg_ms > 0 else None
+        fp64_equiv = fp64_flop_per_launch / (gemm_avg_ms * 1e-3) / 1e12 if gemm_avg_ms > 0 else None
+        op_bytes = digits if impl_name == 'tcgen05-i8' else esz
+        traffic, stamp = (profiled_traffic(_gemm_kernel_name(digits), f'{args.config}/N{rows_local}')
+                          if impl_name == 'tcgen05-i8' else (None, None))
+        roofline = {
+            'bound': 'tensor', 'kernel': 'gp_trisumsq (variance GEMM: || L^-1 k* ||^2)',
+            'kernel_name': _gemm_kernel_name(digits) if impl_name == 'tcgen05-i8' else impl_name, 'impl': impl_name,
+            'pipe': pipe, 'achieved': achieved, 'peak': peak, 'unit': unit,
+            'frac': (achieved / peak) if (achieved and peak) else None, 'peak_source': peak_src_txt,
+            'work_per_launch': work_per_launch, 'avg_launch_ms': gemm_avg_ms, 'launches': inst['gemm_n'],
+            'timed_in': 'second, instrumented pass (events around every launch; graphs / step fusion off): '
+                        f'{inst["ms_total"] / args.steps:.3f} ms per solve vs {plain["ms_total"] / args.steps:.3f} ms '
+                        'on the production path that `value` is taken from',
+            'fp64_equivalent_tflops': fp64_equiv, 'fp64_pipe_peak_tflops': fp64_peak,
+            'share_of_step': inst['gemm_ms'] / inst['ms_total'] if inst['ms_total'] > 0 else None,
+            'kstar_share_of_step': inst['kstar_ms'] / inst['ms_total'] if inst['ms_total'] > 0 else None,
+            'kstar_avg_launch_ms': inst['kstar_ms'] / max(1, inst['kstar_n']),
+            'traffic': traffic, 'traffic_source': stamp,
+            'hbm': {'algorithmic_bytes_per_launch': (w.n_s * rows_local * w.n_train + w.n_s * w.n_train ** 2 / 2) * op_bytes,
+                    'peak_gbs': peaks.get('hbm_gbs')},
+        }
+        roofline.update(extra)
     else:
-        work_per_launch = fp64_flop_per_launch
-        peak = (fp64_peak if args.dtype == 'f64' else pipe_peak([0])) if rank == 0 else None
-        pipe = 'FP64 (DMMA / DFMA)' if args.dtype == 'f64' else 'FP32 FFMA'
-        unit = 'TFLOP/s'
-        peak_src_txt = ('measured in this run with se_measure_peak (register-resident FMA / DMMA loop on every SM); '
-                        f'MEASURED_PEAKS.json ({peak_src}) holds only HBM and bf16 numbers')
-    achieved = work_per_launch / (gemm_avg_ms * 1e-3) / 1e12 if gemm_avg_ms > 0 else None
-    fp64_equiv = fp64_flop_per_launch / (gemm_avg_ms * 1e-3) / 1e12 if gemm_avg_ms > 0 else None
-    op_bytes = digits if impl_name == 'tcgen05-i8' else esz
-    roofline = {
-        'bound': 'tensor', 'kernel': 'gp_trisumsq (variance GEMM: || L^-1 k* ||^2)', 'impl': impl_name, 'pipe': pipe,
-        'achieved': achieved, 'peak': peak, 'unit': unit,
-        'frac': (achieved / peak) if (achieved and peak) else None, 'peak_source': peak_src_txt,
-        'work_per_launch': work_per_launch, 'avg_launch_ms': gemm_avg_ms, 'launches': int(gemm_n.value),
-        'fp64_equivalent_tflops': fp64_equiv, 'fp64_pipe_peak_tflops': fp64_peak,
-        'share_of_step': gemm_ms.value / ms_total if ms_total > 0 else None,
-        'kstar_share_of_step': kstar_ms.value / ms_total if ms_total > 0 else None,
-        'traffic': profiled_traffic('gp_trisumsq_ozaki') if (impl_name == 'tcgen05-i8' and args.config == 'C2' and
-                                                             world == 1) else None,
-        'traffic_source': 'profiles/r01_ncu_full_tc_c2.csv (ncu --set full, dram__bytes_read.sum + dram__bytes_write.sum)',
-        'hbm': {'algorithmic_bytes_per_launch': (w.n_s * rows_local * w.n_train + w.n_s * w.n_train ** 2 / 2) * op_bytes,
-                'peak_gbs': peaks.get('hbm_gbs')},
-    }
-
-    if fused_small:
         # no separate variance GEMM: the whole rollout is one latency-bound kernel; quote the solve's FP64 work rate
         f_step = w.n_s * (w.n_train ** 2 + w.n_train * (5 * (w.n_s + w.n_u) + 8))
         ach = (cand_steps / world) * f_step / (ms_per_step * 1e-3) / 1e12
@@ -391,12 +544,12 @@ def run_b200(args):
         variance_check = {'against': 'float64 DMMA kernel', 'inputs': 2048, 'max_rel_err': float(rel.max()),
                           'median_rel_err': float(rel.median())}
 
-    accuracy_note = {}
+    accuracy = None
     if impl_name == 'tcgen05-i8':
-        accuracy_note = {'variance_digit_planes': digits,
-                         'accuracy_class': 'float64 (variance to 1e-8 relative)' if digits >= 6 else
-                         'reduced: %d digit planes (float32-tolerance dial of se_gp_set_tc_digits; achieved error in '
-                                           'variance_check)' % digits}
+        accuracy = {'variance_digit_planes': digits,
+                    'accuracy_class': 'float64 (variance to 1e-8 relative)' if digits >= 6 else
+                    'reduced: %d digit planes (float32-tolerance dial of se_gp_set_tc_digits; achieved error in '
+                    'variance_check)' % digits}
     cpu_baseline = None
     if rank == 0 and not args.no_cpu_baseline:
         w1 = make_workload(args.config, 1)
@@ -409,20 +562,42 @@ def run_b200(args):
         v2, sec2, _ = cpu_reference_run(w1, args.cpu_sample, 2, 1, loops=False)
         cpu_baseline['delooped'] = {'value': v2, 'unit': UNIT, 'cores': threads, 'kind': 'port',
                                     'sample': f'same sample, eig / trace / constraint loops batched ({sec2:.2f} s)'}
+
+    # the headline solver is done: release it before the side records build their own models
+    found_solution, last_result = bool(int(res['found'][0])), result.name
+    if world > 1:
+        barrier()
+    mpc._destroy()
+    if world > 1:
+        sedist.destroy_nccl_comm(comm)
+    del solver
+
+    side = {}
+    if not args.no_side_records and args.config == 'C2' and args.dtype == 'f64' and args.gemm == 'auto':
+        try:
+            if world == 1:
+                side['c1'] = side_record_c1(lib, _lib, workloads, dev, dtype, barrier, not args.no_cpu_baseline)
+            else:
+                side['strong_scaling'] = side_record_strong_scaling(lib, _lib, workloads, sedist, dev, dtype, rank, world,
+                                                                    barrier)
+                side['c4'] = side_record_c4(lib, _lib, workloads, sedist, dev, dtype, rank, world, barrier)
+        except Exception as exc:  # a side record must never cost the headline line
+            side['side_record_error'] = f'{type(exc).__name__}: {exc}'
+
     if rank == 0:
         line = {
             'metric': METRIC, 'value': value, 'unit': UNIT, 'n_gpus': world, 'steps': args.steps,
-            'warmup': max(3, args.warmup), 'ms_per_step': ms_per_step, 'mpc_solve_ms': ms_per_step,
+            'warmup': warm, 'ms_per_step': ms_per_step, 'mpc_solve_ms': ms_per_step,
             'higher_is_better': True, 'scaling': 'weak', 'vs_baseline': None, 'dtype': args.dtype, 'data': 'synthetic',
-            'config': dict(workload_desc(w, world, args.dtype), **accuracy_note), 'e2e': e2e, 'gpu_launches': launches, 'roofline': roofline,
-            'variance_check': variance_check, 'cpu_baseline': cpu_baseline, 'clocks': clocks.summary(), 'numeric_flags': flags,
-            'found_solution': bool(int(res['found'][0])), 'last_result': result.name,
+            'config': workload_desc(w, world, args.dtype), 'e2e': e2e, 'gpu_launches': launches, 'roofline': roofline,
+            'accuracy': accuracy, 'variance_check': variance_check, 'cpu_baseline': cpu_baseline,
+            'clocks': clocks.summary(), 'numeric_flags': flags, 'found_solution': found_solution,
+            'last_result': last_result,
         }
+        line.update(side)
         print(json.dumps(line), flush=True)
     if world > 1:
         barrier()
-        mpc._destroy()
-        sedist.destroy_nccl_comm(comm)
         dist.destroy_process_group()
 
 

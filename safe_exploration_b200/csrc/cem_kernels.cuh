@@ -4,6 +4,8 @@
 // Restates constrained-cem-mpc/constrained_cem_mpc/constrained_cem_mpc.py:158-170 (sampling), :222-257 (elite
 // selection and refit) and :259-280 (get_actions).  No host round trips: every decision is taken by these kernels.
 #pragma once
+#include <cooperative_groups.h>
+
 #include "common.cuh"
 
 namespace se {
@@ -155,6 +157,59 @@ __device__ __forceinline__ int block_sum_int(int v, int* s_warp) {
   return t;
 }
 
+// Tail shared by the selection kernels: bitonic sort of the P (power of two, padded with ~0 keys) selected (key, index)
+// pairs by ascending (cost, global index), elite ids out, then the refit -- mean and Bessel-corrected std over the
+// elites (constrained_cem_mpc.py:234-235), two passes in fp64, one warp per element of the [T, n_u] action sequence,
+// fixed summation order.  Called by all kSelThreads threads of ONE CTA.
+template <typename T>
+__device__ __forceinline__ void sort_and_refit(const SelectArgs<T>& a, int inst, uint64_t* s_key, int* s_idx, int P) {
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int E = a.num_elites;
+  __syncthreads();
+  for (int size = 2; size <= P; size <<= 1) {
+    for (int stride = size >> 1; stride > 0; stride >>= 1) {
+      for (int t = tid; t < (P >> 1); t += kSelThreads) {
+        const int lo = 2 * t - (t & (stride - 1));
+        const int hi = lo + stride;
+        const bool ascending = (lo & size) == 0;
+        const uint64_t kl = s_key[lo], kh = s_key[hi];
+        const int il = s_idx[lo], ih = s_idx[hi];
+        const bool lo_gt_hi = kl > kh || (kl == kh && il > ih);
+        if (lo_gt_hi == ascending) {
+          s_key[lo] = kh, s_key[hi] = kl;
+          s_idx[lo] = ih, s_idx[hi] = il;
+        }
+      }
+      __syncthreads();
+    }
+  }
+  if (a.elite_ids)
+    for (int i = tid; i < E; i += kSelThreads) a.elite_ids[(int64_t)inst * E + i] = s_idx[i];
+
+  const int tnu = a.src.tnu;
+  for (int e = warp; e < tnu; e += kSelThreads / 32) {
+    double s = 0.0;
+    for (int k = lane; k < E; k += 32) s += (double)candidate_action<T>(a.src, inst, s_idx[k], e);
+#pragma unroll
+    for (int sh = 16; sh > 0; sh >>= 1) s += __shfl_xor_sync(0xffffffffu, s, sh);
+    const double mean = s / (double)E;
+    double v = 0.0;
+    for (int k = lane; k < E; k += 32) {
+      const double dlt = (double)candidate_action<T>(a.src, inst, s_idx[k], e) - mean;
+      v += dlt * dlt;
+    }
+#pragma unroll
+    for (int sh = 16; sh > 0; sh >>= 1) v += __shfl_xor_sync(0xffffffffu, v, sh);
+    const double sd = sqrt(v / (double)(E - 1));  // E == 1 -> NaN, like torch.std (quirk Q5)
+    if (lane == 0) {
+      a.mean_next[(int64_t)inst * tnu + e] = mean;
+      a.std_next[(int64_t)inst * tnu + e] = sd;
+      if (a.mean_hist) a.mean_hist[(int64_t)inst * tnu + e] = (T)mean;
+      if (a.std_hist) a.std_hist[(int64_t)inst * tnu + e] = (T)sd;
+    }
+  }
+}
+
 // One CTA per MPC instance.  Elite order = ascending (cost, global index): the reference's torch.sort is unstable and
 // ties are the norm (constraint costs are small integers), so the index tie-break is fixed here and in the oracle.
 template <typename T>
@@ -298,52 +353,177 @@ cem_select_refit_kernel(SelectArgs<T> a, int cache_n) {
     s_idx[i] = 0x7FFFFFFF;
   }
   }  // n > kSortAllMax
-  // bitonic sort by (key, index): ascending (cost, global index)
-  __syncthreads();
-  for (int size = 2; size <= P; size <<= 1) {
-    for (int stride = size >> 1; stride > 0; stride >>= 1) {
-      for (int t = tid; t < (P >> 1); t += kSelThreads) {
-        const int lo = 2 * t - (t & (stride - 1));
-        const int hi = lo + stride;
-        const bool ascending = (lo & size) == 0;
-        const uint64_t kl = s_key[lo], kh = s_key[hi];
-        const int il = s_idx[lo], ih = s_idx[hi];
-        const bool lo_gt_hi = kl > kh || (kl == kh && il > ih);
-        if (lo_gt_hi == ascending) {
-          s_key[lo] = kh, s_key[hi] = kl;
-          s_idx[lo] = ih, s_idx[hi] = il;
-        }
-      }
-      __syncthreads();
-    }
-  }
-  if (a.elite_ids)
-    for (int i = tid; i < E; i += kSelThreads) a.elite_ids[(int64_t)inst * E + i] = s_idx[i];
+  sort_and_refit<T>(a, inst, s_key, s_idx, P);
+}
 
-  // refit: mean and Bessel-corrected std over the elites (constrained_cem_mpc.py:234-235), two passes in fp64,
-  // one warp per element of the [T, n_u] action sequence, fixed summation order
-  const int tnu = a.src.tnu;
-  for (int e = warp; e < tnu; e += kSelThreads / 32) {
-    double s = 0.0;
-    for (int k = lane; k < E; k += 32) s += (double)candidate_action<T>(a.src, inst, s_idx[k], e);
-#pragma unroll
-    for (int sh = 16; sh > 0; sh >>= 1) s += __shfl_xor_sync(0xffffffffu, s, sh);
-    const double mean = s / (double)E;
-    double v = 0.0;
-    for (int k = lane; k < E; k += 32) {
-      const double dlt = (double)candidate_action<T>(a.src, inst, s_idx[k], e) - mean;
-      v += dlt * dlt;
+// Populations above kSortAllMax: the same selection spread over a thread-block CLUSTER per instance (8 CTAs, one GPC).
+// CTA r of the cluster owns the contiguous index range [r chunk, (r + 1) chunk) of the global population and keeps its
+// keys in its own shared memory; the 8 radix passes build one 256-bin histogram per CTA and every CTA adds the eight of
+// them through distributed shared memory (two cluster barriers per pass), so each takes the same decision; the ordered
+// compaction writes the selected (key, index) pairs straight into the leader's arrays at offsets given by the
+// per-CTA counts (index order = rank order), and the leader sorts the E elites and refits.  The cost of the selection no
+// longer grows with the world size: 131072 keys are 16 per thread and pass (measured: see DESIGN.md section 6).
+constexpr int kSelCluster = 8;
+constexpr int kSelChunkCache = 16384;  // keys a CTA can keep in shared memory (128 KB)
+
+template <typename T>
+__global__ void __launch_bounds__(kSelThreads)
+cem_select_cluster_kernel(SelectArgs<T> a, int chunk, int cached) {
+  namespace cg = cooperative_groups;
+  cg::cluster_group cluster = cg::this_cluster();
+  extern __shared__ __align__(16) unsigned char sel_smem[];
+  uint64_t* s_key = reinterpret_cast<uint64_t*>(sel_smem);          // [kMaxElites]  (used on the leader)
+  int* s_idx = reinterpret_cast<int*>(s_key + kMaxElites);           // [kMaxElites]
+  uint64_t* s_all = reinterpret_cast<uint64_t*>(s_idx + kMaxElites); // [chunk] this CTA's keys when cached
+  __shared__ int s_hist[256];
+  __shared__ int s_ghist[256];
+  __shared__ int s_warp[kSelThreads / 32];
+  __shared__ int s_warp2[kSelThreads / 32];
+  __shared__ int s_cnt[2];  // read by the other CTAs of the cluster: (feasible | less, equal)
+  __shared__ uint64_t s_prefix;
+  __shared__ int s_remaining;
+
+  const int crank = (int)cluster.block_rank(), csize = (int)cluster.num_blocks();
+  const int inst = blockIdx.x / csize, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int n = a.n_global, E = a.num_elites;
+  const int g0 = min(n, crank * chunk), g1 = min(n, g0 + chunk);
+
+  // feasible = constraint_costs == 0   (constrained_cem_mpc.py:247), counted over the whole population
+  int cnt = 0;
+  for (int g = g0 + tid; g < g1; g += kSelThreads) cnt += ((double)a.costs.get(1, inst, g) == 0.0) ? 1 : 0;
+  cnt = block_sum_int(cnt, s_warp);
+  if (tid == 0) s_cnt[0] = cnt;
+  cluster.sync();
+  int num_feasible = 0;
+  for (int r = 0; r < csize; ++r) num_feasible += cluster.map_shared_rank(s_cnt, r)[0];
+  const bool by_objective = num_feasible >= E;  // :248
+  cluster.sync();  // everyone has read s_cnt before it is reused
+
+  auto key_of = [&](int g) -> uint64_t {
+    if (by_objective) {
+      if ((double)a.costs.get(1, inst, g) != 0.0) return ~0ull;  // infeasible: never selected
+      return orderable((double)a.costs.get(0, inst, g));
     }
-#pragma unroll
-    for (int sh = 16; sh > 0; sh >>= 1) v += __shfl_xor_sync(0xffffffffu, v, sh);
-    const double sd = sqrt(v / (double)(E - 1));  // E == 1 -> NaN, like torch.std (quirk Q5)
-    if (lane == 0) {
-      a.mean_next[(int64_t)inst * tnu + e] = mean;
-      a.std_next[(int64_t)inst * tnu + e] = sd;
-      if (a.mean_hist) a.mean_hist[(int64_t)inst * tnu + e] = (T)mean;
-      if (a.std_hist) a.std_hist[(int64_t)inst * tnu + e] = (T)sd;
-    }
+    return orderable((double)a.costs.get(1, inst, g));
+  };
+  if (cached)
+    for (int g = g0 + tid; g < g1; g += kSelThreads) s_all[g - g0] = key_of(g);
+  auto key_at = [&](int g) -> uint64_t { return cached ? s_all[g - g0] : key_of(g); };
+  if (tid == 0) {
+    s_prefix = 0;
+    s_remaining = E;
   }
+  uint64_t mask = 0;
+  for (int pass = 0; pass < 8; ++pass) {
+    const int shift = 56 - 8 * pass;
+    if (tid < 256) s_hist[tid] = 0;
+    __syncthreads();
+    const uint64_t prefix = s_prefix;
+    int run_bin = -1, run_len = 0;
+    for (int g = g0 + tid; g < g1; g += kSelThreads) {
+      const uint64_t k = key_at(g);
+      if ((k & mask) != prefix) continue;
+      const int bin = (int)((k >> shift) & 255);
+      if (bin != run_bin) {
+        if (run_len) atomicAdd(&s_hist[run_bin], run_len);
+        run_bin = bin, run_len = 0;
+      }
+      ++run_len;
+    }
+    if (run_len) atomicAdd(&s_hist[run_bin], run_len);
+    cluster.sync();  // all eight histograms are complete
+    if (tid < 256) {
+      int t = 0;
+      for (int r = 0; r < csize; ++r) t += cluster.map_shared_rank(s_hist, r)[tid];
+      s_ghist[tid] = t;
+    }
+    __syncthreads();
+    if (tid == 0) {  // the same scan on every CTA: identical decisions without a broadcast
+      int rem = s_remaining, b = 0;
+      for (; b < 255; ++b) {
+        if (s_ghist[b] >= rem) break;
+        rem -= s_ghist[b];
+      }
+      s_remaining = rem;
+      s_prefix = prefix | ((uint64_t)b << shift);
+    }
+    mask |= 0xFFull << shift;
+    cluster.sync();  // remote reads of s_hist are done before the next pass clears it (also publishes s_prefix locally)
+  }
+  const uint64_t vstar = s_prefix;
+  const int take_equal = s_remaining;  // how many keys == v* belong to the elite set (lowest indices first)
+  const int num_less = E - take_equal;
+
+  // per-CTA totals -> offsets in index (= rank) order
+  int c_less = 0, c_eq = 0;
+  for (int g = g0 + tid; g < g1; g += kSelThreads) {
+    const uint64_t k = key_at(g);
+    c_less += k < vstar ? 1 : 0;
+    c_eq += k == vstar ? 1 : 0;
+  }
+  c_less = block_sum_int(c_less, s_warp);
+  c_eq = block_sum_int(c_eq, s_warp2);
+  if (tid == 0) s_cnt[0] = c_less, s_cnt[1] = c_eq;
+  cluster.sync();
+  int base_less = 0, base_eq = 0;
+  for (int r = 0; r < crank; ++r) {
+    const int* rc = cluster.map_shared_rank(s_cnt, r);
+    base_less += rc[0];
+    base_eq += rc[1];
+  }
+  uint64_t* l_key = cluster.map_shared_rank(s_key, 0);
+  int* l_idx = cluster.map_shared_rank(s_idx, 0);
+  // ordered compaction of this CTA's range into the leader's arrays
+  for (int gb = g0; gb < g1; gb += kSelThreads) {
+    const int g = gb + tid;
+    uint64_t k = ~0ull;
+    bool f_less = false, f_eq = false;
+    if (g < g1) {
+      k = key_at(g);
+      f_less = k < vstar;
+      f_eq = k == vstar;
+    }
+    const unsigned b_less = __ballot_sync(0xffffffffu, f_less), b_eq = __ballot_sync(0xffffffffu, f_eq);
+    __syncthreads();
+    if (lane == 0) {
+      s_warp[warp] = __popc(b_less);
+      s_warp2[warp] = __popc(b_eq);
+    }
+    __syncthreads();
+    int off_less = base_less, off_eq = base_eq, tot_less = 0, tot_eq = 0;
+    for (int w = 0; w < kSelThreads / 32; ++w) {
+      if (w < warp) {
+        off_less += s_warp[w];
+        off_eq += s_warp2[w];
+      }
+      tot_less += s_warp[w];
+      tot_eq += s_warp2[w];
+    }
+    const unsigned lt = (1u << lane) - 1u;
+    if (f_less) {
+      const int slot = off_less + __popc(b_less & lt);
+      l_key[slot] = k;
+      l_idx[slot] = g;
+    }
+    if (f_eq) {
+      const int slot = off_eq + __popc(b_eq & lt);
+      if (slot < take_equal) {
+        l_key[num_less + slot] = k;
+        l_idx[num_less + slot] = g;
+      }
+    }
+    base_less += tot_less;
+    base_eq += tot_eq;
+  }
+  cluster.sync();  // every CTA's elites have landed in the leader's shared memory
+  if (crank != 0) return;
+  int P = 1;
+  while (P < E) P <<= 1;
+  for (int i = E + tid; i < P; i += kSelThreads) {
+    s_key[i] = ~0ull;
+    s_idx[i] = 0x7FFFFFFF;
+  }
+  sort_and_refit<T>(a, inst, s_key, s_idx, P);
 }
 
 // get_actions (constrained_cem_mpc.py:272-280): from the LAST iteration's rollouts return the first feasible one

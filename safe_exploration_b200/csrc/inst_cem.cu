@@ -24,8 +24,38 @@ int launch_cem_noise(uint64_t seed, int iteration, int num_inst, int n_global, i
   return 0;
 }
 
+// 0 = never, 1 (default) = populations above kSortAllMax run the 8-CTA cluster kernel
+static int select_cluster_mode() {
+  static const int mode = getenv("SE_SELECT_CLUSTER") ? atoi(getenv("SE_SELECT_CLUSTER")) : 1;
+  return mode;
+}
+
+template <typename T>
+static int launch_cem_select_cluster(const SelectArgs<T>& a, int num_inst, cudaStream_t stream) {
+  const int chunk = (int)round_up(ceil_div(a.n_global, kSelCluster), 32);
+  const int cached = chunk <= kSelChunkCache ? 1 : 0;
+  const int smem = kMaxElites * 12 + (cached ? chunk * 8 : 0);
+  SE_TRY(set_max_dyn_smem(cem_select_cluster_kernel<T>, smem));
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3((unsigned)(num_inst * kSelCluster), 1, 1);
+  cfg.blockDim = dim3(kSelThreads, 1, 1);
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr;
+  attr.id = cudaLaunchAttributeClusterDimension;
+  attr.val.clusterDim.x = kSelCluster;
+  attr.val.clusterDim.y = 1;
+  attr.val.clusterDim.z = 1;
+  cfg.attrs = &attr;
+  cfg.numAttrs = 1;
+  SE_CUDA(cudaLaunchKernelEx(&cfg, cem_select_cluster_kernel<T>, a, chunk, cached));
+  g_launches.fetch_add(1, std::memory_order_relaxed);
+  return 0;
+}
+
 template <typename T>
 int launch_cem_select_refit(const SelectArgs<T>& a, int num_inst, cudaStream_t stream) {
+  if (a.n_global > kSortAllMax && select_cluster_mode() != 0) return launch_cem_select_cluster<T>(a, num_inst, stream);
   // selected keys + indices, and (populations of 4097 .. 16384) a cache of every key
   const int cache_n = a.n_global > kSortAllMax && a.n_global <= 16384 ? a.n_global : 0;
   const int smem = kMaxElites * 12 + cache_n * 8;

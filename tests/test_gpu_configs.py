@@ -69,7 +69,9 @@ def test_cartpole_cem_solve_matches_oracle_on_the_tensor_core_path(n_train, t_le
     res = mpc.solve(G(w.p0).unsqueeze(0), seed=5)
     assert ssm.gemm_info()[0] == 'tcgen05-i8'
     ref = oracle.cem_solve(oracle_problem(w), T(w.p0), T(philox_noise(5, w)), w.num_elites)
-    assert_solve_equals_oracle(res, ref)
+    # elementwise on [p | vec q] with a floor of 1e-6: the 1e-9-class variance error of the 6-plane GEMM compounds over
+    # the horizon through the squared radius (measured 1.2e-7 at T = 8), so 1e-6 here; decisions stay bit-exact
+    assert_solve_equals_oracle(res, ref, traj_tol=1e-6)
     feasible = [(r.constraint_costs == 0).sum().item() for r in ref['rollouts']]
     if t_len == 8:
         assert feasible[-1] >= elites and feasible[0] < elites  # both selection modes occurred

@@ -238,8 +238,12 @@ def test_safety_distance_matches_reference_golden(golden_algebra):
 # ---- CEM: integer work is bit-exact -----------------------------------------------------------------------------------
 @pytest.mark.parametrize('dtype', [torch.float64, torch.float32])
 @pytest.mark.parametrize('N,E,ties', [(4, 2, False), (96, 12, True), (5000, 64, True), (65536, 1024, True),
-                                      (1000, 1000, True), (777, 1, False)])
+                                      (1000, 1000, True), (777, 1, False), (4097, 4096, True), (131072, 2048, True),
+                                      (200003, 4096, True), (16384, 256, False)])
 def test_select_elites_bit_exact_against_oracle(N, E, ties, dtype):
+    """Populations up to 4096 sort whole in one CTA; larger ones run the 8-CTA cluster kernel (131072 keys = the global
+    population of the 8-GPU weak-scaling bench; 200003 keys do not fit the clusters' shared memory and take its uncached
+    path; 4097 / 4096 leaves one key out)."""
     rng = np.random.default_rng(N + E)
     Tn, n_u = 3, 2
     obj = rng.standard_normal(N)
