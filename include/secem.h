@@ -287,7 +287,9 @@ void se_launch_count_reset(void);
 /* Runs a register-resident FMA loop on every SM and returns the measured FLOP/s (synchronises the device).
  * kind: 0 = FP32 FFMA, 1 = FP64 DFMA, 2 = FP64 DMMA m8n8k4, 3 = int8 tcgen05.mma (OP/s = 2 x MAC/s, operands resident; burst),
  *       4 = the same sustained for ~1.5 s (what the pipe delivers under the 1 kW power cap),
- *       5 / 6 = burst / sustained with the variance GEMM's own instruction shape (128 x 64 x 32, A tile reused) */
+ *       5 / 6 = burst / sustained with the variance GEMM's own instruction shape (128 x 64 x 32, A tile reused),
+ *       7 / 8 / 9 / 10 = burst with two issuing warps (N = 64, N = 256), N = 128 with one and with two issuers:
+ *       micro-benchmarks behind DESIGN.md's account of where the variance GEMM's time goes */
 int se_measure_peak(int kind, double* flops_out);
 /* Device time (ms, CUDA events recorded by the library on the launch stream) spent in the variance GEMM kernel and
  * in the kernel-row kernel since the last reset, and their launch counts; timing must be enabled first
@@ -302,6 +304,11 @@ int se_gp_timing_read(se_gp_t gp, double* gemm_ms, int64_t* gemm_launches, doubl
  * D_l = sum_{t+u=l} A_t B_u^T. */
 int se_debug_tc_probe(const int8_t* dev_a_img, const int8_t* dev_b_img, int nk, int digits, int lbo, int sbo,
                       int32_t* dev_out, void* stream);
+
+/* Test hook (runs on the HOST, no GPU needed): the general small-matrix eigenvalue routine of the remainder bound
+ * (csrc/eig_small.cuh; the device code calls the same function for a non-symmetric shape matrix, utils.py:175-185,
+ * 651-665): host_out[0] = the largest real eigenvalue of the n x n row-major matrix host_m, NaN for a complex pair. */
+int se_debug_eig_max(const double* host_m, int n, double* host_out);
 
 /* Test hook: out[i] = the branch-free double exp() of the model-refresh gradient kernel (csrc/common.cuh exp_nb, polynomial from
  * tools/exp_poly.py), for finite dev_x[i] <= 700.  Lets a test pin its accuracy against a libm exp. */

@@ -57,6 +57,7 @@ SIGNATURES = {
     "se_gp_set_tc_digits": (_i, [_vp, _i]),
     "se_gp_get_gemm_info": (_i, [_vp, C.POINTER(_i), C.POINTER(_i)]),
     "se_debug_tc_probe": (_i, [_vp, _vp, _i, _i, _i, _i, _vp, _vp]),
+    "se_debug_eig_max": (_i, [_dbl_p, _i, _dbl_p]),
     "se_debug_exp": (_i, [_vp, _i64, _vp, _vp]),
     "se_debug_exp_table": (_i, [_vp, _i64, _vp, _vp]),
     "se_gp_predict": (_i, [_vp, _vp, _i64, _vp, _vp, _vp, _vp]),

@@ -367,7 +367,7 @@ class B200ConstrainedCemMpc:
             _lib.check(self._lib.se_cem_solve(self._handle, _lib.ptr(p0), _lib.ptr(noise), C.c_uint64(int(seed)),
                                               C.byref(out), _lib.stream_ptr(dev)))
         if sync:
-            check_flags(self._collective_flags(res['flags']), 'CEM rollouts')
+            check_flags(self._collective_flags(res['flags']), 'CEM rollouts', dump=(self._ssm, p0, None))
         return res
 
     def _collective_flags(self, flags: Tensor) -> Tensor:
@@ -420,7 +420,7 @@ class B200ConstrainedCemMpc:
         torch.cuda.current_stream(dev).synchronize()
         a_bytes = T * n_u * h_p0.element_size()
         tail = h_pack[a_bytes:].view(torch.int32)  # found, best_id, flags[4]
-        check_flags(tail[2:], 'CEM rollouts')
+        check_flags(tail[2:], 'CEM rollouts', dump=(self._ssm, p0_buf, None))
         if int(tail[0]) != 1:
             return None
         return h_pack[:a_bytes].view(dt).view(T, n_u).numpy().copy()

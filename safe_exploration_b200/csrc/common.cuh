@@ -183,6 +183,27 @@ __device__ __forceinline__ double exp_tab(double x, const double* __restrict__ t
   p *= tab[k & 63];
   return __hiloint2double(__double2hiint(p) + ((k >> 6) << 20), __double2loint(p));
 }
+// 2^shift exp(x), same contract: the power of two rides on the exponent add that exp_tab performs anyway, so the kernel-row
+// kernel gets its fixed-point scaled value k 2^(63 - eA) without a multiply (|shift| and the result stay far inside the
+// normal range: x >= -700, shift ~ 60 .. 80).
+__device__ __forceinline__ double exp_tab_scaled(double x, const double* __restrict__ tab, int shift) {
+  const bool tiny = (unsigned)__double2hiint(x) >= 0xC085E000u;  // x <= -700 (or -Inf)
+  const double xc = tiny ? -700.0 : x;
+  const double t = fma(xc, 92.33248261689366, 6755399441055744.0);  // k = rint(64 x / ln 2) in the low word
+  const int k = __double2loint(t);
+  const double kf = t - 6755399441055744.0;
+  double r = fma(kf, -0.010830424696249145, xc);  // ln 2 / 64 = hi + lo
+  r = fma(kf, -3.623510646634843e-19, r);
+  double p = 1.0 / 720.0;
+  p = fma(p, r, 1.0 / 120.0);
+  p = fma(p, r, 1.0 / 24.0);
+  p = fma(p, r, 1.0 / 6.0);
+  p = fma(p, r, 0.5);
+  p = fma(p, r, 1.0);
+  p = fma(p, r, 1.0);
+  p *= tab[k & 63];
+  return __hiloint2double(__double2hiint(p) + (((k >> 6) + shift) << 20), __double2loint(p));
+}
 __device__ __forceinline__ bool finite_f64(double x) { return (__double2hiint(x) & 0x7ff00000) != 0x7ff00000; }
 
 template <typename T>

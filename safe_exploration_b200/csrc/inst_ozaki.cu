@@ -43,6 +43,13 @@ int launch_kstar_slices(const GpDev<double>& gp, const double* p, int64_t p_stri
     const int segs = gp.n_pad / 128;
     const int spc = seg_per_cta > 0 ? seg_per_cta : segs;
     dim3 grid8((unsigned)ceil_div(rows_pad / 8, 2), (unsigned)ceil_div(segs, spc));
+    // One output per warp group (NS x the warps per CTA, 80 registers each): the default for plain launches of models
+    // with two or more outputs -- C3 kernel rows 2.45 -> 1.83 ms, C2 0.221 -> 0.208 ms (SE_KSTAR_OPT=0: all outputs per
+    // thread).  The fused-step launches of small batches keep one thread per cell.
+    static const int opt_env = getenv("SE_KSTAR_OPT") ? atoi(getenv("SE_KSTAR_OPT")) : 1;
+    if (opt_env == 1 && !fuse_io && gp.ns >= 2)
+      return launch_kstar_slices_opt1(gp, p, p_stride, u, u_stride, row0, nrows, rows_pad, exp_a, S, a_img, mean, jac,
+                                      spc, kpart, grid8.x, grid8.y, stream);
 #define SE_CASE8(NS_, NU_)                                                                                          \
   if (gp.ns == NS_ && gp.nu == NU_) {                                                                               \
     if (fuse_io) {                                                                                                  \
@@ -178,7 +185,7 @@ int launch_debug_exp(const double* x, int64_t n, double* out, int table, cudaStr
 
 // measured int8 tensor-pipe peak in OP/s (2 x MAC).  sustained = 0: best of a few short launches (burst clocks);
 // sustained = 1: launches back to back for ~1.5 s and reports the last third (the 1 kW power cap has settled by then).
-int measure_peak_i8(int sustained, int n_mma, double* ops_out) {
+int measure_peak_i8(int sustained, int n_mma, int issuers, double* ops_out) {
   int dev = 0, sms = 0;
   SE_CUDA(cudaGetDevice(&dev));
   SE_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
@@ -193,7 +200,7 @@ int measure_peak_i8(int sustained, int n_mma, double* ops_out) {
     double best_ms = 1e30;
     for (int rep = 0; rep < 4; ++rep) {
       SE_CUDA(cudaEventRecord(e0, 0));
-      SE_LAUNCH(oz::oz_peak_kernel, sms, 128, smem, 0, iters, n_mma, nullptr);
+      SE_LAUNCH(oz::oz_peak_kernel, sms, 128, smem, 0, iters, n_mma, issuers, nullptr);
       SE_CUDA(cudaEventRecord(e1, 0));
       SE_CUDA(cudaEventSynchronize(e1));
       float ms = 0.f;
@@ -205,7 +212,7 @@ int measure_peak_i8(int sustained, int n_mma, double* ops_out) {
     const int reps = 450;  // ~3 ms each
     for (int rep = 0; rep < reps; ++rep) {
       if (rep == reps * 2 / 3) SE_CUDA(cudaEventRecord(e0, 0));
-      SE_LAUNCH(oz::oz_peak_kernel, sms, 128, smem, 0, iters, n_mma, nullptr);
+      SE_LAUNCH(oz::oz_peak_kernel, sms, 128, smem, 0, iters, n_mma, issuers, nullptr);
     }
     SE_CUDA(cudaEventRecord(e1, 0));
     SE_CUDA(cudaEventSynchronize(e1));

@@ -67,7 +67,7 @@ int launch_cem_init_dist(double* mean, double* stdv, int count, cudaStream_t str
 int launch_cem_set_seed(uint64_t* dst, uint64_t seed, cudaStream_t stream);
 
 int measure_peak(int kind, double* flops_out);
-int measure_peak_i8(int sustained, int n_mma, double* ops_out);
+int measure_peak_i8(int sustained, int n_mma, int issuers, double* ops_out);
 
 // tcgen05 (kind::i8) digit-sliced variance GEMM (ozaki_kernels.cuh)
 int launch_oz_pack_model(const double* w, int n_pad, int ns, const double* host_outputscale, int S, int* exp_a,
@@ -76,6 +76,10 @@ int launch_kstar_slices(const GpDev<double>& gp, const double* p, int64_t p_stri
                         int64_t row0, int nrows, int rows_pad, const int* exp_a, int S, int8_t* a_img, double* mean,
                         double* jac, int seg_per_cta, double* kpart, cudaStream_t stream,
                         const ProbDev<double>* fuse_pr = nullptr, const StepIO<double>* fuse_io = nullptr);
+int launch_kstar_slices_opt1(const GpDev<double>& gp, const double* p, int64_t p_stride, const double* u,
+                             int64_t u_stride, int64_t row0, int nrows, int rows_pad, const int* exp_a, int S,
+                             int8_t* a_img, double* mean, double* jac, int spc, double* kpart, unsigned grid_x,
+                             unsigned grid_y, cudaStream_t stream);
 int launch_trisumsq_ozaki(const int8_t* a_img, const int8_t* b_img, const double* scale_b, int n, int n_pad,
                           int rows_pad, int ns, int S, double* partial, int sm_count, int* nb_out, cudaStream_t stream);
 int launch_oz_probe(const int8_t* a_img, const int8_t* b_img, int nk, int S, int lbo, int sbo, int32_t* out,

@@ -238,7 +238,7 @@ __device__ __forceinline__ void digits4(const long long (&q)[4], uint32_t (&word
 // model packing: per-row exponents of L^-1, scale factors of the epilogue, digit image of L^-1
 // ---------------------------------------------------------------------------------------------------------------------
 // scale_b[o][i] = 2^(eA_o + eB_oi - 12 - 21); exp_b[o][i] = eB_oi.  One warp per row.
-__global__ void oz_row_scale_kernel(const double* __restrict__ w, int n_pad, int ns, const int* __restrict__ exp_a,
+static __global__ void oz_row_scale_kernel(const double* __restrict__ w, int n_pad, int ns, const int* __restrict__ exp_a,
                                     int* __restrict__ exp_b, double* __restrict__ scale_b) {
   const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
   if (warp >= ns * n_pad) return;
@@ -257,7 +257,7 @@ __global__ void oz_row_scale_kernel(const double* __restrict__ w, int n_pad, int
 
 // Digits are always taken from the 48-bit fixed-point value (7 digits); a model / workspace with S < 7 planes keeps the
 // S most significant ones (the dropped balanced digits are at most half a unit of the last kept digit).
-__global__ void oz_pack_b_kernel(const double* __restrict__ w, int n_pad, const int* __restrict__ exp_b, int S,
+static __global__ void oz_pack_b_kernel(const double* __restrict__ w, int n_pad, const int* __restrict__ exp_b, int S,
                                  int8_t* __restrict__ b_img) {
   // one thread per 4 consecutive j of one row
   const int j0 = (blockIdx.x * blockDim.x + threadIdx.x) * 4;
@@ -427,16 +427,26 @@ struct FuseArgs<true> {
   StepIO<double> io;
 };
 
-template <int NS, int D, bool JAC, bool FUSE = false>
+// OPT = outputs per thread.  OPT == NS: a thread carries all n_s outputs of its (row, points) cell (the (z - x)^2 terms
+// are shared between the outputs).  OPT == 1: the CTA has NS times the warps and each warp group works on one output --
+// the differences are recomputed per output, but a thread holds 1 / NS of the accumulators, so more warps fit an SM;
+// the kernel waits on dependent FP64 issue (ncu: `wait` 2.5 per issue, 3.3 warps per scheduler at 128 registers), not
+// on the pipe.  Same arithmetic per output either way: the results are bit-identical.
+template <int NS, int D, bool JAC, bool FUSE = false, int OPT = NS>
 // CTAs per SM: 8 (128 registers) is the measured optimum for n_s <= 3 (C2: 0.216 ms; 6 -> 0.279, 10 -> 0.226, 12 -> 0.240);
 // with 4 and more outputs the accumulators no longer fit and 6 (168 registers) wins (C3: 3.10 vs 3.82 ms)
-__global__ void __launch_bounds__(64, NS <= 3 ? 8 : 6)
+// (OPT == 1: 768 threads per SM -> 80 registers for inputs of up to 5 dimensions, 512 -> 128 registers beyond)
+__global__ void __launch_bounds__(64 * (NS / OPT), OPT == NS ? (NS <= 3 ? 8 : 6)
+                                                               : ((D <= 5 ? 768 : 512) / (64 * NS) > 0 ? (D <= 5 ? 768 : 512) / (64 * NS) : 1))
 gp_kstar_slices8_kernel(GpDev<double> gp, const double* __restrict__ p, int64_t p_stride, const double* __restrict__ u,
                         int64_t u_stride, int64_t row0, int nrows, int rows_pad, const int* __restrict__ exp_a, int S,
                         int8_t* __restrict__ a_img, double* __restrict__ mean, double* __restrict__ jac,
                         int seg_per_cta, double* __restrict__ kpart, FuseArgs<FUSE> fa) {
+  static_assert(OPT == NS || OPT == 1, "a thread carries all outputs or one");
+  constexpr int NT = 64 * (NS / OPT);  // threads per CTA
   const int lane = threadIdx.x & 31;
-  const int64_t warp = blockIdx.x * (int64_t)(blockDim.x >> 5) + (threadIdx.x >> 5);
+  const int o_base = OPT == NS ? 0 : (int)(threadIdx.x >> 6);  // this warp group's first output
+  const int64_t warp = blockIdx.x * 2ll + ((threadIdx.x >> 5) & 1);
   const int64_t r0 = warp * 8;  // rows_pad is a multiple of 128 and the grid is rows_pad / 16 CTAs: every warp has rows
   const int r8 = lane & 7, quad = lane >> 3;
   const int64_t row = r0 + r8;
@@ -449,7 +459,8 @@ gp_kstar_slices8_kernel(GpDev<double> gp, const double* __restrict__ p, int64_t 
     double p1[NS];
 #pragma unroll
     for (int dd = 0; dd < NS; ++dd) p1[dd] = 0.0;
-    if (valid) reach_step_body<double, NS, D - NS>(fa.pr, fa.io, row0 + row, quad == 0 && blockIdx.y == 0, p1);
+    if (valid)
+      reach_step_body<double, NS, D - NS>(fa.pr, fa.io, row0 + row, quad == 0 && blockIdx.y == 0 && o_base == 0, p1);
 #pragma unroll
     for (int dd = 0; dd < D; ++dd) z[dd] = dd < NS ? p1[dd] : (valid ? u[(row0 + row) * u_stride + (dd - NS)] : 0.0);
   } else {
@@ -460,13 +471,22 @@ gp_kstar_slices8_kernel(GpDev<double> gp, const double* __restrict__ p, int64_t 
       z[dd] = v;
     }
   }
-  double qscale[NS], log_s[NS], nh_inv_l2[NS][D];
+  // k = s exp(-1/2 sum_d ((z_d - x_d) / l_d)^2) is evaluated in scaled coordinates: with c_d = 1 / (sqrt 2 l_d),
+  // e_d = z_d c_d - x_d c_d (one FMA) and arg = ln s - sum_d e_d^2 (one FMA each).  The fixed-point scale 2^shift of the
+  // digit planes is folded into the exponential (exp_tab_scaled), so the sums below run on k 2^shift and are scaled back
+  // by the exact power of two when a segment is folded -- bit-identical to summing k itself.
+  double log_s[OPT], cs[OPT][D], zs[OPT][D], inv_q[OPT];
+  int shift[OPT];
 #pragma unroll
-  for (int o = 0; o < NS; ++o) {
-    log_s[o] = log(gp.outputscale[o]);
-    qscale[o] = ldexp(1.0, RB * MAX_S - 1 - exp_a[o]);
+  for (int o = 0; o < OPT; ++o) {
+    log_s[o] = log(gp.outputscale[o_base + o]);
+    shift[o] = RB * MAX_S - 1 - exp_a[o_base + o];
+    inv_q[o] = ldexp(1.0, -shift[o]);
 #pragma unroll
-    for (int dd = 0; dd < D; ++dd) nh_inv_l2[o][dd] = -0.5 * gp.inv_l2[o][dd];
+    for (int dd = 0; dd < D; ++dd) {
+      cs[o][dd] = sqrt(0.5 * gp.inv_l2[o_base + o][dd]);
+      zs[o][dd] = z[dd] * cs[o][dd];
+    }
   }
   // exp_nb() wants finite arguments: a non-finite input or hyper-parameter poisons the row's mean (and Jacobian)
   // instead, which is what the NaN check of the ellipsoid step looks at (gp_reachability_pytorch.py:234-243)
@@ -474,27 +494,27 @@ gp_kstar_slices8_kernel(GpDev<double> gp, const double* __restrict__ p, int64_t 
 #pragma unroll
   for (int dd = 0; dd < D; ++dd) poison |= !finite_f64(z[dd]);
 #pragma unroll
-  for (int o = 0; o < NS; ++o) {
+  for (int o = 0; o < OPT; ++o) {
     poison |= !finite_f64(log_s[o]) && log_s[o] > 0.0;
     poison |= log_s[o] != log_s[o];
 #pragma unroll
-    for (int dd = 0; dd < D; ++dd) poison |= !finite_f64(nh_inv_l2[o][dd]);
+    for (int dd = 0; dd < D; ++dd) poison |= !finite_f64(cs[o][dd]);
   }
   // Mean and Jacobian sums are formed per 128-point segment (lane partials folded over the four quads) and the
   // segments are added in order -- by this CTA, or, when the training set is split over blockIdx.y because the batch
   // is too small to fill the machine, by gp_var_kernel from kpart.  Same additions in the same order either way, so
   // the result does not depend on how a batch was chunked or split.
-  double m_acc[NS], j_acc[NS][JAC ? D : 1], m_tot[NS], j_tot[NS][JAC ? D : 1];
+  double m_acc[OPT], j_acc[OPT][JAC ? D : 1], m_tot[OPT], j_tot[OPT][JAC ? D : 1];
 #pragma unroll
-  for (int o = 0; o < NS; ++o) {
+  for (int o = 0; o < OPT; ++o) {
     m_acc[o] = m_tot[o] = 0.0;
 #pragma unroll
     for (int dd = 0; dd < (JAC ? D : 1); ++dd) j_acc[o][dd] = j_tot[o][dd] = 0.0;
   }
   // byte offset of (this lane's row, K index 4 quad) inside a digit-plane block; the K half adds 128
   const int ct = (int)(r0 / TM), rl = (int)(r0 % TM) + r8;
-  int8_t* const img_row = a_img + (int64_t)ct * nkb * (int64_t)(S * A_BLK) + blk_off(rl, 4 * quad);
   const int64_t img_o = (int64_t)rt_count * nkb * (int64_t)(S * A_BLK);
+  int8_t* const img_row = a_img + (int64_t)ct * nkb * (int64_t)(S * A_BLK) + blk_off(rl, 4 * quad) + o_base * img_o;
 
   // Training inputs and alpha go through shared memory: the CTA copies them in chunks of 128 points with cp.async
   // (no registers, double buffered, one chunk ahead), so a step reads its operands with short, fixed latency.  Straight
@@ -505,11 +525,13 @@ gp_kstar_slices8_kernel(GpDev<double> gp, const double* __restrict__ p, int64_t 
   __shared__ double etab[64];  // exp_tab's table; published by the first barrier of the chunk loop
   if (threadIdx.x < 64) etab[threadIdx.x] = kExpTab[threadIdx.x];
   auto fill = [&](int chunk, int buf) {
+    // 64 x 16 bytes = one array row of the chunk; the CTA's threads walk the (array, 16-byte piece) pairs
 #pragma unroll
-    for (int a = 0; a < D + NS; ++a) {
+    for (int i = threadIdx.x; i < (D + NS) * 64; i += NT) {
+      const int a = i >> 6, piece = i & 63;
       const double* src = (a < D ? gp.xt + (int64_t)a * n_pad : gp.alpha + (int64_t)(a - D) * n_pad) + chunk * CH +
-                          2 * threadIdx.x;  // 64 threads x 16 bytes = one array row of the chunk
-      const uint32_t dst = smem_u32(&stage[buf][a][2 * threadIdx.x]);
+                          2 * piece;
+      const uint32_t dst = smem_u32(&stage[buf][a][2 * piece]);
       asm volatile("cp.async.cg.shared.global [%0], [%1], 16;\n" ::"r"(dst), "l"(src) : "memory");
     }
     asm volatile("cp.async.commit_group;\n" ::: "memory");
@@ -531,7 +553,7 @@ gp_kstar_slices8_kernel(GpDev<double> gp, const double* __restrict__ p, int64_t 
 #pragma unroll 1
   for (int jl = 0; jl < CH; jl += 16) {
     const int j16 = ch * CH + jl;
-    double x[D][4], al[NS][4];
+    double x[D][4], al[OPT][4];
 #pragma unroll
     for (int dd = 0; dd < D; ++dd) {
       const double2 t0 = *reinterpret_cast<const double2*>(&stage[buf][dd][jl + 4 * quad]);
@@ -539,29 +561,27 @@ gp_kstar_slices8_kernel(GpDev<double> gp, const double* __restrict__ p, int64_t 
       x[dd][0] = t0.x, x[dd][1] = t0.y, x[dd][2] = t1.x, x[dd][3] = t1.y;
     }
 #pragma unroll
-    for (int o = 0; o < NS; ++o) {
-      const double2 t0 = *reinterpret_cast<const double2*>(&stage[buf][D + o][jl + 4 * quad]);
-      const double2 t1 = *reinterpret_cast<const double2*>(&stage[buf][D + o][jl + 4 * quad + 2]);
+    for (int o = 0; o < OPT; ++o) {
+      const double2 t0 = *reinterpret_cast<const double2*>(&stage[buf][D + o_base + o][jl + 4 * quad]);
+      const double2 t1 = *reinterpret_cast<const double2*>(&stage[buf][D + o_base + o][jl + 4 * quad + 2]);
       al[o][0] = t0.x, al[o][1] = t0.y, al[o][2] = t1.x, al[o][3] = t1.y;
     }
     // zero-padded training points: finite garbage kernel values that meet alpha = 0 and zero columns of L^-1
-    long long q[NS][4];
+    long long q[OPT][4];
 #pragma unroll
     for (int e = 0; e < 4; ++e) {
-      double diff[D], sq[D];
 #pragma unroll
-      for (int dd = 0; dd < D; ++dd) {
-        diff[dd] = z[dd] - x[dd][e];
-        sq[dd] = diff[dd] * diff[dd];
-      }
-#pragma unroll
-      for (int o = 0; o < NS; ++o) {
+      for (int o = 0; o < OPT; ++o) {
+        double diff[D];
         double arg = log_s[o];
 #pragma unroll
-        for (int dd = 0; dd < D; ++dd) arg = fma(sq[dd], nh_inv_l2[o][dd], arg);
-        const double k = exp_tab(arg, etab);
-        q[o][e] = __double2ll_rn(k * qscale[o]);
-        const double wk = al[o][e] * k;
+        for (int dd = 0; dd < D; ++dd) {
+          diff[dd] = fma(-x[dd][e], cs[o][dd], zs[o][dd]);
+          arg = fma(-diff[dd], diff[dd], arg);
+        }
+        const double kq = exp_tab_scaled(arg, etab, shift[o]);  // k 2^shift
+        q[o][e] = __double2ll_rn(kq);
+        const double wk = al[o][e] * kq;
         m_acc[o] += wk;
         if (JAC) {
 #pragma unroll
@@ -571,7 +591,7 @@ gp_kstar_slices8_kernel(GpDev<double> gp, const double* __restrict__ p, int64_t 
     }
     int8_t* const dst0 = img_row + (int64_t)(j16 >> 5) * (S * A_BLK) + ((j16 & 16) ? 128 : 0);
 #pragma unroll
-    for (int o = 0; o < NS; ++o) {
+    for (int o = 0; o < OPT; ++o) {
       uint32_t word[MAX_S];
       digits4(q[o], word);
       int8_t* dst = dst0 + o * img_o;
@@ -583,14 +603,15 @@ gp_kstar_slices8_kernel(GpDev<double> gp, const double* __restrict__ p, int64_t 
     // segment done: fold the quads (lanes r8, r8 + 8, r8 + 16, r8 + 24 hold disjoint training points), then add the
     // segment to the running total or hand it to gp_var_kernel
 #pragma unroll
-    for (int o = 0; o < NS; ++o) {
+    for (int o = 0; o < OPT; ++o) {
       double v = m_acc[o];
       v += __shfl_xor_sync(0xffffffffu, v, 8);
       v += __shfl_xor_sync(0xffffffffu, v, 16);
+      v *= inv_q[o];  // exact: a power of two
       m_acc[o] = 0.0;
       if (poison) v = __longlong_as_double(0x7ff8000000000000ll);
       if (split) {
-        if (quad == 0) kpart[(((int64_t)ch * rows_pad + row) * NS + o) * (1 + D)] = v;
+        if (quad == 0) kpart[(((int64_t)ch * rows_pad + row) * NS + o_base + o) * (1 + D)] = v;
       } else {
         m_tot[o] += v;
       }
@@ -600,10 +621,11 @@ gp_kstar_slices8_kernel(GpDev<double> gp, const double* __restrict__ p, int64_t 
           double g = j_acc[o][dd];
           g += __shfl_xor_sync(0xffffffffu, g, 8);
           g += __shfl_xor_sync(0xffffffffu, g, 16);
+          g = g * inv_q[o] / cs[o][dd];  // back to sum_i alpha_i k_i (z_d - x_id)
           j_acc[o][dd] = 0.0;
           if (poison) g = __longlong_as_double(0x7ff8000000000000ll);
           if (split) {
-            if (quad == 0) kpart[(((int64_t)ch * rows_pad + row) * NS + o) * (1 + D) + 1 + dd] = g;
+            if (quad == 0) kpart[(((int64_t)ch * rows_pad + row) * NS + o_base + o) * (1 + D) + 1 + dd] = g;
           } else {
             j_tot[o][dd] += g;
           }
@@ -615,16 +637,16 @@ gp_kstar_slices8_kernel(GpDev<double> gp, const double* __restrict__ p, int64_t 
   if (split) return;  // gp_var_kernel adds the segments
 
 #pragma unroll
-  for (int o = 0; o < NS; ++o) {
+  for (int o = 0; o < OPT; ++o) {
     double v = m_tot[o];
     if (poison) v = __longlong_as_double(0x7ff8000000000000ll);
-    if (quad == 0 && valid) mean[(row0 + row) * NS + o] = v;
+    if (quad == 0 && valid) mean[(row0 + row) * NS + o_base + o] = v;
     if (JAC) {
 #pragma unroll
       for (int dd = 0; dd < D; ++dd) {
         double g = j_tot[o][dd];  // sum_i alpha_i k_i (z_d - x_id); d mean / d z_d = -that / l_d^2
         if (poison) g = __longlong_as_double(0x7ff8000000000000ll);
-        if (quad == 0 && valid) jac[((row0 + row) * NS + o) * D + dd] = -g * gp.inv_l2[o][dd];
+        if (quad == 0 && valid) jac[((row0 + row) * NS + o_base + o) * D + dd] = -g * gp.inv_l2[o_base + o][dd];
       }
     }
   }
@@ -872,11 +894,11 @@ oz_probe_kernel(const int8_t* __restrict__ a_img, const int8_t* __restrict__ b_i
 // Pipe peak (se_measure_peak kind 3): back-to-back 128 x 256 x 32 s8 MMAs on every SM, operands resident in shared
 // memory, no loads and no epilogue -- the denominator bench.py quotes for the tcgen05 variance GEMM.
 // ---------------------------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(128, 1) oz_peak_kernel(int iters, int n_mma, int32_t* __restrict__ sink) {
+static __global__ void __launch_bounds__(128, 1) oz_peak_kernel(int iters, int n_mma, int issuers, int32_t* __restrict__ sink) {
   extern __shared__ unsigned char smem_raw[];
   const uint32_t raw = smem_u32(smem_raw);
   const uint32_t base = (raw + 1023u) & ~1023u;
-  const uint32_t bar = base + 12 * 1024, tmem_slot = bar + 8;
+  const uint32_t bar = base + 12 * 1024, tmem_slot = bar + 16;
   const int warp = threadIdx.x >> 5;
   // pseudo-random digit bytes: the power drawn by the tensor pipe (and so the sustained clock) depends on the data
   for (int i = threadIdx.x; i < 12 * 1024 / 4; i += blockDim.x) {
@@ -886,6 +908,7 @@ __global__ void __launch_bounds__(128, 1) oz_peak_kernel(int iters, int n_mma, i
   }
   if (threadIdx.x == 0) {
     mbar_init(bar, 1);
+    mbar_init(bar + 8, 1);
     mbar_fence_init();
   }
   if (warp == 0) tmem_alloc(tmem_slot, TMEM_COLS);
@@ -895,32 +918,39 @@ __global__ void __launch_bounds__(128, 1) oz_peak_kernel(int iters, int n_mma, i
   tc_fence_after();
   uint32_t tmem_base;
   asm volatile("ld.shared.u32 %0, [%1];\n" : "=r"(tmem_base) : "r"(tmem_slot));
-  if (warp == 0) {
-    const uint32_t tb = __shfl_sync(0xffffffffu, tmem_base, 0);
+  // issuers = 2 (n_mma = 64 shape only): two warps issue half of the MMAs each, into their own 256 TMEM columns -- does
+  // the time one thread needs between two tcgen05.mma limit the pipe, or the pipe itself?
+  if (warp < issuers) {
+    const uint32_t tb = __shfl_sync(0xffffffffu, tmem_base, 0) + (uint32_t)(warp * 256);
     const uint32_t alo = desc_lo(__shfl_sync(0xffffffffu, base, 0), LBO), dhi = desc_hi(SBO);
     const uint32_t idesc = make_idesc(128, n_mma);
+    const int my_iters = iters / issuers;
     if (elect_one()) {
       const uint64_t ad = pack_desc(alo, dhi), bd = pack_desc(alo + (4096 >> 4), dhi);
       if (n_mma == 256) {
-        for (int i = 0; i < iters; i += 2) {
+        for (int i = 0; i < my_iters; i += 2) {
           mma_i8<0>(tb, ad, bd, idesc, 1u);
-          mma_i8<0>(tb + 256, ad, bd, idesc, 1u);
+          mma_i8<0>(issuers == 1 ? tb + 256 : tb, ad, bd, idesc, 1u);
         }
       } else {  // the variance GEMM's own shape: one A tile kept in the collector across several N = 64 MMAs
         const uint64_t bd1 = pack_desc(alo + (6144 >> 4), dhi), bd2 = pack_desc(alo + (8192 >> 4), dhi);
         const uint64_t bd3 = pack_desc(alo + (10240 >> 4), dhi);
-        for (int i = 0; i < iters; i += 4) {
+        const uint32_t span = issuers == 2 ? 256u : 512u;  // TMEM columns this issuer owns
+        const uint32_t c1 = tb + (uint32_t)n_mma % span, c2 = tb + (uint32_t)(2 * n_mma) % span;
+        const uint32_t c3 = tb + (uint32_t)(3 * n_mma) % span;
+        for (int i = 0; i < my_iters; i += 4) {
           mma_i8<1>(tb, ad, bd, idesc, 1u);
-          mma_i8<2>(tb + n_mma, ad, bd1, idesc, 1u);
-          mma_i8<2>(tb + 2 * n_mma, ad, bd2, idesc, 1u);
-          mma_i8<3>(tb + 3 * n_mma, ad, bd3, idesc, 1u);
+          mma_i8<2>(c1, ad, bd1, idesc, 1u);
+          mma_i8<2>(c2, ad, bd2, idesc, 1u);
+          mma_i8<3>(c3, ad, bd3, idesc, 1u);
         }
       }
-      tc_commit(bar);
+      tc_commit(bar + 8 * warp);
     }
     __syncwarp();
   }
   mbar_wait(bar, 0);
+  if (issuers == 2) mbar_wait(bar + 8, 0);
   tc_fence_after();
   if (sink == reinterpret_cast<int32_t*>(1)) {  // never true: keeps the accumulators observable
     int32_t v[8];

@@ -5,6 +5,7 @@
 // and the constraint / objective epilogue of safempc_cem.py:102-132, 304-312 + constrained_cem_mpc.py:100-110.
 #pragma once
 #include "common.cuh"
+#include "eig_small.cuh"
 
 namespace se {
 
@@ -55,9 +56,11 @@ __device__ __forceinline__ T sym_lambda_max(T (&m)[NS][NS]) {
 }
 
 // r^2 = lambda_max(q B), B = I + k_fb^T k_fb  (utils.py:175-185).  For NS <= 2 the characteristic polynomial of the
-// (possibly non-symmetric) product q B is solved in closed form, like the reference's general `eig`; for NS >= 3 the
-// product is similar to the symmetric C^T q C (B = C C^T), whose spectrum Jacobi resolves to full relative accuracy
-// (q is symmetric on the hot path; the symmetric part is used).
+// (possibly non-symmetric) product q B is solved in closed form, like the reference's general `eig`; for NS >= 3 a
+// symmetric q (every shape matrix the path itself produces: asymmetry at rounding level) makes the product similar to
+// the symmetric C^T q C (B = C C^T), whose spectrum Jacobi resolves to full relative accuracy, and a q that is NOT
+// symmetric (an entry point may be handed one, test_utils.py:35-59) takes the general route of the reference: the
+// largest real eigenvalue of q B by shifted QR (eig_small.cuh), NaN for a complex pair where the reference asserts.
 template <typename T, int NS>
 __device__ __forceinline__ T remainder_r_sqr(const T (&q)[NS][NS], const ProbDev<T>& pr) {
   if (NS == 1) return q[0][0] * pr.bmat[0][0];
@@ -72,6 +75,27 @@ __device__ __forceinline__ T remainder_r_sqr(const T (&q)[NS][NS], const ProbDev
     return half_tr + Num<T>::sqrt_(disc);              // NaN if the pair is complex (reference asserts)
   }
   T tmp[NS][NS], m[NS][NS];
+  T asym = T(0), scale = T(0);
+#pragma unroll
+  for (int i = 0; i < NS; ++i)
+#pragma unroll
+    for (int j = 0; j < NS; ++j) {
+      scale = Num<T>::abs_(q[i][j]) > scale ? Num<T>::abs_(q[i][j]) : scale;
+      if (j > i) asym = Num<T>::abs_(q[i][j] - q[j][i]) > asym ? Num<T>::abs_(q[i][j] - q[j][i]) : asym;
+    }
+  if (asym > (sizeof(T) == 8 ? T(1e-12) : T(1e-5)) * scale) {
+    T mg[NS][NS];  // its own array: this one goes to local memory (the routine is not inlined), `m` below stays in registers
+#pragma unroll
+    for (int i = 0; i < NS; ++i)
+#pragma unroll
+      for (int j = 0; j < NS; ++j) {
+        T s = T(0);
+#pragma unroll
+        for (int k = 0; k < NS; ++k) s += q[i][k] * pr.bmat[k][j];
+        mg[i][j] = s;
+      }
+    return max_real_eig_general<T, NS>(mg, NS);
+  }
 #pragma unroll
   for (int i = 0; i < NS; ++i)
 #pragma unroll

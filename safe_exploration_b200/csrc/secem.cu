@@ -113,8 +113,12 @@ extern "C" int se_version(void) { return 100; }
 extern "C" uint64_t se_launch_count(void) { return g_launches.load(); }
 extern "C" void se_launch_count_reset(void) { g_launches.store(0); }
 extern "C" int se_measure_peak(int kind, double* flops_out) {
-  SE_REQUIRE(kind >= 0 && kind <= 6 && flops_out, "se_measure_peak: bad arguments");
-  if (kind >= 3) return measure_peak_i8(kind == 4 || kind == 6, kind >= 5 ? 64 : 256, flops_out);
+  SE_REQUIRE(kind >= 0 && kind <= 10 && flops_out, "se_measure_peak: bad arguments");
+  if (kind == 7) return measure_peak_i8(0, 64, 2, flops_out);    // N = 64 shape, two issuing warps (burst)
+  if (kind == 8) return measure_peak_i8(0, 256, 2, flops_out);   // N = 256, two issuing warps (burst)
+  if (kind == 9) return measure_peak_i8(0, 128, 1, flops_out);   // N = 128 shape (burst)
+  if (kind == 10) return measure_peak_i8(0, 128, 2, flops_out);  // N = 128 shape, two issuing warps (burst)
+  if (kind >= 3) return measure_peak_i8(kind == 4 || kind == 6, kind >= 5 ? 64 : 256, 1, flops_out);
   return measure_peak(kind, flops_out);
 }
 
@@ -278,6 +282,15 @@ extern "C" int se_debug_tc_probe(const int8_t* dev_a_img, const int8_t* dev_b_im
                                  int32_t* dev_out, void* stream) {
   SE_REQUIRE(dev_a_img && dev_b_img && dev_out && nk >= 1, "se_debug_tc_probe: bad arguments");
   return launch_oz_probe(dev_a_img, dev_b_img, nk, digits, lbo, sbo, dev_out, static_cast<cudaStream_t>(stream));
+}
+
+extern "C" int se_debug_eig_max(const double* host_m, int n, double* host_out) {
+  SE_REQUIRE(host_m && host_out && n >= 1 && n <= SE_MAX_NS, "se_debug_eig_max: bad arguments");
+  double a[SE_MAX_NS][SE_MAX_NS] = {};
+  for (int i = 0; i < n; ++i)
+    for (int j = 0; j < n; ++j) a[i][j] = host_m[i * n + j];
+  *host_out = max_real_eig_general<double, SE_MAX_NS>(a, n);
+  return 0;
 }
 
 extern "C" int se_debug_exp(const double* dev_x, int64_t n, double* dev_out, void* stream) {

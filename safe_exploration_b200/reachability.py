@@ -92,10 +92,28 @@ class ReachabilityNumericsError(ValueError):
     149-153)."""
 
 
-def check_flags(flags: Tensor, where: str) -> None:
-    """Host side of _fix_zeros_nans (gp_reachability_pytorch.py:234-243): one sync per call instead of 2-3 per step."""
+def _save_model(ssm, state: Optional[Tensor], action: Optional[Tensor]) -> None:
+    """gp_reachability_pytorch.py:256-266: before raising on a NaN variance the reference dumps the model and the inputs
+    that produced it to `negative_variance_state.pt` in the working directory.  Same file, same keys where they exist
+    here ('state', 'action', 'x_train', 'y_train'); the GPyTorch state dicts become the materialised hyper-parameters."""
+    try:
+        cpu = lambda t: None if t is None else t.detach().cpu()
+        torch.save({'gp_model': {k: cpu(getattr(ssm, k, None)) for k in ('lengthscale', 'outputscale')},
+                    'gp_likelihood': {'noise': cpu(getattr(ssm, 'noise', None))},
+                    'state': cpu(state), 'action': cpu(action),
+                    'x_train': cpu(getattr(ssm, 'x_train', None)), 'y_train': cpu(getattr(ssm, 'y_train', None))},
+                   'negative_variance_state.pt')
+    except Exception as exc:  # the dump is a debugging aid: never mask the numeric error with an I/O error
+        print(f'WARNING: could not write negative_variance_state.pt: {exc}')
+
+
+def check_flags(flags: Tensor, where: str, dump=None) -> None:
+    """Host side of _fix_zeros_nans (gp_reachability_pytorch.py:234-243): one sync per call instead of 2-3 per step.
+    `dump` = (ssm, state, action): what the reference's _save_model writes before the ValueError."""
     n_nan, n_zero = int(flags[0]), int(flags[1])
     if n_nan > 0:
+        if dump is not None:
+            _save_model(*dump)
         raise ReachabilityNumericsError(f'nan in sigm_0 / rkhs_bounds / b_sigma_eps ({n_nan} entries) in {where}')
     if n_zero > 0:
         print(f'WARNING: found 0 in {where} but carried on ({n_zero} entries set to 1e-5)')
@@ -139,7 +157,7 @@ def _onestep_generic_ssm(p_center, ssm, k_ff, prob: SafeProblem, q_shape):
             _lib.check(lib.se_reach_step(code, C.byref(cs), _lib.ptr(p), _lib.ptr(q), _lib.ptr(u), _lib.ptr(mean),
                                          _lib.ptr(var), _lib.ptr(jac), N, _lib.ptr(p1), _lib.ptr(q1), _lib.ptr(sig),
                                          _lib.ptr(flags), _lib.stream_ptr(dev)))
-        check_flags(flags.cpu(), 'onestep_reachability')
+        check_flags(flags.cpu(), 'onestep_reachability', dump=(ssm, p_center, k_ff))
     return p1, q1, sig
 
 
@@ -178,7 +196,7 @@ def onestep_reachability(p_center: Tensor, ssm: CemSSM, k_ff: Tensor, l_mu: Tens
             _lib.check(gp._lib.se_reach_onestep(gp.handle, C.byref(cs), _lib.ptr(p), _lib.ptr(q), _lib.ptr(u), N,
                                                 _lib.ptr(p1), _lib.ptr(q1), _lib.ptr(sig), _lib.ptr(flags),
                                                 _lib.stream_ptr(dev)))
-        check_flags(flags.cpu(), 'onestep_reachability')
+        check_flags(flags.cpu(), 'onestep_reachability', dump=(ssm, p_center, k_ff))
     return p1, q1, sig
 
 
@@ -224,7 +242,7 @@ def multistep_reachability(p_0: Tensor, ssm: CemSSM, k_fb, k_ff: Tensor, l_mu, l
             _lib.check(gp._lib.se_reach_multistep(gp.handle, C.byref(cs), _lib.ptr(p0), _lib.ptr(q0), _lib.ptr(u), N,
                                                   T, steps_ptr, _lib.ptr(p_all), _lib.ptr(q_all), _lib.ptr(s_all),
                                                   _lib.ptr(pT), _lib.ptr(qT), _lib.ptr(flags), _lib.stream_ptr(dev)))
-        check_flags(flags.cpu(), 'multistep_reachability')
+        check_flags(flags.cpu(), 'multistep_reachability', dump=(ssm, p_0, k_ff))
     return pT, qT, p_all, q_all, s_all
 
 

@@ -232,3 +232,39 @@ def test_environment_objective_selectors_match_oracle(kind, theta):
     assert_solve_equals_oracle(res, ref)
     feasible = [(r.constraint_costs == 0).sum().item() for r in ref['rollouts']]
     assert max(feasible) >= w.num_elites  # the objective decided at least one selection
+
+
+@pytest.mark.parametrize('n_s', [3, 4, 6])
+def test_remainder_bound_with_nonsymmetric_q_in_higher_dimensions(n_s):
+    """test_utils.py:35-59 generalised: the reference takes r^2 = max Re lambda(q B) from a general `torch.eig`
+    (utils.py:175-185, 651-665), so a NON-symmetric shape matrix handed to onestep_reachability must go through a general
+    eigenvalue routine for n_s >= 3 as well (csrc/eig_small.cuh), not through the symmetrised Jacobi form."""
+    rng = np.random.default_rng(60 + n_s)
+    n, N = 140, 96
+    x = rng.uniform(-1, 1, (n, n_s + 1))
+    y = 0.1 * np.sin(x @ rng.standard_normal((n_s + 1, n_s)))
+    ls, os_, nz = np.full((n_s, n_s + 1), 0.9), np.full(n_s, 0.05), np.full(n_s, 5e-5)
+    a_ = rng.standard_normal((N, n_s, n_s))
+    q = 1e-2 * (a_ @ a_.transpose(0, 2, 1) / n_s + 0.1 * np.eye(n_s))
+    q = q + 0.05 * np.abs(q).max(axis=(1, 2), keepdims=True) * rng.standard_normal((N, n_s, n_s))  # clearly non-symmetric
+    k_fb = rng.uniform(-1, 0, (1, n_s))
+    bmat = np.eye(n_s) + k_fb.T @ k_fb
+    real = np.array([np.abs(np.linalg.eigvals(qi @ bmat).imag).max() == 0 for qi in q])
+    assert real.sum() >= N // 2
+    q = q[real]
+    N = q.shape[0]
+    p, u = 0.1 * rng.standard_normal((N, n_s)), rng.uniform(-1, 1, (N, 1))
+    l = np.full(n_s, 0.05)
+    ssm = se.B200GpCemSSM(None, n_s, 1, ls, os_, nz, device=DEV)
+    ssm.update_model(G(x), G(y), replace_old=True)
+    p1, q1, sig = se.onestep_reachability(G(p), ssm, G(u), G(l), G(l), G(q), k_fb=G(k_fb), c_safety=2.0)
+    gp = oracle.OracleGpCemSSM(n_s, 1, ls, os_, nz)
+    gp.update_model(T(x), T(y), replace_old=True)
+    rp, rq, rs = oracle.onestep_reachability(T(p), gp, T(u), T(l), T(l), T(q), T(k_fb), 2.0)
+    assert rel_err(p1.cpu(), rp, 1e-3) < 1e-9 and rel_err(sig.cpu(), rs) < 1e-8
+    assert rel_err(q1.cpu(), rq, float(rq.abs().max()) * 1e-3) < 1e-8
+    # and it matters: the symmetrised matrix has a different spectrum
+    sym = np.array([np.linalg.eigvalsh(0.5 * (qi + qi.T) @ bmat @ np.eye(n_s)).max() if False else
+                    np.linalg.eigvals(0.5 * (qi + qi.T) @ bmat).real.max() for qi in q])
+    gen = np.array([np.linalg.eigvals(qi @ bmat).real.max() for qi in q])
+    assert np.abs(sym / gen - 1).max() > 1e-4

@@ -324,3 +324,38 @@ def test_runner_host_logic_with_a_scripted_solver():
     assert solver.batch_shapes == [(3, 2)] * 4  # the finished scenario keeps its slot
     assert np.array_equal(res[0][0], xx) and np.array_equal(res[2][0], xx)
     assert res[1][0].shape == (3, 3) and res[1][4] and res[1][3][:, 0].tolist() == [0, 0, 0]
+
+
+def test_general_eigenvalue_routine_matches_lapack():
+    """csrc/eig_small.cuh (host build of the function the kernels call for a non-symmetric shape matrix): the largest real
+    eigenvalue of q B as the reference takes it from a general `torch.eig` (utils.py:175-185, 651-665); NaN for a complex
+    pair, where the reference asserts.  Includes the reference's own non-symmetric case (test_utils.py:35-59)."""
+    lib = _lib.load()
+
+    def eig_max(m):
+        m = np.ascontiguousarray(m, dtype=np.float64)
+        out = ctypes.c_double(0)
+        assert lib.se_debug_eig_max(m.ctypes.data_as(ctypes.POINTER(ctypes.c_double)), m.shape[0], ctypes.byref(out)) == 0
+        return out.value
+
+    q = np.array([[.8, .2], [.1, .9]])  # hmm... the 2 x 2 of test_utils.py:35-59 (non-symmetric on purpose)
+    k_fb = np.array([[.5, .2]])
+    assert np.isclose(eig_max(q @ (np.eye(2) + k_fb.T @ k_fb)), np.linalg.eigvals(q @ (np.eye(2) + k_fb.T @ k_fb)).real.max(),
+                      rtol=1e-13)
+    rng = np.random.default_rng(5)
+    checked = 0
+    for trial in range(3000):
+        n = int(rng.integers(1, 7))
+        a = rng.standard_normal((n, n))
+        q = a @ a.T / n + 0.1 * np.eye(n)
+        q = q + 0.02 * np.abs(q).max() * rng.standard_normal((n, n))  # clearly non-symmetric
+        k = rng.uniform(-1, 0, (1, n))
+        m = q @ (np.eye(n) + k.T @ k) if trial % 3 else np.eye(n) * 2.0 + 1e-7 * rng.standard_normal((n, n))
+        ev = np.linalg.eigvals(m)
+        got = eig_max(m)
+        if np.abs(ev.imag).max() > 1e-9 * np.abs(ev).max():
+            continue  # complex pair: NaN or the real part, like an assertion in the reference
+        checked += 1
+        assert abs(got - ev.real.max()) <= 1e-9 * np.abs(ev).max(), (trial, n, got, ev)
+    assert checked > 2000
+    assert np.isnan(eig_max(np.array([[0., 1., 0.], [-1., 0., 0.], [0., 0., -5.]])))  # rotation block: +-i
