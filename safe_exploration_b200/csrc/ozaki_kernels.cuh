@@ -721,6 +721,15 @@ gp_trisumsq_ozaki_kernel(const int8_t* __restrict__ a_img, const int8_t* __restr
           mbar_wait(empty_bar(stage), phase ^ 1u);
           if (dbg & 1) {  // measurement only: no operand traffic
             mbar_arrive(full_bar(stage));
+          } else if (dbg & 12) {  // measurement only: one operand's traffic (4: candidates' digits skipped, 8: L^-1's)
+            const uint32_t dst = base + stage * C::STAGE_BYTES;
+            if (dbg & 4) {
+              mbar_expect_tx(full_bar(stage), ks * S * B_BLK);
+              bulk_g2s(dst + C::KS * S * A_BLK, b_src + (int64_t)kb * (S * B_BLK), ks * S * B_BLK, full_bar(stage));
+            } else {
+              mbar_expect_tx(full_bar(stage), ks * S * A_BLK);
+              bulk_g2s(dst, a_src + (int64_t)kb * (S * A_BLK), ks * S * A_BLK, full_bar(stage));
+            }
           } else {
             mbar_expect_tx(full_bar(stage), ks * C::STEP_BYTES);
             const uint32_t dst = base + stage * C::STAGE_BYTES;
