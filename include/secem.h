@@ -122,6 +122,24 @@ int se_gp_mll_grad(int n_s, int d, int64_t n, const double* dev_x, const double*
                    const double* host_lengthscale, const double* host_outputscale, const double* host_noise,
                    double* dev_workspace, double* dev_grad, void* stream);
 
+/* se_gp_mll_grad without a caller workspace and without any allocation.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight
+ * serving loops, harnesses that forbid it).  The per-tile partial sums live in a file-scope
+ * `static __device__ __align__(256)` array of SE_MLL_GRAD_STATIC_MAX_BYTES inside libsecem.so (every GPU that loads
+ * the library holds it until the process exits); the entry point resolves its device address once per device with
+ * cudaGetSymbolAddress and calls no cudaMalloc / cudaFree / allocating library routine.  Same arguments and result
+ * (bit for bit: same kernels, same fixed reduction order) as se_gp_mll_grad minus dev_workspace.
+ *   - sizes with se_gp_mll_grad_workspace(n_s, d, n) > SE_MLL_GRAD_STATIC_MAX_BYTES are refused (< 0, message in
+ *     se_last_error()); 4 MiB covers n = 5000, n_s = 4, d = 5 (0.7 MB) up to n = 8000, n_s = 6, d = 9.
+ *   - every call on a device shares the one array (it keeps the last call's contents; nothing in it has to start at
+ *     zero, each call overwrites every slot it reads).  Calls that OVERLAP on the same GPU -- two streams, or two
+ *     host threads -- race on it: serialise them (one stream, or events between streams). */
+#define SE_MLL_GRAD_STATIC_MAX_BYTES (4 << 20)
+int64_t se_gp_mll_grad_static_max_bytes(void);
+int se_gp_mll_grad_static(int n_s, int d, int64_t n, const double* dev_x, const double* dev_alpha,
+                          const double* dev_kinv, const double* host_lengthscale, const double* host_outputscale,
+                          const double* host_noise, double* dev_grad, void* stream);
+
 /* ---------------------------------------------------------------------------------------------------------------
  * Problem constants: what CemSafeMPC._dynamics_func and construct_constraints close over
  * (safe_exploration/safempc_cem.py:135-146, 162-200, 288-312).  All host pointers, double.

@@ -89,3 +89,64 @@ extern "C" int se_gp_mll_grad(int n_s, int d, int64_t n, const double* dev_x, co
   SE_LAUNCH(gp_mll_grad_reduce_kernel, n_s, 256, 0, st, dev_workspace, tri, d, h, dev_grad);
   return 0;
 }
+
+// ---------------------------------------------------------------------------------------------------------------
+// se_gp_mll_grad_static: the same gradient with the per-tile partial sums in library-owned static device memory, for
+// callers that may not allocate (CUDA graph capture, serving loops).  No counterpart in the reference.
+// ---------------------------------------------------------------------------------------------------------------
+
+// The scratch array.  File scope, so every GPU that loads libsecem.so holds these 4 MiB until the process exits.
+// In HOST code the name `g_mll_scratch` is only a stand-in for the symbol, never a device address: the address comes
+// from cudaGetSymbolAddress, once per device, with that device current (mll_scratch_ptr below).
+constexpr int64_t kMllScratchDoubles = SE_MLL_GRAD_STATIC_MAX_BYTES / (int64_t)sizeof(double);
+static __device__ __align__(256) double g_mll_scratch[kMllScratchDoubles];
+
+namespace se {
+
+constexpr int kMaxDevices = 64;
+
+// Device address of g_mll_scratch on the CURRENT device (resolved on first use per device, then cached).
+static int mll_scratch_ptr(double** out) {
+  static std::mutex mu;
+  static double* ptrs[kMaxDevices] = {};
+  int dev = 0;
+  SE_CUDA(cudaGetDevice(&dev));
+  SE_REQUIRE(dev >= 0 && dev < kMaxDevices, "se_gp_mll_grad_static: device ordinal %d outside 0..%d", dev,
+             kMaxDevices - 1);
+  std::lock_guard<std::mutex> lock(mu);
+  if (!ptrs[dev]) {
+    double* p = nullptr;
+    const cudaError_t e = cudaGetSymbolAddress(reinterpret_cast<void**>(&p), g_mll_scratch);
+    if (e != cudaSuccess || !p)
+      return fail("se_gp_mll_grad_static: cudaGetSymbolAddress(g_mll_scratch) on device %d -> %s", dev,
+                  cudaGetErrorString(e));
+    ptrs[dev] = p;
+  }
+  *out = ptrs[dev];
+  return 0;
+}
+
+}  // namespace se
+
+extern "C" int64_t se_gp_mll_grad_static_max_bytes(void) { return SE_MLL_GRAD_STATIC_MAX_BYTES; }
+
+extern "C" int se_gp_mll_grad_static(int n_s, int d, int64_t n, const double* dev_x, const double* dev_alpha,
+                                     const double* dev_kinv, const double* host_lengthscale,
+                                     const double* host_outputscale, const double* host_noise, double* dev_grad,
+                                     void* stream) {
+  SE_REQUIRE(n_s >= 1 && n_s <= SE_MAX_NS && d >= 1 && d <= SE_MAX_D, "n_s = %d / d = %d outside 1..%d / 1..%d", n_s,
+             d, SE_MAX_NS, SE_MAX_D);
+  SE_REQUIRE(n >= 1 && n <= 46340 * (int64_t)kTrainTile / 2, "se_gp_mll_grad_static: n = %lld out of range",
+             (long long)n);
+  const int64_t need = se_gp_mll_grad_workspace(n_s, d, n);
+  SE_REQUIRE(need <= SE_MLL_GRAD_STATIC_MAX_BYTES,
+             "se_gp_mll_grad_static: n_s = %d, d = %d, n = %lld needs %lld bytes of per-tile partial sums, the static "
+             "scratch array holds %lld (SE_MLL_GRAD_STATIC_MAX_BYTES); use se_gp_mll_grad with a caller workspace",
+             n_s, d, (long long)n, (long long)need, (long long)SE_MLL_GRAD_STATIC_MAX_BYTES);
+  double* scratch = nullptr;
+  SE_TRY(mll_scratch_ptr(&scratch));
+  // Every slot the reduction reads is written by the tile kernel of the same call (all o, tiles, d + 2 sums), so the
+  // previous call's contents never need clearing.  The two kernels below are the only work: no allocation anywhere.
+  return se_gp_mll_grad(n_s, d, n, dev_x, dev_alpha, dev_kinv, host_lengthscale, host_outputscale, host_noise, scratch,
+                        dev_grad, stream);
+}
