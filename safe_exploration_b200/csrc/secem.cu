@@ -352,23 +352,57 @@ static int gp_reserve(se_gp_s* g, int64_t N) {
   SE_TRY(grow(&g->partial, &g->partial_bytes, (size_t)g->ns * (g->n_pad / 32) * rows * g->esz));
   if (g->impl == SE_GEMM_TC) {
     const int64_t split_rows = rows < kSplitRows ? rows : kSplitRows;
-    // two sets: the fused ellipsoid step reads one step's segment sums while the kernel rows of the next are written
-    SE_TRY(grow(&g->kpart, &g->kpart_bytes, 2 * kpart_set_bytes(g, split_rows)));
+    // two sets for small batches: the fused ellipsoid step reads one step's segment sums while the kernel rows of the
+    // next are written; one set for the whole chunk when large batches cut the training set to balance the tail
+    const size_t two_small = 2 * kpart_set_bytes(g, split_rows), one_large = kpart_set_bytes(g, rows);
+    SE_TRY(grow(&g->kpart, &g->kpart_bytes, two_small > one_large ? two_small : one_large));
   }
   return 0;
 }
-// Kernel-row launches of fewer than kSplitRows candidates do not fill the machine with one CTA per 16 rows (148 SMs x
-// 8 CTAs); the training set is then split over CTAs in runs of 128-point segments.  Returns segments per CTA, 0 = none.
-static int kstar_segments_per_cta(const se_gp_s* g, int rows_pad) {
+// Resident CTAs per SM of the kernel-row kernel of the tensor-core path (its launch bounds, ozaki_kernels.cuh): one
+// thread per cell carrying all outputs (n_s = 1) -> 64-thread CTAs, 8 (n_s <= 3) or 6 per SM; one output per warp
+// group (n_s >= 2, SE_KSTAR_OPT != 0) -> 64 n_s threads, 768 (d <= 5) or 512 threads per SM.
+static int kstar_ctas_per_sm(const se_gp_s* g) {
+  static const int opt_env = getenv("SE_KSTAR_OPT") ? atoi(getenv("SE_KSTAR_OPT")) : 1;
+  if (g->ns < 2 || opt_env != 1) return g->ns <= 3 ? 8 : 6;
+  const int per_sm = (g->d <= 5 ? 768 : 512) / (64 * g->ns);
+  return per_sm > 0 ? per_sm : 1;
+}
+// How a kernel-row launch of rows_pad candidates cuts the training set over blockIdx.y (runs of 128-point segments);
+// returns segments per CTA, 0 = one CTA walks all of it.  The segment sums are added in a fixed order by the consumer,
+// so the result does not depend on the cut.  Two reasons to cut:
+//  - fewer than kSplitRows candidates do not fill the machine with one CTA per 16 rows;
+//  - more than one wave of CTAs leaves a tail: C2's 1024 CTAs on 148 x 6 = 888 slots run as one full wave and one that
+//    is 15 % full (ncu: achieved occupancy 28.8 % of a theoretical 37.5 %).  Shorter CTAs shrink the tail to a
+//    fraction of a wave; the cut with the lowest modelled time ceil(CTAs / slots) x (length + fixed cost) is taken.
+static int kstar_segments_per_cta(const se_gp_s* g, int rows_pad, int64_t cap_rows) {
   static const int env = getenv("SE_KSTAR_SPLIT") ? atoi(getenv("SE_KSTAR_SPLIT")) : 1;
+  static const int tail_env = getenv("SE_KSTAR_TAIL") ? atoi(getenv("SE_KSTAR_TAIL")) : 1;  // > 1: force that many ways
   const int segs = g->n_pad / 128;
-  if (!env || g->impl != SE_GEMM_TC || rows_pad >= kSplitRows || segs < 2) return 0;
+  if (!env || g->impl != SE_GEMM_TC || segs < 2 || rows_pad > cap_rows) return 0;
   const int row_ctas = rows_pad / 16;
-  int ways = (2 * g->sm_count + row_ctas - 1) / row_ctas;  // ~2 CTAs per SM in total
-  if (ways > segs) ways = segs;
-  if (ways < 2) return 0;
-  const int spc = (segs + ways - 1) / ways;
-  return spc < segs ? spc : 0;
+  if (rows_pad < kSplitRows) {
+    int ways = (2 * g->sm_count + row_ctas - 1) / row_ctas;  // ~2 CTAs per SM in total
+    if (ways > segs) ways = segs;
+    if (ways < 2) return 0;
+    const int spc = (segs + ways - 1) / ways;
+    return spc < segs ? spc : 0;
+  }
+  if (!tail_env) return 0;
+  const int64_t slots = (int64_t)g->sm_count * kstar_ctas_per_sm(g);
+  auto cost = [&](int spc) {  // in units of one full-length CTA; 0.5 % of it per CTA for the prologue
+    const int ny = (segs + spc - 1) / spc;
+    const int64_t waves = ((int64_t)row_ctas * ny + slots - 1) / slots;
+    return (double)waves * ((double)spc / segs + 0.005);
+  };
+  int best = segs;
+  if (tail_env > 1) {
+    best = (segs + tail_env - 1) / tail_env;
+  } else {
+    for (int spc = segs - 1; spc >= 1; --spc)
+      if (cost(spc) < 0.97 * cost(best)) best = spc;  // a finer cut has to pay for its extra segment traffic
+  }
+  return best < segs ? best : 0;
 }
 static int gp_reserve_posterior(se_gp_s* g, int64_t N) {
   if (g->post_cap >= N) return 0;
@@ -412,11 +446,14 @@ static PostPart post_part(se_gp_s* g, int64_t row0, int nrows, int64_t slot_row0
   // slot_row0: first (padded) row of this part inside the workspace
   pp.kst = (char*)g->kst + (size_t)g->ns * slot_row0 * g->n_pad * g->esz;
   pp.partial = (char*)g->partial + (size_t)g->ns * (g->n_pad / 32) * slot_row0 * g->esz;
-  pp.seg_per_cta = kstar_segments_per_cta(g, pp.rows_pad);
+  // rows of segment sums the workspace holds beyond this part's slot (small batches: half of it, see gp_reserve)
+  const int64_t set_rows = g->kpart ? (int64_t)(g->kpart_bytes / kpart_set_bytes(g, 1)) : 0;
+  const int64_t cap_rows = pp.rows_pad < kSplitRows ? (set_rows / 2 < kSplitRows ? set_rows / 2 : kSplitRows) - slot_row0
+                                                    : set_rows - slot_row0;
+  pp.seg_per_cta = kstar_segments_per_cta(g, pp.rows_pad, cap_rows);
   pp.nseg = pp.seg_per_cta > 0 ? g->n_pad / 128 : 0;
   pp.kpart = g->kpart ? (char*)g->kpart + (size_t)(g->n_pad / 128) * slot_row0 * g->ns * (1 + g->d) * sizeof(double)
                       : nullptr;
-  if (pp.nseg > 0 && (slot_row0 + pp.rows_pad > kSplitRows || !g->kpart)) pp.seg_per_cta = pp.nseg = 0;
   return pp;
 }
 

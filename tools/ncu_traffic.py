@@ -32,6 +32,8 @@ def main():
                 kname = re.sub(r'\(.*$', '', r[name]).replace('se::', '', 1).replace(', ', ',').replace('void ', '')
                 if '<' in kname and 'kstar' in kname:
                     kname = kname.split('<')[0]
+                if not kname.startswith('oz::'):  # the raw page prints the bare function name; bench.py asks with the namespace
+                    kname = 'oz::' + kname
                 e = per_kernel.setdefault(kname, dict(bytes=[], us=[]))
                 e['bytes'].append(float(r[rd]) * SCALE[units[rd]] + float(r[wr]) * SCALE[units[wr]])
                 e['us'].append(float(r[dur]) * {'ns': 1e-3, 'us': 1.0, 'ms': 1e3}.get(units[dur], 1.0))
