@@ -15,6 +15,9 @@
 #include "../../include/secem.h"
 
 #define SE_MAX_D (SE_MAX_NS + SE_MAX_NU)
+#ifndef SE_KSTAR_TPS
+#define SE_KSTAR_TPS 512  // resident threads per SM of the one-output-per-warp-group kernel-row kernel: 128 registers each (measured: C2 0.164 ms, C3 1.29 ms; 768 threads / 80 registers 0.168 / 1.40; 896 and 1024 slower still)
+#endif
 #define SE_HD __host__ __device__ __forceinline__
 
 namespace se {
@@ -187,8 +190,10 @@ __device__ __forceinline__ double exp_tab(double x, const double* __restrict__ t
 // kernel gets its fixed-point scaled value k 2^(63 - eA) without a multiply (|shift| and the result stay far inside the
 // normal range: x >= -700, shift ~ 60 .. 80).
 __device__ __forceinline__ double exp_tab_scaled(double x, const double* __restrict__ tab, int shift) {
-  const bool tiny = (unsigned)__double2hiint(x) >= 0xC085E000u;  // x <= -700 (or -Inf)
-  const double xc = tiny ? -700.0 : x;
+  // clamp at -700 with ONE unsigned minimum on the high word: negative doubles order like their bit patterns, so
+  // x <= -700 (or -Inf / NaN with the sign set) becomes -700 - (a fraction of 2^-11 from the untouched low word), and
+  // non-negative x (high word below 2^31) pass through.  The clamped value only has to make the result vanish.
+  const double xc = __hiloint2double((int)min((unsigned)__double2hiint(x), 0xC085E000u), __double2loint(x));
   const double t = fma(xc, 92.33248261689366, 6755399441055744.0);  // k = rint(64 x / ln 2) in the low word
   const int k = __double2loint(t);
   const double kf = t - 6755399441055744.0;

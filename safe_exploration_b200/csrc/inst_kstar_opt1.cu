@@ -10,6 +10,9 @@ int launch_kstar_slices_opt1(const GpDev<double>& gp, const double* p, int64_t p
                              int8_t* a_img, double* mean, double* jac, int spc, double* kpart, unsigned grid_x,
                              unsigned grid_y, cudaStream_t stream) {
   const dim3 grid(grid_x, grid_y);
+  if (S == 6)  // the default plane count of float64-class models: compile-time plane count (inst_kstar_opt1_s6.cu)
+    return launch_kstar_slices_opt1_s6(gp, p, p_stride, u, u_stride, row0, nrows, rows_pad, exp_a, a_img, mean, jac, spc,
+                                       kpart, grid_x, grid_y, stream);
 #define SE_CASE(NS_, NU_)                                                                                            \
   if (NS_ >= 2 && gp.ns == NS_ && gp.nu == NU_) {                                                                    \
     if (jac)                                                                                                         \

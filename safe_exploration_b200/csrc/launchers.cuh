@@ -80,6 +80,10 @@ int launch_kstar_slices_opt1(const GpDev<double>& gp, const double* p, int64_t p
                              int64_t u_stride, int64_t row0, int nrows, int rows_pad, const int* exp_a, int S,
                              int8_t* a_img, double* mean, double* jac, int spc, double* kpart, unsigned grid_x,
                              unsigned grid_y, cudaStream_t stream);
+int launch_kstar_slices_opt1_s6(const GpDev<double>& gp, const double* p, int64_t p_stride, const double* u,
+                                int64_t u_stride, int64_t row0, int nrows, int rows_pad, const int* exp_a, int8_t* a_img,
+                                double* mean, double* jac, int spc, double* kpart, unsigned grid_x, unsigned grid_y,
+                                cudaStream_t stream);
 int launch_trisumsq_ozaki(const int8_t* a_img, const int8_t* b_img, const double* scale_b, int n, int n_pad,
                           int rows_pad, int ns, int S, double* partial, int sm_count, int* nb_out, cudaStream_t stream);
 int launch_oz_probe(const int8_t* a_img, const int8_t* b_img, int nk, int S, int lbo, int sbo, int32_t* out,

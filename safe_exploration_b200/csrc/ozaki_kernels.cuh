@@ -432,17 +432,22 @@ struct FuseArgs<true> {
 // the differences are recomputed per output, but a thread holds 1 / NS of the accumulators, so more warps fit an SM;
 // the kernel waits on dependent FP64 issue (ncu: `wait` 2.5 per issue, 3.3 warps per scheduler at 128 registers), not
 // on the pipe.  Same arithmetic per output either way: the results are bit-identical.
-template <int NS, int D, bool JAC, bool FUSE = false, int OPT = NS>
+// SFIX > 0: the number of digit planes is a compile-time constant (the launcher passes S == SFIX): the eight predicated
+// stores of a step, each with its own address arithmetic and compare against S, become SFIX plain stores off one base
+// pointer -- 35 of the ~230 instructions a warp issues per 16-point step (the kernel is issue-bound: ncu shows 64 - 72 %
+// of the issue slots busy, `not selected` and `math pipe throttle` the leading stall reasons).
+template <int NS, int D, bool JAC, bool FUSE = false, int OPT = NS, int SFIX = 0>
 // CTAs per SM: 8 (128 registers) is the measured optimum for n_s <= 3 (C2: 0.216 ms; 6 -> 0.279, 10 -> 0.226, 12 -> 0.240);
 // with 4 and more outputs the accumulators no longer fit and 6 (168 registers) wins (C3: 3.10 vs 3.82 ms)
 // (OPT == 1: 768 threads per SM -> 80 registers for inputs of up to 5 dimensions, 512 -> 128 registers beyond)
 __global__ void __launch_bounds__(64 * (NS / OPT), OPT == NS ? (NS <= 3 ? 8 : 6)
-                                                               : ((D <= 5 ? 768 : 512) / (64 * NS) > 0 ? (D <= 5 ? 768 : 512) / (64 * NS) : 1))
+                                                               : ((D <= 5 ? SE_KSTAR_TPS : 512) / (64 * NS) > 0 ? (D <= 5 ? SE_KSTAR_TPS : 512) / (64 * NS) : 1))
 gp_kstar_slices8_kernel(GpDev<double> gp, const double* __restrict__ p, int64_t p_stride, const double* __restrict__ u,
-                        int64_t u_stride, int64_t row0, int nrows, int rows_pad, const int* __restrict__ exp_a, int S,
+                        int64_t u_stride, int64_t row0, int nrows, int rows_pad, const int* __restrict__ exp_a, int S_arg,
                         int8_t* __restrict__ a_img, double* __restrict__ mean, double* __restrict__ jac,
                         int seg_per_cta, double* __restrict__ kpart, FuseArgs<FUSE> fa) {
   static_assert(OPT == NS || OPT == 1, "a thread carries all outputs or one");
+  const int S = SFIX > 0 ? SFIX : S_arg;
   constexpr int NT = 64 * (NS / OPT);  // threads per CTA
   const int lane = threadIdx.x & 31;
   const int o_base = OPT == NS ? 0 : (int)(threadIdx.x >> 6);  // this warp group's first output
@@ -597,7 +602,7 @@ gp_kstar_slices8_kernel(GpDev<double> gp, const double* __restrict__ p, int64_t 
       int8_t* dst = dst0 + o * img_o;
 #pragma unroll
       for (int t = 0; t < MAX_S; ++t)
-        if (t < S) *reinterpret_cast<uint32_t*>(dst + t * A_BLK) = word[t];
+        if (SFIX > 0 ? t < SFIX : t < S) *reinterpret_cast<uint32_t*>(dst + t * A_BLK) = word[t];
     }
   }
     // segment done: fold the quads (lanes r8, r8 + 8, r8 + 16, r8 + 24 hold disjoint training points), then add the

@@ -361,11 +361,11 @@ static int gp_reserve(se_gp_s* g, int64_t N) {
 }
 // Resident CTAs per SM of the kernel-row kernel of the tensor-core path (its launch bounds, ozaki_kernels.cuh): one
 // thread per cell carrying all outputs (n_s = 1) -> 64-thread CTAs, 8 (n_s <= 3) or 6 per SM; one output per warp
-// group (n_s >= 2, SE_KSTAR_OPT != 0) -> 64 n_s threads, 768 (d <= 5) or 512 threads per SM.
+// group (n_s >= 2, SE_KSTAR_OPT != 0) -> 64 n_s threads, SE_KSTAR_TPS (d <= 5) or 512 threads per SM.
 static int kstar_ctas_per_sm(const se_gp_s* g) {
   static const int opt_env = getenv("SE_KSTAR_OPT") ? atoi(getenv("SE_KSTAR_OPT")) : 1;
   if (g->ns < 2 || opt_env != 1) return g->ns <= 3 ? 8 : 6;
-  const int per_sm = (g->d <= 5 ? 768 : 512) / (64 * g->ns);
+  const int per_sm = (g->d <= 5 ? SE_KSTAR_TPS : 512) / (64 * g->ns);
   return per_sm > 0 ? per_sm : 1;
 }
 // How a kernel-row launch of rows_pad candidates cuts the training set over blockIdx.y (runs of 128-point segments);
