@@ -259,8 +259,13 @@ def _max_over_ranks(x, world, dev):
     return float(t.item())
 
 
-def _gemm_kernel_name(digits):
+def _gemm_kernel_name(digits, rows_local=0):
+    """Name of the variance-GEMM kernel the library launches for this run (csrc/inst_ozaki.cu: launch_trisumsq_ozaki)."""
     mode = int(os.environ.get('SE_OZ_REUSE', '2'))
+    shape = int(os.environ.get('SE_OZ_CLUSTER', '12'))
+    tiles = (rows_local + 127) // 128
+    if mode == 2 and shape in (12, 21) and not (shape == 12 and tiles % 2):
+        return f'oz::gp_trisumsq_ozaki_cluster_kernel<{digits},{shape // 10},{shape % 10}>'
     return f'oz::gp_trisumsq_ozaki_kernel<{digits},{mode}>'
 
 
@@ -498,11 +503,11 @@ def run_b200(args):
             achieved = work_per_launch / (gemm_avg_ms * 1e-3) / 1e12 if gemm_avg_ms > 0 else None
         fp64_equiv = fp64_flop_per_launch / (gemm_avg_ms * 1e-3) / 1e12 if gemm_avg_ms > 0 else None
         op_bytes = digits if impl_name == 'tcgen05-i8' else esz
-        traffic, stamp = (profiled_traffic(_gemm_kernel_name(digits), f'{args.config}/N{rows_local}')
+        traffic, stamp = (profiled_traffic(_gemm_kernel_name(digits, rows_local), f'{args.config}/N{rows_local}')
                           if impl_name == 'tcgen05-i8' else (None, None))
         roofline = {
             'bound': 'tensor', 'kernel': 'gp_trisumsq (variance GEMM: || L^-1 k* ||^2)',
-            'kernel_name': _gemm_kernel_name(digits) if impl_name == 'tcgen05-i8' else impl_name, 'impl': impl_name,
+            'kernel_name': _gemm_kernel_name(digits, rows_local) if impl_name == 'tcgen05-i8' else impl_name, 'impl': impl_name,
             'pipe': pipe, 'achieved': achieved, 'peak': peak, 'unit': unit,
             'frac': (achieved / peak) if (achieved and peak) else None, 'peak_source': peak_src_txt,
             'work_per_launch': work_per_launch, 'avg_launch_ms': gemm_avg_ms, 'launches': inst['gemm_n'],

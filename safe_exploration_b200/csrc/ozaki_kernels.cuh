@@ -850,6 +850,234 @@ gp_trisumsq_ozaki_kernel(const int8_t* __restrict__ a_img, const int8_t* __restr
 }
 
 // ---------------------------------------------------------------------------------------------------------------------
+// K2, cluster flavour: a thread-block cluster of CA x CB CTAs works on CA neighbouring row tiles of L^-1 times CB
+// neighbouring candidate tiles (CTA rank = rb CA + ra takes row tile CA ibg + ra and candidate tile CB rtg + rb).
+// Digit planes are fetched from L2 once per GROUP instead of once per CTA: the CB CTAs that share a row tile each issue one
+// cp.async.bulk ... .multicast::cluster for 1 / CB of the stage's L^-1 bytes, the CA CTAs that share a candidate tile each
+// 1 / CA of its kernel-row bytes; a multicast lands at the same shared-memory offset in every CTA of its mask and signals
+// the full barrier there.  A stage may only be refilled when every CTA that receives the copy has read it, so a stage's
+// empty barrier counts CA + CB - 1 arrivals and the MMA warps commit to all CTAs that write into them
+// (tcgen05.commit ... .multicast::cluster).  All CTAs of a cluster run the same item sequence with the K extent of the
+// group's deepest row tile -- the extra K steps of the shallower tiles multiply the exact zeros that the image holds
+// above the diagonal, so the level sums (integers) are unchanged -- and the rings stay in lock step by construction.
+// L2 -> SM traffic per K step per SM at S = 6: 24 / CA + 12 / CB KB instead of 36.  Same partial-sum layout.
+// ---------------------------------------------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;\n" : "=r"(r));
+  return r;
+}
+__device__ __forceinline__ void cluster_sync_all() {
+  asm volatile("barrier.cluster.arrive.release.aligned;\n" ::: "memory");
+  asm volatile("barrier.cluster.wait.acquire.aligned;\n" ::: "memory");
+}
+__device__ __forceinline__ void bulk_g2s_multicast(uint32_t dst, const void* src, uint32_t bytes, uint32_t bar,
+                                                   uint16_t cta_mask) {
+  asm volatile(
+      "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.multicast::cluster [%0], [%1], %2, [%3], %4;\n" ::"r"(dst),
+      "l"(src), "r"(bytes), "r"(bar), "h"(cta_mask)
+      : "memory");
+}
+__device__ __forceinline__ void tc_commit_multicast(uint32_t bar, uint16_t cta_mask) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;\n" ::"r"(bar),
+               "h"(cta_mask)
+               : "memory");
+}
+
+// item sequence of cluster b (of G clusters): as next_item, over (output, candidate-tile group, row-tile group)
+template <int CA, int CB>
+__device__ __forceinline__ bool next_group_item(int round, const TriOrder& od_grp, int total, int ra, int rb, TriItem* it) {
+  const int G = gridDim.x / (CA * CB), b = blockIdx.x / (CA * CB);
+  const int idx = round * G + ((round & 1) ? G - 1 - b : b);
+  if (idx >= total) return false;
+  *it = decode_item_chunked(idx, od_grp);
+  it->rt = CB * it->rt + rb;
+  it->ib = CA * it->ib + ra;
+  return true;
+}
+
+template <int S, int CA, int CB>
+__global__ void __launch_bounds__(THREADS, 1)
+gp_trisumsq_ozaki_cluster_kernel(const int8_t* __restrict__ a_img, const int8_t* __restrict__ b_img,
+                                 const double* __restrict__ scale_b, int n, int n_pad, int rows_pad, TriOrder od_grp,
+                                 int rt_count, int nb, double* __restrict__ partial) {
+  using C = Cfg<S>;
+  static_assert((S * A_BLK) % (16 * CA) == 0 && (S * B_BLK) % (16 * CB) == 0, "a multicast piece is a multiple of 16 bytes");
+  static_assert(CA <= 2, "the image of L^-1 holds an even number of row tiles (n_pad is a multiple of 128), not a multiple of 4");
+  extern __shared__ unsigned char smem_raw[];
+  const uint32_t raw = smem_u32(smem_raw);
+  const uint32_t base = (raw + 1023u) & ~1023u;
+  const uint32_t bars = base + C::STAGES * C::STAGE_BYTES;
+  const uint32_t tmem_slot = bars + (2 * C::STAGES + 2) * 8;
+  auto full_bar = [&](int s) { return bars + 8u * s; };
+  auto empty_bar = [&](int s) { return bars + 8u * (C::STAGES + s); };
+  const uint32_t tmem_full = bars + 8u * (2 * C::STAGES), tmem_empty = tmem_full + 8u;
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int crank = (int)cluster_ctarank(), ra = crank % CA, rb = crank / CA;
+  // CTAs that share this CTA's candidate tile (same rb) / its row tile (same ra); every CTA that writes into this one
+  uint16_t mask_a = 0, mask_b = 0;
+#pragma unroll
+  for (int a = 0; a < CA; ++a) mask_a |= (uint16_t)(1u << (rb * CA + a));
+#pragma unroll
+  for (int b = 0; b < CB; ++b) mask_b |= (uint16_t)(1u << (b * CA + ra));
+  const uint16_t mask_all = mask_a | mask_b;
+  const int total = tri_total_items(od_grp.nb, od_grp.rt_count, od_grp.ns);
+  const int G = gridDim.x / (CA * CB);
+  const int rounds = (total + G - 1) / G;
+  const int nkb = n_pad / KB, nb_img = n_pad / TN;
+  // K extent of a group = that of its deepest row tile (rows of the image beyond nb are zero padding)
+  auto group_ksteps = [&](int ib) { return item_ksteps(min(ib - ib % CA + CA - 1, nb_img - 1), n); };
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < C::STAGES; ++s) {
+      mbar_init(full_bar(s), 1);
+      mbar_init(empty_bar(s), CA + CB - 1);  // every CTA this one receives copies from (itself included) releases a stage
+    }
+    mbar_init(tmem_full, 1);
+    mbar_init(tmem_empty, EPI_THREADS);
+    mbar_fence_init();
+  }
+  if (warp == 1) tmem_alloc(tmem_slot, TMEM_COLS);
+  tc_fence_before();
+  cluster_sync_all();  // the peers' barriers are initialised before anything is multicast or committed to them
+  tc_fence_after();
+  uint32_t tmem_base;
+  asm volatile("ld.shared.u32 %0, [%1];\n" : "=r"(tmem_base) : "r"(tmem_slot));
+
+  if (warp == 0) {
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int r = 0; r < rounds; ++r) {
+        TriItem it;
+        if (!next_group_item<CA, CB>(r, od_grp, total, ra, rb, &it)) continue;
+        const int8_t* a_src = a_img + ((int64_t)it.o * rt_count + it.rt) * nkb * (int64_t)(S * A_BLK);
+        const int8_t* b_src = b_img + ((int64_t)it.o * nb_img + it.ib) * nkb * (int64_t)(S * B_BLK);
+        const int nk = group_ksteps(it.ib);
+        for (int kb = 0; kb < nk; kb += C::KS) {
+          const int ks = min(C::KS, nk - kb);
+          mbar_wait(empty_bar(stage), phase ^ 1u);
+          mbar_expect_tx(full_bar(stage), ks * C::STEP_BYTES);
+          const uint32_t dst = base + stage * C::STAGE_BYTES;
+          // this CTA's piece of the stage's kernel-row bytes -> the CTAs on its candidate tile; of its L^-1 bytes -> the
+          // CTAs on its row tile
+          const uint32_t a_piece = ks * S * A_BLK / CA, b_piece = ks * S * B_BLK / CB;
+          if (CA == 1)
+            bulk_g2s(dst, a_src + (int64_t)kb * (S * A_BLK), a_piece, full_bar(stage));
+          else
+            bulk_g2s_multicast(dst + ra * a_piece, a_src + (int64_t)kb * (S * A_BLK) + ra * a_piece, a_piece,
+                               full_bar(stage), mask_a);
+          if (CB == 1)
+            bulk_g2s(dst + C::KS * S * A_BLK, b_src + (int64_t)kb * (S * B_BLK), b_piece, full_bar(stage));
+          else
+            bulk_g2s_multicast(dst + C::KS * S * A_BLK + rb * b_piece, b_src + (int64_t)kb * (S * B_BLK) + rb * b_piece,
+                               b_piece, full_bar(stage), mask_b);
+          if (++stage == C::STAGES) stage = 0, phase ^= 1u;
+        }
+      }
+    }
+  } else if (warp == 1) {
+    const uint32_t tb = __shfl_sync(0xffffffffu, tmem_base, 0);
+    const uint32_t a_lo0 = desc_lo(__shfl_sync(0xffffffffu, base, 0), LBO), dhi = desc_hi(SBO);
+    int stage = 0;
+    uint32_t phase = 0, tphase = 0;
+    for (int r = 0; r < rounds; ++r) {
+      TriItem it;
+      if (!next_group_item<CA, CB>(r, od_grp, total, ra, rb, &it)) continue;
+      const int nk = group_ksteps(it.ib);
+      // a row tile beyond nb is padding (zero rows): the narrowest MMA keeps the protocol going at next to no cost
+      const int cols = it.ib < nb ? item_cols(it.ib, n) : 16;
+      const uint32_t idesc = make_idesc(TM, cols);
+      const bool full_width = cols == TN;
+      mbar_wait(tmem_empty, tphase ^ 1u);
+      tc_fence_after();
+      for (int kb = 0; kb < nk; kb += C::KS) {
+        const int ks = min(C::KS, nk - kb);
+        mbar_wait(full_bar(stage), phase);
+        tc_fence_after();
+        const uint32_t a_lo = a_lo0 + stage * (C::STAGE_BYTES >> 4);
+        const uint32_t b_lo = a_lo + (C::KS * S * A_BLK >> 4);
+        if (elect_one()) {
+          if (!full_width) {
+#pragma unroll
+            for (int k = 0; k < C::KS; ++k)
+              if (k < ks)
+                issue_kstep<S, 1>(tb, a_lo + k * (S * A_BLK >> 4), b_lo + k * (S * B_BLK >> 4), dhi, idesc,
+                                  kb + k > 0 ? 1u : 0u);
+          } else {
+#pragma unroll
+            for (int k = 0; k < C::KS; ++k)
+              if (k < ks)
+                issue_kstep<S, 2>(tb, a_lo + k * (S * A_BLK >> 4), b_lo + k * (S * B_BLK >> 4), dhi, idesc,
+                                  kb + k > 0 ? 1u : 0u);
+          }
+          tc_commit_multicast(empty_bar(stage), mask_all);  // this CTA is done with the stage: tell every writer
+          if (kb + ks == nk) tc_commit(tmem_full);
+        }
+        __syncwarp();
+        if (++stage == C::STAGES) stage = 0, phase ^= 1u;
+      }
+      tphase ^= 1u;
+    }
+  } else {
+    const int quad = warp & 3;
+    const int half = (warp - 2) >> 2;
+    const int row = quad * 32 + lane;
+    const double lo_scale = S > 4 ? ldexp(1.0, 3 * RB - RB * (S - 1)) : 0.0;
+    uint32_t tphase = 0;
+    for (int r = 0; r < rounds; ++r) {
+      TriItem it;
+      if (!next_group_item<CA, CB>(r, od_grp, total, ra, rb, &it)) continue;
+      mbar_wait(tmem_full, tphase);
+      tc_fence_after();
+      const bool real = it.ib < nb;
+      const double* sbp = scale_b + (int64_t)it.o * n_pad + (int64_t)it.ib * TN;
+      const uint32_t tlane = tmem_base + ((uint32_t)(quad * 32) << 16);
+      const int c_end = real ? min((half + 1) * (TN / 2), item_cols(it.ib, n)) : 0;
+      long long hi[TN / 2], lo[TN / 2];
+#pragma unroll
+      for (int b = 0; b < TN / 16; ++b) {
+        const int c8 = half * (TN / 2) + b * 8;
+        if (c8 < c_end) {
+          int32_t d[S][8];
+#pragma unroll
+          for (int l = 0; l < S; ++l) tmem_ld8(tlane + (uint32_t)(l * TN + c8), d[l]);
+          tmem_ld_wait();
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            long long h = 0, w = 0;
+#pragma unroll
+            for (int l = 0; l < S && l < 4; ++l) h += (long long)d[l][j] << (RB * (3 - l));
+#pragma unroll
+            for (int l = 4; l < S; ++l) w += (long long)d[l][j] << (RB * (S - 1 - l));
+            hi[b * 8 + j] = h, lo[b * 8 + j] = w;
+          }
+        } else {
+#pragma unroll
+          for (int j = 0; j < 8; ++j) hi[b * 8 + j] = 0, lo[b * 8 + j] = 0;
+        }
+      }
+      tc_fence_before();
+      mbar_arrive(tmem_empty);
+      if (real) {
+        double sum = 0.0;
+#pragma unroll
+        for (int e = 0; e < TN / 2; ++e) {
+          const double v = ((double)hi[e] + (double)lo[e] * lo_scale) * __ldg(sbp + half * (TN / 2) + e);
+          sum += v * v;
+        }
+        partial[((int64_t)it.o * (2 * nb) + 2 * it.ib + half) * rows_pad + (int64_t)it.rt * TM + row] = sum;
+      }
+      tphase ^= 1u;
+    }
+  }
+  tc_fence_before();
+  cluster_sync_all();  // peers may still be arriving on this CTA's barriers: leave together
+  if (warp == 1) tmem_dealloc(tmem_base, TMEM_COLS);
+}
+
+// ---------------------------------------------------------------------------------------------------------------------
 // Probe (tests): one CTA, nk K steps of a single 128 x 64 tile; dumps every level accumulator.  out[S][128][64] int32.
 // lbo / sbo are parameters so the descriptor convention is pinned by a test and not by a comment.
 // ---------------------------------------------------------------------------------------------------------------------
