@@ -15,6 +15,9 @@
 #include "../../include/secem.h"
 
 #define SE_MAX_D (SE_MAX_NS + SE_MAX_NU)
+#ifndef SE_KSTAR_UNROLL
+#define SE_KSTAR_UNROLL 1  // 16-point steps of the kernel-row kernel unrolled together
+#endif
 #ifndef SE_KSTAR_TPS
 #define SE_KSTAR_TPS 512  // resident threads per SM of the one-output-per-warp-group kernel-row kernel: 128 registers each (measured: C2 0.164 ms, C3 1.29 ms; 768 threads / 80 registers 0.168 / 1.40; 896 and 1024 slower still)
 #endif

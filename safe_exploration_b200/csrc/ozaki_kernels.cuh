@@ -200,6 +200,7 @@ __device__ __forceinline__ uint64_t make_desc(uint32_t smem_addr, uint32_t lbo, 
          ((uint64_t)((sbo >> 4) & 0x3FFFu) << 32) | (1ull << 46);
 }
 
+constexpr int kKstarUnroll = SE_KSTAR_UNROLL;
 constexpr int RB = 8;  // radix bits
 // exponent e with |x| / 2^e <= 0.99, so that the top digit of rint(x / 2^e * 2^(8 S - 1)) stays inside [-127, 127]
 __host__ __device__ __forceinline__ int digit_exponent(double x) {
@@ -555,7 +556,7 @@ gp_kstar_slices8_kernel(GpDev<double> gp, const double* __restrict__ p, int64_t 
       asm volatile("cp.async.wait_group 0;\n" ::: "memory");
     }
     __syncthreads();
-#pragma unroll 1
+#pragma unroll kKstarUnroll
   for (int jl = 0; jl < CH; jl += 16) {
     const int j16 = ch * CH + jl;
     double x[D][4], al[OPT][4];

@@ -140,6 +140,45 @@ def test_tc_chunked_workspace_and_reruns_are_bit_identical():
         assert torch.equal(s, t) and torch.equal(s, r)
 
 
+_CLUSTER_SCRIPT = """
+import sys, numpy as np, torch
+sys.path.insert(0, {root!r})
+sys.path.insert(0, {tests!r})
+import safe_exploration_b200 as se
+from safe_exploration_b200 import _lib
+from test_gpu_tc import _random_model, G, DEV
+x, y, ls, os_, nz = _random_model({n_s}, 1, {n}, 9)
+z = G(np.random.default_rng(4).uniform(-1, 1, ({N}, {n_s} + 1)))
+gp = se.B200GpCemSSM(None, {n_s}, 1, ls, os_, nz, device=DEV, gemm_impl=_lib.SE_GEMM_TC)
+gp.update_model(G(x), G(y), replace_old=True)
+mean, var, jac = gp.predict_with_jacobians(z[:, :{n_s}].contiguous(), z[:, {n_s}:].contiguous())
+np.save({out!r}, var.cpu().numpy())
+"""
+
+
+@pytest.mark.parametrize('n_s,n,N', [(2, 500, 1024), (4, 333, 2048)])
+def test_cluster_gemm_equals_the_one_cta_gemm_bit_for_bit(n_s, n, N, tmp_path):
+    """The default variance GEMM runs 2-CTA clusters that share the digit planes of L^-1 through a multicast bulk copy
+    (SE_OZ_CLUSTER=12); the one-CTA kernel (0) and the pairs that share the candidates' planes (21: the shallower row
+    tile is padded with the exact zeros above the diagonal) form the same integer level sums and reduce them in the same
+    order, so the variances must agree to the last bit.  The engine is chosen per process: the other two run in
+    subprocesses."""
+    import os
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    got = {}
+    for shape in ('12', '0', '21'):
+        out = str(tmp_path / f'var_{shape}.npy')
+        script = _CLUSTER_SCRIPT.format(root=root, tests=os.path.join(root, 'tests'), n_s=n_s, n=n, N=N, out=out)
+        env = dict(os.environ, SE_OZ_CLUSTER=shape)
+        proc = subprocess.run([sys.executable, '-c', script], env=env, capture_output=True, text=True, timeout=300)
+        assert proc.returncode == 0, proc.stderr[-2000:]
+        got[shape] = np.load(out)
+    assert np.isfinite(got['12']).all() and (got['12'] > 0).all()
+    assert np.array_equal(got['12'], got['0']) and np.array_equal(got['12'], got['21'])
+
+
 def test_tc_model_update_rebuilds_the_digit_image():
     """update_model appends data (ssm_cem.py:72-99): the digit image of the new factor must be used afterwards."""
     x, y, ls, os_, nz = _random_model(2, 1, 600, 11)
