@@ -122,6 +122,27 @@ int se_gp_mll_grad(int n_s, int d, int64_t n, const double* dev_x, const double*
                    const double* host_lengthscale, const double* host_outputscale, const double* host_noise,
                    double* dev_workspace, double* dev_grad, void* stream);
 
+/* On-device factor refresh: W_o = L_o^-1 for K_o + noise_o I = L_o L_o^T, built block row by block
+ * row of 128 points from FP64 tensor-core (DMMA) products and one small Cholesky per block -- the arithmetic GPyTorch
+ * does lazily behind GpCemSSM._update_model (ssm_cem/gp_ssm_cem.py:96-101).  Because a block row only needs the rows
+ * above it, a model that only GREW (CemSSM.update_model(replace_old=False), ssm_cem.py:72-99; the reference's
+ * update_cholesky idea, ssm_pytorch/utilities.py:122-165) is extended from its old factor: pass the first block row that
+ * changed.  No cuSOLVER / cuBLAS call.
+ *   n_pad          a multiple of 128 >= n; rows / columns >= n of dev_k hold the identity (1 on the diagonal)
+ *   dev_k          [n_s, n_pad, n_pad] covariance (only rows >= 128 first_block are read, lower triangle + diagonal blocks)
+ *   dev_w, dev_wt  [n_s, n_pad, n_pad] W and W^T; rows (of W) / columns (of W^T) below 128 first_block must hold the old
+ *                  factor, everything else must be ZERO on entry
+ *   dev_diag       [n_s, n_pad] diagonal of L (log det K = 2 sum log diag)
+ *   dev_workspace  se_gp_factor_workspace(n_s, n_pad) bytes
+ *   dev_info       int32[n_s], zeroed by the caller: 1 + the first row whose pivot was not positive (0 = success) */
+int64_t se_gp_factor_workspace(int n_s, int64_t n_pad);
+int se_gp_factor(int n_s, int64_t n_pad, int first_block, const double* dev_k, double* dev_w, double* dev_wt,
+                 double* dev_diag, double* dev_workspace, int32_t* dev_info, void* stream);
+/* dev_kinv [n_s, n_pad, n_pad] = W^T W = (K + noise I)^-1, LOWER triangle only (64 x 128 tiles that touch it; the rest is
+ * left untouched), from dev_wt = W^T as written by se_gp_factor: what se_gp_mll_grad reads.  The reference gets the same
+ * quantity implicitly from autograd through GPyTorch's factorisation (gp_ssm_cem.py:116-121). */
+int se_gp_kinv(int n_s, int64_t n_pad, const double* dev_wt, double* dev_kinv, void* stream);
+
 /* se_gp_mll_grad without a caller workspace and without any allocation.  NO COUNTERPART IN THE REFERENCE: added
  * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight
  * serving loops, harnesses that forbid it).  The per-tile partial sums live in a file-scope

@@ -64,6 +64,9 @@ SIGNATURES = {
     "se_gp_kernel_matrix": (_i, [_i, _i, _i64, _vp, _dbl_p, _dbl_p, _dbl_p, _vp, _vp]),
     "se_gp_mll_grad_workspace": (_i64, [_i, _i, _i64]),
     "se_gp_mll_grad": (_i, [_i, _i, _i64, _vp, _vp, _vp, _dbl_p, _dbl_p, _dbl_p, _vp, _vp, _vp]),
+    "se_gp_factor_workspace": (_i64, [_i, _i64]),
+    "se_gp_factor": (_i, [_i, _i64, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
+    "se_gp_kinv": (_i, [_i, _i64, _vp, _vp, _vp]),
     "se_gp_mll_grad_static_max_bytes": (_i64, []),
     "se_gp_mll_grad_static": (_i, [_i, _i, _i64, _vp, _vp, _vp, _dbl_p, _dbl_p, _dbl_p, _vp, _vp]),
     "se_reach_onestep": (_i, [_vp, C.POINTER(SeProblem), _vp, _vp, _vp, _i64, _vp, _vp, _vp, _vp, _vp]),

@@ -122,11 +122,15 @@ class B200GpCemSSM(CemSSM):
                   (never fewer than 6); 7 / 8 = float64-equivalent; 4 / 3 = float32 tolerance (see set_tc_digits)
     :param incremental: keep the float64 inverse Cholesky factor on the device (n_s n^2 doubles) so that
                         `update_model(..., replace_old=False)` only computes the rows of the appended samples
+    :param factor_impl: 'native' (default): L^-1 and (K + noise I)^-1 come from this library's blocked factorisation
+                        (`se_gp_factor`, `se_gp_kinv`: FP64 DMMA products, no cuSOLVER / cuBLAS), which also extends a
+                        factor whose training set only grew; 'cusolver': the round-1 path through torch.linalg
     """
 
     def __init__(self, conf, state_dimen: int, action_dimen: int, lengthscale=None, outputscale=None, noise=None,
                  dtype: torch.dtype = torch.float64, device: Optional[str] = None, gemm_impl: int = _lib.SE_GEMM_AUTO,
-                 workspace_bytes: Optional[int] = None, tc_digits: int = 0, incremental: bool = True):
+                 workspace_bytes: Optional[int] = None, tc_digits: int = 0, incremental: bool = True,
+                 factor_impl: str = 'native'):
         super().__init__(state_dimen, action_dimen)
         kernel = getattr(conf, 'exact_gp_kernel', 'rbf') if conf is not None else 'rbf'
         if kernel != 'rbf':
@@ -147,6 +151,10 @@ class B200GpCemSSM(CemSSM):
             torch.as_tensor(noise, **f64).reshape(state_dimen).clone()
         self._gemm_impl = gemm_impl
         self._incremental = incremental  # keep the float64 inverse factor so appended samples cost O(m n^2)
+        if factor_impl not in ('native', 'cusolver'):
+            raise ValueError(f"factor_impl must be 'native' or 'cusolver', got {factor_impl!r}")
+        self._factor_impl = factor_impl
+        self._factor_pad = None          # native path: (x, W_pad, W^T_pad, hyper-parameters) of the current handle
         self._factor = None              # (x [n, d], L^-1 [n_s, n, n], hyper-parameters) of the current handle
         self._tc_digits = tc_digits
         self._workspace_bytes = workspace_bytes
@@ -197,21 +205,27 @@ class B200GpCemSSM(CemSSM):
         y = y_train.detach().to(device=self.device, dtype=torch.float64)
         n = x.size(0)
         hyp = torch.cat((self.lengthscale.reshape(-1), self.outputscale, self.noise))
-        linv = self._append_rows(x, hyp) if self._incremental else None
-        self.last_update = 'full' if linv is None else 'incremental'
-        if linv is None:
-            k = self.kernel_matrix(x)
-            chol = torch.linalg.cholesky(k)
-            del k
-            eye = torch.eye(n, dtype=torch.float64, device=self.device).expand(self.num_states, -1, -1)
-            linv = torch.linalg.solve_triangular(chol, eye, upper=False).tril_()
-            # alpha = (L L^T)^-1 y by two triangular solves (cholesky_solve's batched cuSOLVER path rejects n = 16384)
-            alpha = torch.linalg.solve_triangular(chol, y.t().unsqueeze(-1), upper=False)
-            alpha = torch.linalg.solve_triangular(chol.transpose(1, 2), alpha, upper=True).squeeze(-1)
-            del chol
-        else:
+        if self._factor_impl == 'native':
+            w_pad, first_block = self._factor_native(x, hyp)
+            self.last_update = 'full' if first_block == 0 else 'incremental'
+            linv = w_pad[:, :n, :n]
             alpha = torch.matmul(linv.transpose(1, 2), torch.matmul(linv, y.t().unsqueeze(-1))).squeeze(-1)
-        if self._incremental:
+        else:
+            linv = self._append_rows(x, hyp) if self._incremental else None
+            self.last_update = 'full' if linv is None else 'incremental'
+            if linv is None:
+                k = self.kernel_matrix(x)
+                chol = torch.linalg.cholesky(k)
+                del k
+                eye = torch.eye(n, dtype=torch.float64, device=self.device).expand(self.num_states, -1, -1)
+                linv = torch.linalg.solve_triangular(chol, eye, upper=False).tril_()
+                # alpha = (L L^T)^-1 y by two triangular solves (cholesky_solve's batched cuSOLVER path rejects n = 16384)
+                alpha = torch.linalg.solve_triangular(chol, y.t().unsqueeze(-1), upper=False)
+                alpha = torch.linalg.solve_triangular(chol.transpose(1, 2), alpha, upper=True).squeeze(-1)
+                del chol
+            else:
+                alpha = torch.matmul(linv.transpose(1, 2), torch.matmul(linv, y.t().unsqueeze(-1))).squeeze(-1)
+        if self._incremental and self._factor_impl != 'native':
             self._factor = (x, linv, hyp)
         xs = x.to(self.dtype).contiguous()
         al = alpha.to(self.dtype).contiguous()
@@ -234,6 +248,60 @@ class B200GpCemSSM(CemSSM):
             _lib.check(self._lib.se_gp_set_tc_digits(handle, self._tc_digits))
         if self._workspace_bytes is not None:
             _lib.check(self._lib.se_gp_set_workspace_limit(handle, int(self._workspace_bytes)))
+
+    def _padded_covariance(self, x: Tensor, n_pad: int, ls=None, os_=None, nz=None) -> Tensor:
+        """[n_s, n_pad, n_pad]: K + noise I on the training inputs, the identity on the padding."""
+        n = x.size(0)
+        k_pad = torch.zeros((self.num_states, n_pad, n_pad), dtype=torch.float64, device=x.device)
+        k_pad[:, :n, :n] = self.kernel_matrix(x, ls, os_, nz)
+        if n_pad > n:
+            k_pad.diagonal(dim1=1, dim2=2)[:, n:] = 1.0
+        return k_pad
+
+    def _run_factor(self, k_pad: Tensor, w_pad: Tensor, wt_pad: Tensor, first_block: int) -> Tensor:
+        """`se_gp_factor` on padded buffers -> diag(L) [n_s, n_pad]; raises like torch.linalg.cholesky on a bad pivot."""
+        n_pad = k_pad.size(1)
+        dev = k_pad.device
+        diag = torch.ones((self.num_states, n_pad), dtype=torch.float64, device=dev)
+        ws = torch.empty(max(1, self._lib.se_gp_factor_workspace(self.num_states, n_pad) // 8), dtype=torch.float64,
+                         device=dev)
+        info = torch.zeros((self.num_states,), dtype=torch.int32, device=dev)
+        with torch.cuda.device(dev):
+            _lib.check(self._lib.se_gp_factor(self.num_states, n_pad, first_block, _lib.ptr(k_pad), _lib.ptr(w_pad),
+                                              _lib.ptr(wt_pad), _lib.ptr(diag), _lib.ptr(ws), _lib.ptr(info),
+                                              _lib.stream_ptr(dev)))
+        bad = info.cpu()
+        if int(bad.max()) != 0:
+            o = int(torch.nonzero(bad)[0])
+            raise torch.linalg.LinAlgError(f'se_gp_factor: the covariance of output {o} is not positive definite '
+                                           f'(pivot of row {int(bad[o]) - 1})')
+        return diag
+
+    def _factor_native(self, x: Tensor, hyp: Tensor) -> Tuple[Tensor, int]:
+        """W = L^-1 on the device through `se_gp_factor`, padded to a multiple of 128 rows.  When the previous factor was
+        built on a prefix of `x` with the same hyper-parameters (update_model(replace_old=False), ssm_cem.py:72-99; the
+        idea of ssm_pytorch/utilities.py:122-165), the block rows that lie entirely inside the old training set are kept
+        and only the later ones are computed: O((n - n_kept) n^2) instead of O(n^3).  -> (W_pad, first block row computed)"""
+        n = x.size(0)
+        n_pad = -(-n // 128) * 128
+        first_block = 0
+        w_pad = torch.zeros((self.num_states, n_pad, n_pad), dtype=torch.float64, device=x.device)
+        wt_pad = torch.zeros_like(w_pad)
+        prev = self._factor_pad if self._incremental else None
+        if prev is not None:
+            x_old, w_old, wt_old, hyp_old = prev
+            n_old = x_old.size(0)
+            if (n_old < n and hyp_old.shape == hyp.shape and torch.equal(hyp_old, hyp) and
+                    torch.equal(x[:n_old], x_old)):
+                first_block = n_old // 128  # the old factor's last, partly padded block row is recomputed
+                keep = first_block * 128
+                w_pad[:, :keep, :keep] = w_old[:, :keep, :keep]
+                wt_pad[:, :keep, :keep] = wt_old[:, :keep, :keep]
+        k_pad = self._padded_covariance(x, n_pad)
+        self._run_factor(k_pad, w_pad, wt_pad, first_block)
+        del k_pad
+        self._factor_pad = (x, w_pad, wt_pad, hyp) if self._incremental else None
+        return w_pad, first_block
 
     def _append_rows(self, x: Tensor, hyp: Tensor) -> Optional[Tensor]:
         """Incremental factor update (the idea of ssm_pytorch/utilities.py:122-165 `update_cholesky`):
@@ -305,17 +373,33 @@ class B200GpCemSSM(CemSSM):
                        self.outputscale if outputscale is None else outputscale,
                        self.noise if noise is None else noise)
         keep, (p_ls, p_os, p_nz) = self._hyp_ptrs(ls, os_, nz)
-        k = self.kernel_matrix(x, ls, os_, nz)
-        chol = torch.linalg.cholesky(k)
-        del k
-        logdet_half = chol.diagonal(dim1=1, dim2=2).log().sum(-1)
-        # K^-1 = L^-T L^-1 from one triangular solve and one DGEMM (potri is 3x slower at n = 2000 .. 5000)
-        eye = torch.eye(n, dtype=torch.float64, device=x.device).expand(self.num_states, -1, -1)
-        linv = torch.linalg.solve_triangular(chol, eye, upper=False)
-        del chol
-        kinv = torch.matmul(linv.transpose(1, 2), linv).contiguous()
-        alpha = torch.matmul(linv.transpose(1, 2), torch.matmul(linv, yt.unsqueeze(-1))).squeeze(-1).contiguous()
-        del linv
+        if self._factor_impl == 'native':
+            n_pad = -(-n // 128) * 128
+            k_pad = self._padded_covariance(x, n_pad, ls, os_, nz)
+            w_pad = torch.zeros_like(k_pad)
+            wt_pad = torch.zeros_like(k_pad)
+            diag = self._run_factor(k_pad, w_pad, wt_pad, 0)
+            logdet_half = diag[:, :n].log().sum(-1)
+            kinv_pad = k_pad  # reuse the buffer: se_gp_kinv writes the lower triangle, the gradient kernel reads only that
+            with torch.cuda.device(x.device):
+                _lib.check(self._lib.se_gp_kinv(self.num_states, n_pad, _lib.ptr(wt_pad), _lib.ptr(kinv_pad),
+                                                _lib.stream_ptr(x.device)))
+            linv = w_pad[:, :n, :n]
+            alpha = torch.matmul(linv.transpose(1, 2), torch.matmul(linv, yt.unsqueeze(-1))).squeeze(-1).contiguous()
+            kinv = kinv_pad[:, :n, :n].contiguous()
+            del w_pad, wt_pad, kinv_pad, k_pad, linv
+        else:
+            k = self.kernel_matrix(x, ls, os_, nz)
+            chol = torch.linalg.cholesky(k)
+            del k
+            logdet_half = chol.diagonal(dim1=1, dim2=2).log().sum(-1)
+            # K^-1 = L^-T L^-1 from one triangular solve and one DGEMM (potri is 3x slower at n = 2000 .. 5000)
+            eye = torch.eye(n, dtype=torch.float64, device=x.device).expand(self.num_states, -1, -1)
+            linv = torch.linalg.solve_triangular(chol, eye, upper=False)
+            del chol
+            kinv = torch.matmul(linv.transpose(1, 2), linv).contiguous()
+            alpha = torch.matmul(linv.transpose(1, 2), torch.matmul(linv, yt.unsqueeze(-1))).squeeze(-1).contiguous()
+            del linv
         mll = -0.5 * (yt * alpha).sum(-1) - logdet_half - 0.5 * n * math.log(2 * math.pi)
         ws = torch.empty(max(1, self._lib.se_gp_mll_grad_workspace(self.num_states, d, n) // 8), dtype=torch.float64,
                          device=x.device)

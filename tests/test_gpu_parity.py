@@ -56,7 +56,9 @@ def test_gp_predict_matches_golden_fp64(golden_onestep, tag, impl):
     assert rel_err(var.cpu(), g[f'{tag}_var']) < RTOL64
     assert rel_err(jac.cpu(), g[f'{tag}_jac'], 1e-3 * np.abs(g[f'{tag}_jac']).max()) < RTOL64
     m2, v2 = gp.predict_without_jacobians(G(g['p']), G(g['u']))
-    assert torch.allclose(m2, mean, rtol=1e-13, atol=1e-16) and torch.equal(v2, var)
+    # the two kernels contract alpha_i k_i differently (FMA or multiply + add): the means agree to rounding of a sum with
+    # ~1e3 cancellation (measured 9.5e-14 on the trained model), not to the bit
+    assert torch.allclose(m2, mean, rtol=1e-12, atol=1e-16) and torch.equal(v2, var)
     mr, vr = gp.predict_raw(torch.cat((G(g['p']), G(g['u'])), dim=1))  # [n_s, N] layout (gp_ssm_cem.py:90-94)
     assert mr.shape == (2, 34) and torch.equal(mr.t(), m2) and torch.equal(vr.t(), var)
 

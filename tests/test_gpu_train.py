@@ -153,3 +153,128 @@ def test_create_solver_end_to_end_matches_oracle(golden_cem):
         assert np.allclose(action, ref['rollouts'][-1].actions[ref['best_id'], 0].numpy(), rtol=1e-12)
     else:
         assert result == se.MpcResult.SAFE_CONTROLLER and np.allclose(action, safe_policy(g['p0']))
+
+
+# ---- on-device factor refresh (se_gp_factor / se_gp_kinv): SURVEY.md 8f rank 1 -----------------------------------------
+def _factor_through_cabi(k, first_block=0, w_old=None, wt_old=None):
+    """k [n_s, n, n] (device, float64) -> (W_pad, W^T_pad, diag, info) through the C ABI, identity on the padding."""
+    from safe_exploration_b200 import _lib
+    lib = _lib.load()
+    n_s, n = k.shape[0], k.shape[1]
+    n_pad = -(-n // 128) * 128
+    k_pad = torch.zeros((n_s, n_pad, n_pad), dtype=torch.float64, device=DEV)
+    k_pad[:, :n, :n] = k
+    k_pad.diagonal(dim1=1, dim2=2)[:, n:] = 1.0
+    w = torch.zeros_like(k_pad)
+    wt = torch.zeros_like(k_pad)
+    if w_old is not None:
+        keep = first_block * 128
+        w[:, :keep, :keep] = w_old[:, :keep, :keep]
+        wt[:, :keep, :keep] = wt_old[:, :keep, :keep]
+    diag = torch.ones((n_s, n_pad), dtype=torch.float64, device=DEV)
+    ws = torch.empty(lib.se_gp_factor_workspace(n_s, n_pad) // 8, dtype=torch.float64, device=DEV)
+    info = torch.zeros(n_s, dtype=torch.int32, device=DEV)
+    _lib.check(lib.se_gp_factor(n_s, n_pad, first_block, _lib.ptr(k_pad), _lib.ptr(w), _lib.ptr(wt), _lib.ptr(diag),
+                                _lib.ptr(ws), _lib.ptr(info), _lib.stream_ptr(DEV)))
+    torch.cuda.synchronize()
+    return w, wt, diag, info
+
+
+@pytest.mark.parametrize('n,n_s,n_u', [(1, 1, 1), (100, 2, 1), (128, 1, 1), (129, 2, 1), (300, 4, 1), (700, 2, 1), (1100, 3, 2)])
+def test_native_factor_matches_a_float64_cholesky(n, n_s, n_u):
+    """W = L^-1 from the blocked on-device factorisation against torch's float64 Cholesky + triangular solve ON THE CPU
+    (LAPACK): W L = I to 1e-9, W to 1e-9 of its largest entry per output (K has condition number ~ n s / noise = 1e5),
+    diag(L) to 1e-12, W^T the exact transpose, zeros above the diagonal, the identity on the padding."""
+    x, y, ls, os_, nz = problem(n, n_s, n_u, 500 + n)
+    gp = se.B200GpCemSSM(None, n_s, n_u, ls, os_, nz, device=DEV)
+    k = gp.kernel_matrix(x.to(DEV))
+    w, wt, diag, info = _factor_through_cabi(k)
+    assert int(info.abs().max()) == 0
+    chol = torch.linalg.cholesky(k.cpu())
+    ref = torch.linalg.solve_triangular(chol, torch.eye(n, dtype=torch.float64).expand(n_s, -1, -1), upper=False)
+    got = w[:, :n, :n].cpu()
+    assert float((got - ref).abs().amax(dim=(1, 2)).div(ref.abs().amax(dim=(1, 2))).max()) < 1e-9
+    eye_err = torch.matmul(got, chol) - torch.eye(n, dtype=torch.float64)
+    assert float(eye_err.abs().max()) < 1e-9
+    assert float((diag[:, :n].cpu() / chol.diagonal(dim1=1, dim2=2) - 1).abs().max()) < 1e-12
+    assert torch.equal(wt, w.transpose(1, 2))
+    assert float(torch.triu(w, diagonal=1).abs().max()) == 0.0
+    n_pad = w.shape[1]
+    if n_pad > n:
+        pad = w[:, n:, :]
+        assert torch.equal(pad[:, :, n:], torch.eye(n_pad - n, dtype=torch.float64, device=DEV).expand(n_s, -1, -1))
+        assert float(pad[:, :, :n].abs().max()) == 0.0
+
+
+def test_native_factor_extends_an_old_factor_block_row_by_block_row():
+    """update_model(replace_old=False) (ssm_cem.py:72-99): passing the first block row that changed reproduces the
+    factor of the grown training set -- bit for bit, since every block row is computed from the rows above it by the same
+    kernels in the same order."""
+    x, y, ls, os_, nz = problem(700, 2, 1, 77)
+    gp = se.B200GpCemSSM(None, 2, 1, ls, os_, nz, device=DEV)
+    k_all = gp.kernel_matrix(x.to(DEV))
+    w_full, wt_full, diag_full, _ = _factor_through_cabi(k_all)
+    for n_old in (128, 300, 650):
+        w_old, wt_old, _, _ = _factor_through_cabi(k_all[:, :n_old, :n_old].contiguous())
+        fb = n_old // 128
+        big_w = torch.zeros_like(w_full)
+        big_wt = torch.zeros_like(w_full)
+        big_w[:, :w_old.shape[1], :w_old.shape[1]] = w_old
+        big_wt[:, :w_old.shape[1], :w_old.shape[1]] = wt_old
+        w_inc, wt_inc, diag_inc, info = _factor_through_cabi(k_all, first_block=fb, w_old=big_w, wt_old=big_wt)
+        assert int(info.abs().max()) == 0
+        assert torch.equal(w_inc, w_full) and torch.equal(wt_inc, wt_full)
+        assert torch.equal(diag_inc[:, fb * 128:], diag_full[:, fb * 128:])
+
+
+def test_native_inverse_covariance_matches_float64_and_feeds_the_gradient():
+    from safe_exploration_b200 import _lib
+    lib = _lib.load()
+    n, n_s = 450, 3
+    x, y, ls, os_, nz = problem(n, n_s, 1, 901)
+    gp = se.B200GpCemSSM(None, n_s, 1, ls, os_, nz, device=DEV)
+    k = gp.kernel_matrix(x.to(DEV))
+    w, wt, _, _ = _factor_through_cabi(k)
+    n_pad = w.shape[1]
+    kinv = torch.full((n_s, n_pad, n_pad), float('nan'), dtype=torch.float64, device=DEV)
+    _lib.check(lib.se_gp_kinv(n_s, n_pad, _lib.ptr(wt), _lib.ptr(kinv), _lib.stream_ptr(DEV)))
+    torch.cuda.synchronize()
+    ref = torch.linalg.inv(k.cpu())
+    got = torch.tril(kinv[:, :n, :n]).cpu()
+    assert torch.isfinite(got).all()
+    assert float((got - torch.tril(ref)).abs().amax(dim=(1, 2)).div(ref.abs().amax(dim=(1, 2))).max()) < 1e-9
+    # the same model through both factor engines: marginal likelihood and gradient agree
+    a = se.B200GpCemSSM(None, n_s, 1, ls, os_, nz, device=DEV, factor_impl='native').mll_and_grad(x.to(DEV), y.to(DEV))
+    b = se.B200GpCemSSM(None, n_s, 1, ls, os_, nz, device=DEV, factor_impl='cusolver').mll_and_grad(x.to(DEV), y.to(DEV))
+    assert float(((a[0] - b[0]).abs() / b[0].abs()).max()) < 1e-10
+    scale = b[1].abs().amax(dim=1, keepdim=True)
+    assert float(((a[1] - b[1]).abs() / scale).max()) < 1e-8
+
+
+def test_native_factor_reports_a_matrix_that_is_not_positive_definite():
+    k = torch.eye(200, dtype=torch.float64, device=DEV).unsqueeze(0).repeat(2, 1, 1)
+    k[1, 150, 150] = -1.0
+    _, _, _, info = _factor_through_cabi(k)
+    assert info.cpu().tolist() == [0, 151]
+    gp = se.B200GpCemSSM(None, 2, 1, device=DEV)
+    k_pad = torch.eye(256, dtype=torch.float64, device=DEV).unsqueeze(0).repeat(2, 1, 1)
+    k_pad[1, 150, 150] = -1.0
+    with pytest.raises(torch.linalg.LinAlgError, match='output 1'):  # the host wrapper raises like torch.linalg.cholesky
+        gp._run_factor(k_pad, torch.zeros_like(k_pad), torch.zeros_like(k_pad), 0)
+
+
+def test_update_model_engines_agree_and_append_reuses_block_rows():
+    """The whole `update_model` through both factor engines: predictions agree to 1e-9 / 1e-8 (variance), and an append
+    reports the incremental path."""
+    x, y, ls, os_, nz = problem(900, 2, 1, 31)
+    z = torch.rand((257, 3), dtype=torch.float64, device=DEV) * 2 - 1
+    out = {}
+    for impl in ('native', 'cusolver'):
+        gp = se.B200GpCemSSM(None, 2, 1, ls, os_, nz, device=DEV, factor_impl=impl)
+        gp.update_model(x[:500].to(DEV), y[:500].to(DEV), replace_old=True)
+        assert gp.last_update == 'full'
+        gp.update_model(x[500:].to(DEV), y[500:].to(DEV))
+        assert gp.last_update == 'incremental'
+        out[impl] = gp.predict_with_jacobians(z[:, :2].contiguous(), z[:, 2:].contiguous())
+    for a, b, tol in zip(out['native'], out['cusolver'], (1e-9, 1e-8, 1e-9)):
+        assert float((a - b).abs().max() / b.abs().max()) < tol

@@ -21,6 +21,28 @@ for name in sys.argv[1:] or ['C2', 'C3']:
     gp = se.B200GpCemSSM(None, n_s, d - n_s, w.lengthscale, w.outputscale, w.noise, device='cuda:0', incremental=False)
     rec = {'config': name, 'n': n, 'n_s': n_s}
     rec['update_model_ms'] = ms(lambda: gp.update_model(x, y, replace_old=True))
+    gc = se.B200GpCemSSM(None, n_s, d - n_s, w.lengthscale, w.outputscale, w.noise, device='cuda:0', incremental=False,
+                         factor_impl='cusolver')
+    rec['update_model_cusolver_ms'] = ms(lambda: gc.update_model(x, y, replace_old=True))
+    rec['train_iteration_native_ms'] = ms(lambda: gp.mll_and_grad(x, y))
+    rec['train_iteration_cusolver_ms'] = ms(lambda: gc.mll_and_grad(x, y))
+    n_pad = -(-n // 128) * 128
+    k_pad = gp._padded_covariance(x, n_pad)
+    w_pad = torch.zeros_like(k_pad); wt_pad = torch.zeros_like(k_pad)
+    def fac():
+        w_pad.zero_(); wt_pad.zero_()
+        gp._run_factor(k_pad, w_pad, wt_pad, 0)
+    rec['se_gp_factor_ms (incl. zeroing W, W^T)'] = ms(fac)
+    del k_pad, w_pad, wt_pad
+    gi = se.B200GpCemSSM(None, n_s, d - n_s, w.lengthscale, w.outputscale, w.noise, device='cuda:0', incremental=True)
+    def append():
+        gi.update_model(x[: n - 100], y[: n - 100], replace_old=True)
+    append(); torch.cuda.synchronize()
+    t_base = ms(append)
+    def append2():
+        gi.update_model(x[: n - 100], y[: n - 100], replace_old=True)
+        gi.update_model(x[n - 100:], y[n - 100:])
+    rec['append_100_rows_ms'] = ms(append2) - t_base
     k = gp.kernel_matrix(x)
     rec['kernel_matrix_ms'] = ms(lambda: gp.kernel_matrix(x))
     rec['cholesky_ms'] = ms(lambda: torch.linalg.cholesky(k))
