@@ -97,9 +97,9 @@ int se_gp_predict(se_gp_t gp, const void* dev_z, int64_t N, void* dev_mean, void
 /* ---------------------------------------------------------------------------------------------------------------
  * Model refresh: what happens between episodes in CemSafeMPC.update_model
  * (safe_exploration/safempc_cem.py:314-327) -> CemSSM.update_model (ssm_cem.py:72-99) -> GpCemSSM._update_model /
- * _train_model (gp_ssm_cem.py:96-129).  In the reference the arithmetic is GPyTorch's; here the covariance assembly and
- * the marginal-log-likelihood gradient are kernels of this library, the Cholesky factorisation / inverse between them
- * are cuSOLVER / cuBLAS calls made by the Python host through torch.linalg.  float64 only.
+ * _train_model (gp_ssm_cem.py:96-129).  In the reference the arithmetic is GPyTorch's; here the covariance assembly
+ * (se_gp_kernel_matrix), the factorisation / inverse factor (se_gp_factor), the inverse covariance (se_gp_kinv) and the
+ * marginal-log-likelihood gradient (se_gp_mll_grad) are all kernels of this library.  float64 only.
  * ------------------------------------------------------------------------------------------------------------- */
 
 /* dev_k [n_s, n, n] = outputscale_o exp(-1/2 sum_c ((x_ic - x_jc) / lengthscale_oc)^2) + noise_o [i == j]: the
