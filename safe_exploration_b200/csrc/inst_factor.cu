@@ -15,26 +15,31 @@ static int launch_gemm_nt(const fac::GemmNT& p, int batch, cudaStream_t st) {
 }
 
 // The Schur complement + small Cholesky of a block row (a few CTAs, latency-bound) run on a side stream beside the
-// T^T product (throughput-bound) -- both only need L21.  One side stream and two events per device, created on first use.
-struct FactorStreams {
-  cudaStream_t side = nullptr;
-  cudaEvent_t ev_l21 = nullptr, ev_chol = nullptr;
-};
-static int factor_streams(FactorStreams** out) {
+// T^T product (throughput-bound) -- both only need L21.  One side stream per device, created on first use; the two events
+// that order it against the caller's stream belong to the call (concurrent calls on one device must not share them).
+static int factor_side_stream(cudaStream_t* out) {
   static std::mutex mu;
-  static std::map<int, FactorStreams> per_device;
+  static std::map<int, cudaStream_t> per_device;
   int dev = 0;
   SE_CUDA(cudaGetDevice(&dev));
   std::lock_guard<std::mutex> lock(mu);
-  FactorStreams& fs = per_device[dev];
-  if (!fs.side) {
-    SE_CUDA(cudaStreamCreateWithFlags(&fs.side, cudaStreamNonBlocking));
-    SE_CUDA(cudaEventCreateWithFlags(&fs.ev_l21, cudaEventDisableTiming));
-    SE_CUDA(cudaEventCreateWithFlags(&fs.ev_chol, cudaEventDisableTiming));
-  }
-  *out = &fs;
+  cudaStream_t& s = per_device[dev];
+  if (!s) SE_CUDA(cudaStreamCreateWithFlags(&s, cudaStreamNonBlocking));
+  *out = s;
   return 0;
 }
+struct FactorEvents {
+  cudaEvent_t ev_l21 = nullptr, ev_chol = nullptr;
+  int create() {
+    SE_CUDA(cudaEventCreateWithFlags(&ev_l21, cudaEventDisableTiming));
+    SE_CUDA(cudaEventCreateWithFlags(&ev_chol, cudaEventDisableTiming));
+    return 0;
+  }
+  ~FactorEvents() {  // destroying a recorded event is allowed: its resources go when the work has passed it
+    if (ev_l21) cudaEventDestroy(ev_l21);
+    if (ev_chol) cudaEventDestroy(ev_chol);
+  }
+};
 
 }  // namespace se
 
@@ -61,8 +66,10 @@ extern "C" int se_gp_factor(int n_s, int64_t n_pad, int first_block, const doubl
   double* part = l21 + (int64_t)n_s * fac::FB * n_pad;           // [n_s][kMaxSplits][FB * FB]
   double* tt = part + (int64_t)n_s * fac::kMaxSplits * fac::FB * fac::FB;  // [n_s][n_pad][FB]
   SE_TRY(set_max_dyn_smem(fac::chol_inv_block_kernel, fac::kCholSmemBytes));
-  FactorStreams* fs = nullptr;
-  SE_TRY(factor_streams(&fs));
+  cudaStream_t side = nullptr;
+  FactorEvents ev;
+  SE_TRY(factor_side_stream(&side));
+  SE_TRY(ev.create());
   static const int overlap = getenv("SE_FACTOR_OVERLAP") ? atoi(getenv("SE_FACTOR_OVERLAP")) : 1;
   for (int b = first_block; b < blocks; ++b) {
     const int n1 = b * fac::FB;
@@ -77,9 +84,9 @@ extern "C" int se_gp_factor(int n_s, int64_t n_pad, int first_block, const doubl
       g.alpha = 1.0, g.m_tiles = fac::FB / fac::Cfg::BM, g.n_tiles = b, g.k = n1, g.kmode = fac::K_B_LOWER, g.splits = 1;
       SE_TRY(launch_gemm_nt(g, n_s, st));
       if (overlap) {
-        SE_CUDA(cudaEventRecord(fs->ev_l21, st));
-        SE_CUDA(cudaStreamWaitEvent(fs->side, fs->ev_l21, 0));
-        sc = fs->side;
+        SE_CUDA(cudaEventRecord(ev.ev_l21, st));
+        SE_CUDA(cudaStreamWaitEvent(side, ev.ev_l21, 0));
+        sc = side;
       }
       // split-K slices of L21 L21^T
       splits = n1 / 256 < 1 ? 1 : (n1 / 256 > fac::kMaxSplits ? fac::kMaxSplits : n1 / 256);
@@ -97,7 +104,7 @@ extern "C" int se_gp_factor(int n_s, int64_t n_pad, int first_block, const doubl
               dev_w + (int64_t)n1 * ld + n1, ld, mat, dev_wt + (int64_t)n1 * ld + n1, ld, mat, dev_diag + n1, n_pad, n1,
               dev_info);
     if (n1 > 0) {
-      if (sc != st) SE_CUDA(cudaEventRecord(fs->ev_chol, sc));
+      if (sc != st) SE_CUDA(cudaEventRecord(ev.ev_chol, sc));
       // T^T = W11^T L21^T
       fac::GemmNT t{};
       t.a = dev_wt, t.lda = ld, t.a_batch = mat;
@@ -105,7 +112,7 @@ extern "C" int se_gp_factor(int n_s, int64_t n_pad, int first_block, const doubl
       t.c = tt, t.ldc = fac::FB, t.c_batch = n_pad * fac::FB, t.c_split = 0;
       t.alpha = 1.0, t.m_tiles = n1 / fac::Cfg::BM, t.n_tiles = 1, t.k = n1, t.kmode = fac::K_A_UPPER, t.splits = 1;
       SE_TRY(launch_gemm_nt(t, n_s, st));
-      if (sc != st) SE_CUDA(cudaStreamWaitEvent(st, fs->ev_chol, 0));
+      if (sc != st) SE_CUDA(cudaStreamWaitEvent(st, ev.ev_chol, 0));
       // W21^T = -T^T W22^T -> new columns of W^T, new rows of W
       fac::GemmNT u{};
       u.a = tt, u.lda = fac::FB, u.a_batch = n_pad * fac::FB;

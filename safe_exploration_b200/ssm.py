@@ -120,8 +120,9 @@ class B200GpCemSSM(CemSSM):
                   on the tensor cores).  For float32-class tolerance at higher speed keep float64 and pass tc_digits=4
     :param tc_digits: digit planes of the tensor-core variance GEMM: 0 = float64-class, chosen from outputscale/noise
                   (never fewer than 6); 7 / 8 = float64-equivalent; 4 / 3 = float32 tolerance (see set_tc_digits)
-    :param incremental: keep the float64 inverse Cholesky factor on the device (n_s n^2 doubles) so that
-                        `update_model(..., replace_old=False)` only computes the rows of the appended samples
+    :param incremental: keep the float64 inverse Cholesky factor on the device (W and W^T, 2 n_s n_pad^2 doubles with
+                        the native factor engine) so that `update_model(..., replace_old=False)` only computes the block
+                        rows that the appended samples touch
     :param factor_impl: 'native' (default): L^-1 and (K + noise I)^-1 come from this library's blocked factorisation
                         (`se_gp_factor`, `se_gp_kinv`: FP64 DMMA products, no cuSOLVER / cuBLAS), which also extends a
                         factor whose training set only grew; 'cusolver': the round-1 path through torch.linalg
