@@ -86,6 +86,10 @@ int launch_kstar_slices_opt1_s6(const GpDev<double>& gp, const double* p, int64_
                                 cudaStream_t stream);
 int launch_trisumsq_ozaki(const int8_t* a_img, const int8_t* b_img, const double* scale_b, int n, int n_pad,
                           int rows_pad, int ns, int S, double* partial, int sm_count, int* nb_out, cudaStream_t stream);
+struct TriOrder;
+int launch_trisumsq_ozaki_cluster(int S, int shape, const int8_t* a_img, const int8_t* b_img, const double* scale_b,
+                                  int n, int n_pad, int rows_pad, const TriOrder& od, int sm_count, double* partial,
+                                  cudaStream_t stream);
 int launch_oz_probe(const int8_t* a_img, const int8_t* b_img, int nk, int S, int lbo, int sbo, int32_t* out,
                     cudaStream_t stream);
 int launch_debug_exp(const double* x, int64_t n, double* out, int table, cudaStream_t stream);
