@@ -18,6 +18,8 @@ from .cem import ActionConstraint, B200ConstrainedCemMpc, Constraint, DynamicsFu
 from .reachability import SafeProblem, is_ellipsoid_inside_polytope, multistep_reachability, onestep_reachability
 from .ssm import B200GpCemSSM, CemSSM, assert_shape
 
+STATE_PENALTY = 10  # per ellipsoid outside its polytope (safempc_cem.py:132)
+
 
 class MpcResult(Enum):
     """safempc_cem.py:23-27."""
@@ -59,24 +61,34 @@ class PQFlattener:
         self._state_dimen = state_dimen
 
     def flatten(self, p: Tensor, q: Optional[Tensor]) -> Tensor:
-        N = p.size(0)
+        """(p [N, n_s], q [N, n_s, n_s] | None) -> [N, n_s + n_s^2]; a missing q is written as zeros (point states)."""
+        n, count = self._state_dimen, p.size(0)
+        assert_shape(p, (count, n))
         if q is None:
-            q = torch.zeros((N, self._state_dimen, self._state_dimen), dtype=p.dtype, device=p.device)
-        assert_shape(p, (N, self._state_dimen,))
-        assert_shape(q, (N, self._state_dimen, self._state_dimen))
-        return torch.cat((p.reshape(N, -1), q.reshape(N, -1)), dim=1)
+            return torch.cat((p, p.new_zeros((count, n * n))), dim=1)
+        assert_shape(q, (count, n, n))
+        return torch.cat((p, q.reshape(count, n * n)), dim=1)
 
     def unflatten(self, flat: Tensor) -> Tuple[Tensor, Optional[Tensor]]:
-        N = flat.size(0)
-        assert_shape(flat, (N, self.get_flat_state_dimen(),))
-        p = flat[:, 0:self._state_dimen]
-        q = flat[:, self._state_dimen:].reshape(N, self._state_dimen, self._state_dimen)
-        if not bool((q != 0).any()):
-            q = None
-        return p, q
+        """Inverse of `flatten`; q is None when every shape matrix of the batch is exactly zero."""
+        n, count = self._state_dimen, flat.size(0)
+        assert_shape(flat, (count, self.get_flat_state_dimen()))
+        p, q_flat = flat[:, :n], flat[:, n:]
+        return p, (q_flat.reshape(count, n, n) if bool(q_flat.ne(0).any()) else None)
 
     def get_flat_state_dimen(self):
-        return self._state_dimen + (self._state_dimen * self._state_dimen)
+        n = self._state_dimen
+        return n * (n + 1)
+
+
+def _outside_cost(flattener: 'PQFlattener', states: Tensor, polytope_a: Tensor, polytope_b: Tensor):
+    """STATE_PENALTY for every ellipsoid of `states` [K, n_s + n_s^2] that is not inside the polytope
+    (safempc_cem.py:127-132)."""
+    if states.shape[0] == 0:
+        return 0
+    p, q = flattener.unflatten(states)
+    inside = is_ellipsoid_inside_polytope(p, q, polytope_a.to(p), polytope_b.to(p))
+    return (~inside.bool()).sum() * STATE_PENALTY
 
 
 class EllipsoidStateConstraint(Constraint):
@@ -91,10 +103,8 @@ class EllipsoidStateConstraint(Constraint):
         self.all_states = all_states
 
     def __call__(self, trajectory, actions) -> float:
-        states = trajectory[1:] if self.all_states else trajectory[-1:]
-        p, q = self._pq_flattener.unflatten(states)
-        inside = is_ellipsoid_inside_polytope(p, q, self._polytope_a.to(p), self._polytope_b.to(p))
-        return (inside.size(0) - inside.sum()) * 10
+        checked = trajectory[1:] if self.all_states else trajectory[-1:]
+        return _outside_cost(self._pq_flattener, checked, self._polytope_a, self._polytope_b)
 
     def batch_call(self, trajectories: Tensor, actions: Tensor) -> Tensor:
         """All rollouts at once (interface path of B200ConstrainedCemMpc): trajectories [N, T+1, S] -> costs [N]."""
@@ -111,7 +121,7 @@ class EllipsoidTerminalConstraint(Constraint):
         self._polytope_b = self._constraint._polytope_b
 
     def __call__(self, trajectory, actions) -> float:
-        return self._constraint(trajectory[-1:, :], actions[-1:, :])
+        return self._constraint(trajectory[-1:], actions[-1:])  # the wrapped constraint looks at the last slot
 
     def batch_call(self, trajectories: Tensor, actions: Tensor) -> Tensor:
         return self._constraint.batch_call(trajectories, actions)
@@ -131,12 +141,8 @@ class EllipsoidObstacleConstraint(Constraint):
                                            device=device).reshape(-1, 1)
 
     def __call__(self, trajectory, actions) -> float:
-        states = trajectory[1:-1]  # slot 0 is the (point) initial state, the last slot the terminal ellipsoid
-        if states.shape[0] == 0:
-            return 0
-        p, q = self._pq_flattener.unflatten(states)
-        inside = is_ellipsoid_inside_polytope(p, q, self._polytope_a.to(p), self._polytope_b.to(p))
-        return (inside.size(0) - inside.sum()) * 10
+        # slot 0 is the (point) initial state, the last slot the terminal ellipsoid
+        return _outside_cost(self._pq_flattener, trajectory[1:-1], self._polytope_a, self._polytope_b)
 
     def batch_call(self, trajectories: Tensor, actions: Tensor) -> Tensor:
         if trajectories.shape[1] <= 2:
@@ -152,7 +158,7 @@ def _batch_inside_cost(flattener: PQFlattener, states: Tensor, polytope_a: Tenso
     p = flat[:, :n_s].contiguous()
     q = flat[:, n_s:].reshape(N * K, n_s, n_s).contiguous()
     inside = is_ellipsoid_inside_polytope(p, q, polytope_a.to(p), polytope_b.to(p)).reshape(N, K)
-    return 10.0 * (K - inside.sum(dim=1)).to(states.dtype)
+    return float(STATE_PENALTY) * (K - inside.sum(dim=1)).to(states.dtype)
 
 
 def construct_constraints(conf, env) -> List[Constraint]:
@@ -443,22 +449,23 @@ class B200CemSafeMPC(SafeMPC):
                                        device=getattr(self._ssm, 'device', 'cuda:0')).unsqueeze(0)
             mpc_actions, _ = self._mpc.get_actions(self._pq_flattener.flatten(state_batch, None), reuse_outputs=True)
             mpc_actions = mpc_actions.detach().cpu().numpy() if mpc_actions is not None else mpc_actions
-        if mpc_actions is not None:
-            self._say('Found solution')
-            action = mpc_actions[0]
-            self._last_mpc_actions = mpc_actions
-            self._mpc_actions_executed = 1
-            result = MpcResult.FOUND_SOLUTION
-        elif self._mpc_actions_executed < self._last_mpc_actions.shape[0]:
-            self._say('Using existing solution')
-            action = self._last_mpc_actions[self._mpc_actions_executed]
-            self._mpc_actions_executed += 1
-            result = MpcResult.PREVIOUS_SOLUTION
-        else:
-            self._say('Using safe controller')
-            action = self._safe_policy(state)
-            result = MpcResult.SAFE_CONTROLLER
+        action, result = self._follow_plan(mpc_actions, state)
         return action, result
+
+    def _follow_plan(self, plan: Optional[ndarray], state: ndarray) -> Tuple[ndarray, MpcResult]:
+        """The fall-back chain of safempc_cem.py:243-263: a fresh plan is adopted and its first action returned; without
+        one the stored plan is followed one more step; when that is used up the safe policy takes over."""
+        if plan is not None:
+            self._say('Found solution')
+            self._last_mpc_actions, self._mpc_actions_executed = plan, 1
+            return plan[0], MpcResult.FOUND_SOLUTION
+        step = self._mpc_actions_executed
+        if step < self._last_mpc_actions.shape[0]:
+            self._say('Using existing solution')
+            self._mpc_actions_executed = step + 1
+            return self._last_mpc_actions[step], MpcResult.PREVIOUS_SOLUTION
+        self._say('Using safe controller')
+        return self._safe_policy(state), MpcResult.SAFE_CONTROLLER
 
     def get_action_batch(self, states: ndarray) -> Tuple[ndarray, List[MpcResult]]:
         """M scenarios side by side: what episode_runner.do_rollout (episode_runner.py:206-231) does when it calls

@@ -56,20 +56,18 @@ class CemSSM(ABC):
         """Predict from stacked [state | action] inputs."""
 
     def update_model(self, train_x: Tensor, train_y: Tensor, opt_hyp=False, replace_old=False) -> None:
-        """ssm_cem.py:72-99: replace or append the training data, rebuild the model, optionally train."""
-        N = train_x.size(0)
-        assert_shape(train_x, (N, self.num_states + self.num_actions))
-        assert_shape(train_y, (N, self.num_states))
-        if replace_old or self._x_train is None or self._y_train is None:
-            x_new, y_new = train_x, train_y
-        else:
-            x_new = torch.cat((self._x_train, train_x), dim=0)
-            y_new = torch.cat((self._y_train, train_y), dim=0)
-        self._x_train = x_new
-        self._y_train = y_new
-        self._update_model(x_new, y_new)
-        if self.parametric or opt_hyp:
-            self._train_model(x_new, y_new)
+        """Contract of ssm_cem.py:72-99: the new samples replace the stored training set (`replace_old`, or nothing stored
+        yet) or are appended to it; the model is rebuilt on the result and, for parametric models or on request
+        (`opt_hyp`), trained."""
+        rows = train_x.size(0)
+        assert_shape(train_x, (rows, self.num_states + self.num_actions))
+        assert_shape(train_y, (rows, self.num_states))
+        keep_old = not replace_old and self._x_train is not None and self._y_train is not None
+        self._x_train = torch.cat((self._x_train, train_x), dim=0) if keep_old else train_x
+        self._y_train = torch.cat((self._y_train, train_y), dim=0) if keep_old else train_y
+        self._update_model(self._x_train, self._y_train)
+        if opt_hyp or self.parametric:
+            self._train_model(self._x_train, self._y_train)
 
     @abstractmethod
     def _update_model(self, x_train: Tensor, y_train: Tensor) -> None:
@@ -80,9 +78,9 @@ class CemSSM(ABC):
         pass
 
     def _join_states_actions(self, states: Tensor, actions: Tensor) -> Tensor:
-        N = states.size(0)
-        assert_shape(states, (N, self.num_states))
-        assert_shape(actions, (N, self.num_actions))
+        """z = [state | action] per row, after checking that both have the model's dimensions."""
+        assert_shape(states, (states.size(0), self.num_states))
+        assert_shape(actions, (states.size(0), self.num_actions))
         return torch.cat((states, actions), dim=1)
 
     @abstractmethod
