@@ -278,3 +278,25 @@ def test_update_model_engines_agree_and_append_reuses_block_rows():
         out[impl] = gp.predict_with_jacobians(z[:, :2].contiguous(), z[:, 2:].contiguous())
     for a, b, tol in zip(out['native'], out['cusolver'], (1e-9, 1e-8, 1e-9)):
         assert float((a - b).abs().max() / b.abs().max()) < tol
+
+
+def test_native_factor_properties_at_the_full_c3_model_size():
+    """BASELINE C3's model (cart-pole, n = 5000, n_s = 4: 40 block rows, the long DMMA products and the side stream at
+    their full size) checked through size-independent properties instead of a CPU factorisation: W K W^T = I and
+    W^T W K = I to 1e-8 (cond K ~ 1e6 here), W^T the exact transpose, 2 sum log diag L = log det K to 1e-10."""
+    w = workloads.cartpole_workload(num_rollouts=256)
+    x = torch.as_tensor(w.x_train, device=DEV)
+    n = x.shape[0]
+    gp = se.B200GpCemSSM(None, w.n_s, w.n_u, w.lengthscale, w.outputscale, w.noise, device=DEV)
+    k = gp.kernel_matrix(x)
+    w_pad, wt_pad, diag, info = _factor_through_cabi(k)
+    assert int(info.abs().max()) == 0
+    wm = w_pad[:, :n, :n]
+    assert torch.equal(wt_pad, w_pad.transpose(1, 2))
+    eye = torch.eye(n, dtype=torch.float64, device=DEV)
+    for o in range(w.n_s):
+        assert float((wm[o] @ k[o] @ wm[o].t() - eye).abs().max()) < 1e-8
+        assert float((wm[o].t() @ (wm[o] @ k[o]) - eye).abs().max()) < 1e-8
+    sign, logdet = torch.linalg.slogdet(k)
+    assert bool((sign > 0).all())
+    assert float(((2 * diag[:, :n].log().sum(-1) - logdet) / logdet.abs()).abs().max()) < 1e-10
