@@ -26,7 +26,7 @@ constexpr int kMaxSplits = 32;   // split-K slices of the FB x FB Schur compleme
 using Cfg = DmmaCfg<2, 4, 16, 3, 64, 2>;  // 64 x 128 tile, 256 threads, 2 CTAs / SM
 
 enum KMode {
-  K_FULL = 0,       // k in [0, K)  (or the blockIdx.z slice of it when splits > 1)
+  K_FULL = 0,       // k in [0, K)
   K_B_LOWER = 1,    // B rows are rows of a lower-triangular matrix: column tile jt needs k < (jt + 1) 128
   K_A_UPPER = 2,    // A rows are rows of an upper-triangular matrix: row tile it needs k >= 64 it
   K_SYM_LOWER = 3   // A = B = rows of an upper-triangular matrix, only tiles that touch the lower triangle:
@@ -46,7 +46,8 @@ struct GemmNT {
   int m_tiles, n_tiles;  // 64-row / 128-column tiles
   int k;                 // K extent, a multiple of 16
   int kmode;
-  int splits;
+  int splits;            // > 1: blockIdx.z takes an equal slice of every tile's K range and writes it to c + z c_split;
+                         // the slices are added in index order by sum_slices_kernel / chol_inv_block_kernel
 };
 
 // C = alpha A B^T on the tiles of one batch entry.  grid (m_tiles n_tiles, batch, splits).
@@ -67,9 +68,10 @@ static __global__ void __launch_bounds__(Cfg::THREADS, Cfg::MINB) dgemm_nt_kerne
     if (it * C::BM + C::BM - 1 < jt * C::BN) return;  // the tile lies above the diagonal
     k_lo = max(it * C::BM, jt * C::BN);
   }
-  if (p.splits > 1) {
-    const int per = ((p.k + p.splits - 1) / p.splits + C::BK - 1) / C::BK * C::BK;
-    k_lo = min(p.k, z * per), k_hi = min(p.k, k_lo + per);
+  if (p.splits > 1) {  // slice z of THIS tile's K range (slices past its end are empty and store zeros)
+    const int per = ((k_hi - k_lo + p.splits - 1) / p.splits + C::BK - 1) / C::BK * C::BK;
+    const int lo = min(k_hi, k_lo + z * per);
+    k_hi = min(k_hi, lo + per), k_lo = lo;
   }
   const int ktiles = (k_hi - k_lo) / C::BK;
   const double* a_base = p.a + o * p.a_batch + (int64_t)it * C::BM * p.lda + k_lo;
@@ -145,17 +147,42 @@ static __global__ void __launch_bounds__(Cfg::THREADS, Cfg::MINB) dgemm_nt_kerne
   }
 }
 
+// dst[o][r][c] = sum_z part[o][z][r][c] for a [rows x cols] block, slices added in index order (deterministic).
+static __global__ void sum_slices_kernel(const double* __restrict__ part, int splits, int64_t slice_stride,
+                                         int64_t part_batch, int64_t ld_part, int rows, int cols,
+                                         double* __restrict__ dst, int64_t ld_dst, int64_t dst_batch) {
+  const int64_t e = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  const int o = blockIdx.y;
+  if (e >= (int64_t)rows * (cols / 2)) return;
+  const int64_t r = e / (cols / 2), c = (e % (cols / 2)) * 2;
+  const double* src = part + o * part_batch + r * ld_part + c;
+  double2 acc = *reinterpret_cast<const double2*>(src);
+  for (int z = 1; z < splits; ++z) {
+    const double2 v = *reinterpret_cast<const double2*>(src + z * slice_stride);
+    acc.x += v.x, acc.y += v.y;
+  }
+  *reinterpret_cast<double2*>(dst + o * dst_batch + r * ld_dst + c) = acc;
+}
+
 // packed lower triangle: element (i, k <= i)
 __device__ __forceinline__ int tri(int i, int k) { return i * (i + 1) / 2 + k; }
 constexpr int kTriDoubles = FB * (FB + 1) / 2;
 constexpr int kCholSmemBytes = 2 * kTriDoubles * (int)sizeof(double) + 16;
 
-// One CTA of 4 FB threads per output:  S = K22 - sum_z P_z (slices added in index order),  L22 = chol(S) (right-looking:
-// the four threads 4 i .. 4 i + 3 own row i and split its trailing update by k mod 4),  W22 = L22^-1 (forward
-// substitution in outer-product form, same ownership).  Writes the FB x FB block of W (lower triangle,
-// zeros above) and of W^T, and the diagonal of L22.  A non-positive pivot sets info[o] = 1 + its global row index (first
-// failure wins) and poisons the block with NaN, like a failed potrf.  All loads / stores of the block are spread over the
-// 512 threads with independent addresses (a row-at-a-time loop is a chain of ~1 us global round trips).
+// One CTA of 4 FB threads per output:  S = K22 - sum_z P_z (slices added in index order),  L22 = chol(S),  W22 = L22^-1.
+// Writes the FB x FB block of W (lower triangle, zeros above) and of W^T, and the diagonal of L22.  A non-positive pivot
+// sets info[o] = 1 + its global row index (first failure wins) and poisons the block with NaN, like a failed potrf.
+//
+// Measured with clock64 on the first version of this kernel (two barriers per column, one thread evaluating sqrt and the
+// reciprocal, a barrier per substitution step): 247 k cycles for the Cholesky and 185 k for the inverse of ONE block --
+// block-wide barriers and the single-thread pivot were the time, not the arithmetic.  Hence:
+//  * Cholesky, right-looking on UNSCALED columns (an L D L^T sweep): with d_j the pivot, S[t][k] -= S[t][j] S[k][j] / d_j.
+//    Every thread takes 1 / d_j itself after ONE barrier per column; L = S diag(1 / sqrt d) is formed at the end.
+//    The four threads 4 t .. 4 t + 3 own row t and split its updates by k mod 4, four elements at a time with all loads
+//    before the stores (row and column entries live in the same array: the compiler orders every load behind the
+//    previous store otherwise).
+//  * Inverse, column-parallel forward substitution in outer-product form: the four threads of column c (one warp holds
+//    eight columns) carry x = e_c through k = c .. FB - 1: x_k is final, x_i -= L[i][k] x_k for i > k.  No block barrier.
 constexpr int kCholThreads = 4 * FB;
 static __global__ void __launch_bounds__(kCholThreads) chol_inv_block_kernel(
     const double* __restrict__ k22, int64_t ldk, int64_t k_batch, const double* __restrict__ part, int splits,
@@ -163,14 +190,15 @@ static __global__ void __launch_bounds__(kCholThreads) chol_inv_block_kernel(
     double* __restrict__ wt, int64_t ldwt, int64_t wt_batch, double* __restrict__ diag, int64_t diag_batch, int row0,
     int32_t* __restrict__ info) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
-  double* lp = reinterpret_cast<double*>(smem_raw);  // L22, packed
-  double* xp = lp + kTriDoubles;                      // W22, packed
+  double* lp = reinterpret_cast<double*>(smem_raw);  // S, then L22 (packed lower triangle)
+  double* xp = lp + kTriDoubles;                      // W22 (packed)
+  __shared__ double dsm[FB], rsm[FB];                 // diag(L22) and its reciprocal
   const int o = blockIdx.x, tid = threadIdx.x;
-  const int t = tid >> 2, sub = tid & 3;  // row (Cholesky) / column (inverse) and the quarter of its sums
+  const int t = tid >> 2, sub = tid & 3;  // row (Cholesky) / column (inverse) and the residue class of its updates
   k22 += o * k_batch;
   if (part) part += o * part_batch;
-  // eight elements per thread at a time, so that eight loads are in flight per round trip (the slices are subtracted in
-  // index order for every element: the result does not depend on the grouping)
+  // eight elements per thread and four slices at a time: 8 / 32 loads in flight per round trip (the slices are
+  // subtracted in index order for every element, so the result does not depend on the grouping)
   constexpr int kPerThread = FB * FB / kCholThreads, kGroup = 8;
 #pragma unroll 1
   for (int base = 0; base < kPerThread; base += kGroup) {
@@ -180,7 +208,19 @@ static __global__ void __launch_bounds__(kCholThreads) chol_inv_block_kernel(
       const int e = tid + kCholThreads * (base + u);
       v[u] = k22[(int64_t)(e / FB) * ldk + e % FB];
     }
-    for (int zz = 0; zz < splits; ++zz) {
+    int zz = 0;
+    for (; zz + 4 <= splits; zz += 4) {
+      double pz[4][kGroup];
+#pragma unroll
+      for (int q = 0; q < 4; ++q)
+#pragma unroll
+        for (int u = 0; u < kGroup; ++u) pz[q][u] = part[(zz + q) * part_split + tid + kCholThreads * (base + u)];
+#pragma unroll
+      for (int q = 0; q < 4; ++q)
+#pragma unroll
+        for (int u = 0; u < kGroup; ++u) v[u] -= pz[q][u];
+    }
+    for (; zz < splits; ++zz) {
 #pragma unroll
       for (int u = 0; u < kGroup; ++u) v[u] -= part[zz * part_split + tid + kCholThreads * (base + u)];
     }
@@ -191,54 +231,78 @@ static __global__ void __launch_bounds__(kCholThreads) chol_inv_block_kernel(
     }
   }
   __syncthreads();
-  // Right-looking Cholesky: column j is scaled by 1 / sqrt(pivot), then every row t > j subtracts its outer-product
-  // share from the trailing triangle (independent FMAs, no dot-product chains).  The pivot stays in lp[tri(j, j)]; the
-  // diagonal of L22 and its reciprocal go to dsm / rsm.  Two barriers per column.
-  // sqrt and the reciprocal are software routines on the FP64 pipe: ONE thread evaluates them per column -- the owner of
-  // the next pivot, right after its last update -- and publishes them through shared memory.
-  __shared__ double dsm[FB], rsm[FB];
-  auto publish_pivot = [&](int j, double piv) {
-    if (!(piv > 0.0)) {
-      atomicCAS(&info[o], 0, row0 + j + 1);
-      piv = __longlong_as_double(0x7ff8000000000000ll);
-    }
-    const double sd = sqrt(piv);
-    dsm[j] = sd, rsm[j] = 1.0 / sd;
-  };
-  if (tid == 0) publish_pivot(0, lp[tri(0, 0)]);
-  __syncthreads();
-  for (int j = 0; j < FB; ++j) {
-    if (t > j && sub == 0) lp[tri(t, j)] *= rsm[j];
-    __syncthreads();
+  for (int j = 0; j < FB - 1; ++j) {
+    const double piv = lp[tri(j, j)];
     if (t > j) {
-      const double ltj = lp[tri(t, j)];
+      const double f = -lp[tri(t, j)] * __drcp_rn(piv);  // the reciprocal intrinsic: a third of the instructions of a division
       double* row = lp + tri(t, 0);
-      for (int k = j + 1 + sub; k <= t; k += 4) row[k] = fma(-ltj, lp[tri(k, j)], row[k]);
-      if (t == j + 1 && sub == 0) publish_pivot(j + 1, row[j + 1]);  // this thread just finished the next pivot
+      int k = j + 1 + sub;
+      for (; k + 12 <= t; k += 16) {
+        const double c0 = lp[tri(k, j)], c1 = lp[tri(k + 4, j)], c2 = lp[tri(k + 8, j)], c3 = lp[tri(k + 12, j)];
+        const double r0 = row[k], r1 = row[k + 4], r2 = row[k + 8], r3 = row[k + 12];
+        row[k] = fma(f, c0, r0), row[k + 4] = fma(f, c1, r1);
+        row[k + 8] = fma(f, c2, r2), row[k + 12] = fma(f, c3, r3);
+      }
+      for (; k <= t; k += 4) row[k] = fma(f, lp[tri(k, j)], row[k]);
     }
     __syncthreads();
   }
-  // W22 = L22^-1 by forward substitution in outer-product form on B = I: after step k - 1 row k of B is final and
-  // X[k][:] = B[k][:] / L[k][k]; step k subtracts L[t][k] X[k][c] from every row t > k.  Rows are scaled when stored.
+  if (tid < FB) {
+    double piv = lp[tri(tid, tid)];
+    if (!(piv > 0.0)) piv = __longlong_as_double(0x7ff8000000000000ll);
+    const double r = rsqrt(piv);
+    double sd = piv * r;
+    sd = fma(fma(-sd, sd, piv), 0.5 * r, sd);
+    dsm[tid] = sd, rsm[tid] = r;
+  }
+  __syncthreads();
+  if (tid == 0) {  // first bad pivot in row order (a NaN pivot poisons everything after it)
+    for (int j = 0; j < FB; ++j)
+      if (!(dsm[j] == dsm[j])) {
+        atomicCAS(&info[o], 0, row0 + j + 1);
+        break;
+      }
+  }
   for (int e = tid; e < kTriDoubles; e += kCholThreads) xp[e] = 0.0;
-  __syncthreads();
-  if (tid < FB) xp[tri(tid, tid)] = 1.0;
-  __syncthreads();
-  for (int k = 0; k < FB - 1; ++k) {
-    if (t > k) {
-      const double f = -lp[tri(t, k)] * rsm[k];
-      const double* src = xp + tri(k, 0);
-      double* row = xp + tri(t, 0);
-      for (int c = sub; c <= k; c += 4) row[c] = fma(f, src[c], row[c]);
-    }
-    __syncthreads();
+  // L22 = S diag(1 / sqrt d): column j of the packed triangle times rsm[j]
+  for (int e = tid; e < FB * FB; e += kCholThreads) {
+    const int r = e / FB, c = e % FB;
+    if (c < r) lp[tri(r, c)] *= rsm[c];
   }
+  __syncthreads();
+  // W22 = L22^-1, column t (warp-synchronous: the four threads of a column sit in one warp, which holds 8 columns and
+  // starts at its first column so that __syncwarp is reached by all lanes)
+  {
+    const int c = t;
+    double* xc = xp;  // element (i, c) at tri(i, c)
+    for (int k = t & ~7; k < FB; ++k) {
+      double xk = 0.0;
+      if (k >= c) {
+        const double b = k == c ? 1.0 : xc[tri(k, c)];
+        xk = b * rsm[k];
+      }
+      __syncwarp();  // every lane has read x_k before lane `sub == 0` overwrites it with its final value
+      if (k >= c) {
+        if (sub == 0) xc[tri(k, c)] = xk;
+        int i = k + 1 + sub;
+        for (; i + 12 < FB; i += 16) {
+          const double l0 = lp[tri(i, k)], l1 = lp[tri(i + 4, k)], l2 = lp[tri(i + 8, k)], l3 = lp[tri(i + 12, k)];
+          const double x0 = xc[tri(i, c)], x1 = xc[tri(i + 4, c)], x2 = xc[tri(i + 8, c)], x3 = xc[tri(i + 12, c)];
+          xc[tri(i, c)] = fma(-l0, xk, x0), xc[tri(i + 4, c)] = fma(-l1, xk, x1);
+          xc[tri(i + 8, c)] = fma(-l2, xk, x2), xc[tri(i + 12, c)] = fma(-l3, xk, x3);
+        }
+        for (; i < FB; i += 4) xc[tri(i, c)] = fma(-lp[tri(i, k)], xk, xc[tri(i, c)]);
+      }
+      __syncwarp();  // the updates of step k are visible to the lane that reads x_{k+1}
+    }
+  }
+  __syncthreads();
   w += o * w_batch;
   wt += o * wt_batch;
   for (int e = tid; e < FB * FB; e += kCholThreads) {
     const int r = e / FB, c = e % FB;
-    w[(int64_t)r * ldw + c] = c <= r ? xp[tri(r, c)] * rsm[r] : 0.0;
-    wt[(int64_t)r * ldwt + c] = c >= r ? xp[tri(c, r)] * rsm[c] : 0.0;
+    w[(int64_t)r * ldw + c] = c <= r ? xp[tri(r, c)] : 0.0;
+    wt[(int64_t)r * ldwt + c] = c >= r ? xp[tri(c, r)] : 0.0;
   }
   if (tid < FB) diag[o * diag_batch + tid] = dsm[tid];
 }

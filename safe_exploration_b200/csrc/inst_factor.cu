@@ -41,13 +41,40 @@ struct FactorEvents {
   }
 };
 
+constexpr int kMaxProductSplits = 8;  // K slices of the two long products of a block row
+
+// C = sum of `splits` K slices of A B^T: the product writes its slices to `slices`, sum_slices_kernel adds them into g.c.
+// Few tiles (early block rows, small models) and tiles of very different depth (the K extent of a tile follows the
+// triangle) both leave SMs idle with one CTA per tile; equal slices of every tile give ~4 units per CTA slot.
+static int launch_gemm_nt_sliced(fac::GemmNT g, int batch, int rows, int cols, double* slices, int sm_count,
+                                 cudaStream_t st) {
+  static const int env = getenv("SE_FACTOR_SPLITS") ? atoi(getenv("SE_FACTOR_SPLITS")) : -1;  // -1: automatic, 1: off
+  const int64_t tiles = (int64_t)g.m_tiles * g.n_tiles * batch, slots = 2ll * sm_count;
+  int splits = env > 0 ? env : (int)((4 * slots + tiles - 1) / tiles);
+  if (splits > kMaxProductSplits) splits = kMaxProductSplits;
+  if (splits > g.k / 128) splits = g.k / 128 > 0 ? g.k / 128 : 1;  // at least 128 deep
+  if (splits <= 1) return launch_gemm_nt(g, batch, st);
+  fac::GemmNT s = g;
+  const int64_t elems = (int64_t)rows * g.ldc;  // one slice of one batch entry, laid out like the destination
+  s.c = slices, s.c_batch = (int64_t)kMaxProductSplits * elems, s.c_split = elems, s.ct = nullptr, s.splits = splits;
+  s.alpha = g.alpha;
+  SE_TRY(launch_gemm_nt(s, batch, st));
+  SE_REQUIRE(g.ct == nullptr, "sliced products do not write a transposed copy");
+  const int64_t work = (int64_t)rows * (cols / 2);
+  SE_LAUNCH(fac::sum_slices_kernel, dim3((unsigned)ceil_div(work, (int64_t)256), (unsigned)batch), 256, 0, st, slices,
+            splits, elems, (int64_t)kMaxProductSplits * elems, g.ldc, rows, cols, g.c, g.ldc, g.c_batch);
+  return 0;
+}
+
 }  // namespace se
 
 using namespace se;
 
-// doubles: L21 [n_s][FB][n_pad] | split-K slices [n_s][kMaxSplits][FB * FB] | T^T [n_s][n_pad][FB]
+// doubles: L21 [n_s][FB][n_pad] | split-K slices of the Schur complement [n_s][kMaxSplits][FB * FB] | T^T [n_s][n_pad][FB]
+// | K slices of the two long products [n_s][kMaxProductSplits][FB * n_pad]
 extern "C" int64_t se_gp_factor_workspace(int n_s, int64_t n_pad) {
-  return (int64_t)sizeof(double) * n_s * (2 * fac::FB * n_pad + (int64_t)fac::kMaxSplits * fac::FB * fac::FB);
+  return (int64_t)sizeof(double) * n_s *
+         ((2 + kMaxProductSplits) * fac::FB * n_pad + (int64_t)fac::kMaxSplits * fac::FB * fac::FB);
 }
 
 extern "C" int se_gp_factor(int n_s, int64_t n_pad, int first_block, const double* dev_k, double* dev_w,
@@ -65,6 +92,10 @@ extern "C" int se_gp_factor(int n_s, int64_t n_pad, int first_block, const doubl
   double* l21 = dev_workspace;                                   // [n_s][FB][n_pad]
   double* part = l21 + (int64_t)n_s * fac::FB * n_pad;           // [n_s][kMaxSplits][FB * FB]
   double* tt = part + (int64_t)n_s * fac::kMaxSplits * fac::FB * fac::FB;  // [n_s][n_pad][FB]
+  double* slices = tt + (int64_t)n_s * n_pad * fac::FB;  // [n_s][kMaxProductSplits][FB * n_pad]
+  int dev = 0, sm_count = 148;
+  SE_CUDA(cudaGetDevice(&dev));
+  SE_CUDA(cudaDeviceGetAttribute(&sm_count, cudaDevAttrMultiProcessorCount, dev));
   SE_TRY(set_max_dyn_smem(fac::chol_inv_block_kernel, fac::kCholSmemBytes));
   cudaStream_t side = nullptr;
   FactorEvents ev;
@@ -82,7 +113,7 @@ extern "C" int se_gp_factor(int n_s, int64_t n_pad, int first_block, const doubl
       g.b = dev_w, g.ldb = ld, g.b_batch = mat;
       g.c = l21, g.ldc = ld, g.c_batch = (int64_t)fac::FB * n_pad, g.c_split = 0;
       g.alpha = 1.0, g.m_tiles = fac::FB / fac::Cfg::BM, g.n_tiles = b, g.k = n1, g.kmode = fac::K_B_LOWER, g.splits = 1;
-      SE_TRY(launch_gemm_nt(g, n_s, st));
+      SE_TRY(launch_gemm_nt_sliced(g, n_s, fac::FB, n1, slices, sm_count, st));
       if (overlap) {
         SE_CUDA(cudaEventRecord(ev.ev_l21, st));
         SE_CUDA(cudaStreamWaitEvent(side, ev.ev_l21, 0));
@@ -111,7 +142,7 @@ extern "C" int se_gp_factor(int n_s, int64_t n_pad, int first_block, const doubl
       t.b = l21, t.ldb = ld, t.b_batch = (int64_t)fac::FB * n_pad;
       t.c = tt, t.ldc = fac::FB, t.c_batch = n_pad * fac::FB, t.c_split = 0;
       t.alpha = 1.0, t.m_tiles = n1 / fac::Cfg::BM, t.n_tiles = 1, t.k = n1, t.kmode = fac::K_A_UPPER, t.splits = 1;
-      SE_TRY(launch_gemm_nt(t, n_s, st));
+      SE_TRY(launch_gemm_nt_sliced(t, n_s, n1, fac::FB, slices, sm_count, st));
       if (sc != st) SE_CUDA(cudaStreamWaitEvent(st, ev.ev_chol, 0));
       // W21^T = -T^T W22^T -> new columns of W^T, new rows of W
       fac::GemmNT u{};
