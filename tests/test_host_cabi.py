@@ -359,3 +359,22 @@ def test_general_eigenvalue_routine_matches_lapack():
         assert abs(got - ev.real.max()) <= 1e-9 * np.abs(ev).max(), (trial, n, got, ev)
     assert checked > 2000
     assert np.isnan(eig_max(np.array([[0., 1., 0.], [-1., 0., 0.], [0., 0., -5.]])))  # rotation block: +-i
+
+
+def test_committed_traffic_capture_names_the_kernel_the_bench_line_reports():
+    """bench.py takes `roofline.traffic` from profiles/ncu_traffic.json and refuses a capture of another kernel: the
+    committed capture must be of the kernel the default C2 run launches (the 2-CTA cluster flavour of the variance GEMM),
+    on the default workload, with more DRAM bytes than the algorithmic 417 MB and less than twice that."""
+    import importlib.util
+    import json
+    spec = importlib.util.spec_from_file_location('bench_module', os.path.join(ROOT, 'bench.py'))
+    bench = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(bench)
+    name = bench._gemm_kernel_name(6, 16384)
+    assert name == 'oz::gp_trisumsq_ozaki_cluster_kernel<6,1,2>'
+    assert bench._gemm_kernel_name(6, 128) == 'oz::gp_trisumsq_ozaki_kernel<6,2>'  # one candidate tile: no pairs
+    traffic, stamp = bench.profiled_traffic(name, 'C2/N16384')
+    assert stamp is not None and stamp.get('kernel') == name, stamp
+    assert 417e6 < traffic < 2 * 417e6
+    with open(os.path.join(ROOT, 'profiles', 'ncu_traffic.json')) as f:
+        assert all(os.path.exists(os.path.join(ROOT, e['source'])) for e in json.load(f))
