@@ -12,5 +12,4 @@ for n in 8192 12288 20480 32768; do
     SE_KSTAR_TAIL=$tail timeout 300 python tools/gemm_only.py C2 6 $n 2>&1 | tail -1 | sed "s/^/tail=$tail /" | tee -a $out/timing.log
   done
 done
-timeout 300 python tools/select_bench.py 2>&1 | tee $out/select.log
 timeout 600 python bench.py --steps 10 --warmup 3 --no-cpu-baseline --no-side-records > $out/bench.json 2> $out/bench.err; echo "bench rc=$?"; cut -c1-400 $out/bench.json
